@@ -1,0 +1,216 @@
+/*
+ * pyinterp_b200.h -- C-ABI of the B200-native regular-grid interpolation path.
+ *
+ * This is the drop-in boundary: the entry points below are what the reference's
+ * C++ host layer (the templated "vectorised drivers" under
+ * cxx/include/pyinterp/pybind/{geometric,windowed}/) binds instead of running
+ * its own per-point loops.  Nothing here uses C++ or torch types: plain
+ * pointers, sizes and POD structs only.
+ *
+ * Reference interfaces replaced (paths relative to the reference root):
+ *   pyi_geometric          <- geometric::pybind::bivariate      cxx/include/pyinterp/pybind/geometric/bivariate.hpp:127-161
+ *                             geometric::pybind::trivariate     cxx/include/pyinterp/pybind/geometric/trivariate.hpp:136-181
+ *                             geometric::pybind::quadrivariate  cxx/include/pyinterp/pybind/geometric/quadrivariate.hpp:162-218
+ *   pyi_windowed2d         <- windowed::pybind::bivariate       cxx/include/pyinterp/pybind/windowed/bivariate.hpp:86-115
+ *   pyi_axis_find_indexes  <- pybind Axis.find_indexes          cxx/include/pyinterp/pybind/axis.hpp:84-101
+ *                             (math::Axis<T>::find_indexes      cxx/include/pyinterp/math/axis.hpp:720-778)
+ *   pyi_axis_find_index    <- math::Axis<T>::find_index         cxx/include/pyinterp/math/axis.hpp:319-333
+ *   pyi_axis_create_*      <- math::Axis<T> constructors        cxx/include/pyinterp/math/axis.hpp:683-716
+ *   pyi_axis_create_from_desc: descriptor read from a live reference Axis
+ *                             (public accessors + pack(), axis.hpp:943-972)
+ *   pyi_grid_create        <- pybind::Grid<DataType, Axes...>   cxx/include/pyinterp/pybind/grid.hpp:214-226,443-481
+ *   pyi_format_bounds_error<- Grid::construct_bounds_error_description  pybind/grid.hpp:362-371
+ *
+ * All compute entry points run hand-written sm_100a CUDA kernels.  There is no
+ * CPU fallback: without a usable CUDA device they return PYI_NO_DEVICE.
+ */
+#ifndef PYINTERP_B200_H_
+#define PYINTERP_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PYI_ABI_VERSION 1
+
+/* ---- status codes -------------------------------------------------------- */
+typedef enum pyi_status {
+  PYI_OK = 0,
+  PYI_OOB = 1,        /* bounds_error set and a point is out of bounds: index/axis filled */
+  PYI_BAD_SHAPE = 2,  /* inconsistent sizes (reference: std::invalid_argument) */
+  PYI_BAD_ARG = 3,    /* invalid argument / unsupported combination */
+  PYI_NO_DEVICE = 4,  /* no CUDA device: the product path refuses to run */
+  PYI_CUDA_ERROR = 5, /* a CUDA call failed, see pyi_last_error() */
+  PYI_NOMEM = 6
+} pyi_status;
+
+/* ---- enumerations ---------------------------------------------------------- */
+typedef enum pyi_axis_kind { PYI_AXIS_REGULAR = 0, PYI_AXIS_IRREGULAR = 1 } pyi_axis_kind;
+typedef enum pyi_coord_type { PYI_COORD_F64 = 0, PYI_COORD_I64 = 1 } pyi_coord_type;
+
+/* Grid element types: the ten dtypes of pybind/grid.hpp:604-606,819-879. */
+typedef enum pyi_dtype {
+  PYI_I8 = 0, PYI_U8 = 1, PYI_I16 = 2, PYI_U16 = 3, PYI_I32 = 4,
+  PYI_U32 = 5, PYI_I64 = 6, PYI_U64 = 7, PYI_F32 = 8, PYI_F64 = 9
+} pyi_dtype;
+
+/* math/interpolate/geometric/bivariate.hpp:305-309 */
+typedef enum pyi_geometric_method { PYI_BILINEAR = 0, PYI_IDW = 1, PYI_NEAREST = 2 } pyi_geometric_method;
+/* math/interpolate/geometric/multivariate.hpp:24-27 */
+typedef enum pyi_axis_method { PYI_AXIS_LINEAR = 0, PYI_AXIS_NEAREST = 1 } pyi_axis_method;
+/* windowed 2-D evaluators on the path: bivariate/bicubic.hpp, bivariate/bilinear.hpp */
+typedef enum pyi_windowed_method { PYI_W_BICUBIC = 0, PYI_W_BILINEAR = 1 } pyi_windowed_method;
+/* the two boundary modes the reference exposes, config/windowed.hpp:88-98 */
+typedef enum pyi_boundary { PYI_BOUNDARY_UNDEF = 0, PYI_BOUNDARY_SHRINK = 1 } pyi_boundary;
+/* where caller buffers live */
+typedef enum pyi_mem { PYI_MEM_HOST = 0, PYI_MEM_DEVICE = 1 } pyi_mem;
+
+/* pyi_grid_create flags */
+#define PYI_GRID_DEFAULT 0u
+#define PYI_GRID_PACK_CELLS 1u /* also build the cell-packed copy (2^d corners contiguous) */
+#define PYI_GRID_BORROW_DEVICE 2u /* device data: keep the caller's pointer, do not copy */
+
+/* ---- PODs ---------------------------------------------------------------- */
+typedef union pyi_scalar {
+  double f;
+  int64_t i;
+} pyi_scalar;
+
+/*
+ * Flat mirror of a reference math::Axis<T> (T = double or int64_t).
+ * Every field is either readable through the reference's public accessors
+ * (size/front/increment/is_regular/is_ascending/is_periodic/min_value/
+ * max_value) or, for `period` when is_periodic == 0, from pack()
+ * (axis.hpp:959-960,967-968 write both unconditionally).
+ * `inv_step` and `step_2` are the container's cached values
+ * (container.hpp:547 `1.0/step`, :585 `step >> 1`; note flip() negates
+ * inv_step but leaves step_2 untouched, :567-570 / :473-477).
+ */
+typedef struct pyi_axis_desc {
+  int32_t kind;         /* pyi_axis_kind */
+  int32_t coord_type;   /* pyi_coord_type */
+  int64_t size;
+  int32_t is_ascending;
+  int32_t is_periodic;  /* is_periodic_ after compute_properties() */
+  pyi_scalar period;    /* period_ (may be non-zero with is_periodic == 0) */
+  pyi_scalar start;     /* regular: start_ ; irregular: points[0] */
+  pyi_scalar step;      /* regular only */
+  pyi_scalar min_value;
+  pyi_scalar max_value;
+  double inv_step;      /* regular f64 only */
+  int64_t step_2;       /* regular i64 only */
+  const void *points;   /* irregular only: `size` host values of coord_type */
+} pyi_axis_desc;
+
+/* config/geometric.hpp: spatial method, idw exponent, third/fourth axis
+ * methods; config/common.hpp: bounds_error, num_threads. */
+typedef struct pyi_geometric_config {
+  int32_t method;       /* pyi_geometric_method */
+  int32_t idw_exp;      /* default 2 */
+  int32_t z_method;     /* pyi_axis_method (3-D / 4-D) */
+  int32_t u_method;     /* pyi_axis_method (4-D) */
+  int32_t bounds_error; /* 0: NaN, 1: report first out-of-bounds point */
+  int32_t num_threads;  /* accepted for API parity, ignored on the GPU */
+} pyi_geometric_config;
+
+/* config/windowed.hpp: method, half window sizes (default 3/3, :244-247),
+ * boundary mode. */
+typedef struct pyi_windowed_config {
+  int32_t method;       /* pyi_windowed_method */
+  int32_t half_x;
+  int32_t half_y;
+  int32_t boundary;     /* pyi_boundary */
+  int32_t bounds_error;
+  int32_t num_threads;
+} pyi_windowed_config;
+
+typedef struct pyi_axis pyi_axis; /* opaque */
+typedef struct pyi_grid pyi_grid; /* opaque */
+
+/* ---- library ------------------------------------------------------------- */
+int pyi_abi_version(void);
+/* Number of usable CUDA devices (0 when there is none). */
+int pyi_device_count(void);
+/* Bind the calling thread to `device`. PYI_NO_DEVICE when there is none. */
+int pyi_set_device(int device);
+/* Thread-local text of the last failure. */
+const char *pyi_last_error(void);
+
+/* ---- axes (host side, no GPU needed) --------------------------------------- */
+pyi_axis *pyi_axis_create_f64(const double *values, int64_t n, double epsilon,
+                              int has_period, double period, int *status);
+pyi_axis *pyi_axis_create_i64(const int64_t *values, int64_t n, int64_t epsilon,
+                              int has_period, int64_t period, int *status);
+/* Build from a descriptor read off a live reference Axis (drop-in mode). */
+pyi_axis *pyi_axis_create_from_desc(const pyi_axis_desc *desc, int *status);
+/* Reverse the axis in place (Axis::flip, axis.hpp:250). */
+int pyi_axis_flip(pyi_axis *axis);
+/* Fill `out`; out->points aliases storage owned by `axis`. */
+int pyi_axis_describe(const pyi_axis *axis, pyi_axis_desc *out);
+void pyi_axis_destroy(pyi_axis *axis);
+
+/* ---- axis lookups (GPU) ---------------------------------------------------- */
+/* coords: n values of the axis' coord type. out_pairs: n x 2 int64, (-1,-1)
+ * when the coordinate cannot be bracketed. */
+int pyi_axis_find_indexes(const pyi_axis *axis, int64_t n, const void *coords,
+                          int64_t *out_pairs, int mem, void *stream);
+/* out: n int64, -1 when outside and !bounded. */
+int pyi_axis_find_index(const pyi_axis *axis, int64_t n, const void *coords,
+                        int bounded, int64_t *out, int mem, void *stream);
+
+/* ---- grids ----------------------------------------------------------------- */
+/* data: C-contiguous array of `dtype`, shape[i] == axes[i]->size.
+ * Periodic axes are only legal on axis 0; an int64 axis only on axis 2
+ * (pybind/grid.hpp:450-464, src/pybind/grid.cpp:68-92). The grid copies the
+ * axes; the caller may destroy them afterwards. */
+pyi_grid *pyi_grid_create(int ndim, const pyi_axis *const *axes, int dtype,
+                          const void *data, const int64_t *shape, int mem,
+                          unsigned flags, int *status);
+/* Re-upload the array (the reference borrows the caller's numpy buffer, which
+ * may be mutated between calls). Rebuilds the packed copy if there is one. */
+int pyi_grid_update(pyi_grid *grid, const void *data, int mem);
+/* Build (or rebuild) the cell-packed copy. */
+int pyi_grid_pack(pyi_grid *grid);
+void pyi_grid_destroy(pyi_grid *grid);
+
+/* ---- the hot path ---------------------------------------------------------- */
+/*
+ * x, y, u: n float64. z: n float64, or n int64 when axis 2 is an int64
+ * (temporal) axis. out: n float64 for f64/i64/u64 grids, n float32 otherwise
+ * (pybind/grid_dispatch.hpp:25-30). All n outputs are always written (NaN
+ * where a point cannot be bracketed). With cfg->bounds_error the call returns
+ * PYI_OOB and fills oob_index (lowest offending point) and oob_axis (first
+ * offending axis of that point in x,y,z,u order).
+ * mem == PYI_MEM_HOST: buffers are host memory, copies are staged and
+ * pipelined internally.  mem == PYI_MEM_DEVICE: buffers are device memory and
+ * the call only enqueues work on `stream` (a cudaStream_t, may be NULL); with
+ * bounds_error it synchronises the stream to read the flag.
+ */
+int pyi_geometric(const pyi_grid *grid, const pyi_geometric_config *cfg,
+                  int64_t n, const double *x, const double *y, const void *z,
+                  const double *u, void *out, int mem, int64_t *oob_index,
+                  int *oob_axis, void *stream);
+
+/* Windowed 2-D interpolation (bicubic / windowed bilinear). With
+ * bounds_error, PYI_OOB is reported only for points truly outside an axis
+ * (cache_loader.hpp:69-80), mapped by the host to std::out_of_range. */
+int pyi_windowed2d(const pyi_grid *grid, const pyi_windowed_config *cfg,
+                   int64_t n, const double *x, const double *y, void *out,
+                   int mem, int64_t *oob_index, int *oob_axis, void *stream);
+
+/* Reference text "{coord} is out of bounds for axis {x|y|z|u} [{min}, ...,
+ * {max}]" (pybind/grid.hpp:367-370). `coord` points to a double or an int64
+ * according to the axis. Returns the length written (excluding NUL). */
+int pyi_format_bounds_error(const pyi_grid *grid, int axis, const void *coord,
+                            char *buf, size_t len);
+
+/* Number of kernel launches issued by this library in this process. */
+int64_t pyi_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PYINTERP_B200_H_ */

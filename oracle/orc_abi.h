@@ -1,0 +1,121 @@
+/*
+ * orc_abi.h -- C-ABI shared by the two CPU checkers of this repo.
+ *
+ * TEST INFRASTRUCTURE ONLY.  Nothing under oracle/ is part of the product: only
+ * tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl
+ * reference legs may load these libraries, and only as the checker / the
+ * timed CPU baseline.  The product (pangeo-pyinterp_b200/) never links,
+ * imports or falls back to anything here.
+ *
+ * Two libraries export exactly this interface:
+ *   oracle/liboracle.so            plain-C restatement of the reference algorithm
+ *                                  (oracle/pyi_oracle.c), travels with the repo;
+ *   oracle/_ref/liboracle_ref.so   the reference's OWN headers compiled in place
+ *                                  from /root/reference (oracle/ref/ref_driver.cpp),
+ *                                  used to pin the restatement and as the
+ *                                  "reference" CPU baseline.
+ *
+ * The PODs (axis descriptor, configs, enums) are those of the product header so
+ * that one parametrised test drives the oracle, the reference build and the
+ * CUDA library with identical arguments.
+ */
+#ifndef ORC_ABI_H_
+#define ORC_ABI_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#include "../include/pyinterp_b200.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* Boundary modes of math/axis.hpp:32-38 beyond the two the windowed config
+ * exposes (PYI_BOUNDARY_UNDEF = 0, PYI_BOUNDARY_SHRINK = 1). */
+#define ORC_BOUNDARY_EXPAND 2
+#define ORC_BOUNDARY_WRAP 3
+#define ORC_BOUNDARY_SYM 4
+
+typedef struct orc_axis orc_axis;
+
+/* "reference" for _ref/liboracle_ref.so, "port" for liboracle.so */
+const char *orc_kind(void);
+
+/* math::Axis<T>(values, epsilon, period)  math/axis.hpp:683-716.  NULL on
+ * failure with the exception text in err. */
+orc_axis *orc_axis_new_f64(const double *values, int64_t n, double epsilon,
+                           int has_period, double period, char *err,
+                           size_t errlen);
+orc_axis *orc_axis_new_i64(const int64_t *values, int64_t n, int64_t epsilon,
+                           int has_period, int64_t period, char *err,
+                           size_t errlen);
+void orc_axis_free(orc_axis *axis);
+void orc_axis_flip(orc_axis *axis);
+/* desc->points aliases memory owned by the axis (irregular only). */
+int orc_axis_describe(const orc_axis *axis, pyi_axis_desc *desc);
+
+/* Axis::find_indexes(T)  math/axis.hpp:720-778; (-1,-1) when nullopt. */
+void orc_axis_find_indexes(const orc_axis *axis, int64_t n, const void *coords,
+                           int64_t *out_pairs);
+/* Axis::find_index(T, bounded)  math/axis.hpp:319-333. */
+void orc_axis_find_index(const orc_axis *axis, int64_t n, const void *coords,
+                         int bounded, int64_t *out);
+/* Axis::find_indexes(T, half, boundary)  math/axis.hpp:814-881.
+ * Returns 1 and fills idx[0..*count) and the centre pair, 0 for nullopt. */
+int orc_axis_find_window(const orc_axis *axis, const void *coord, int half,
+                         int boundary, int64_t *idx, int *count, int *c0,
+                         int *c1);
+
+/* geometric::pybind::{bi,tri,quadri}variate
+ * (pybind/geometric/bivariate.hpp:127-161, trivariate.hpp:136-181,
+ * quadrivariate.hpp:162-218) with Point = SphericalPoint and the reference's
+ * parallel_for (cfg->num_threads, 0 = hardware_concurrency).
+ * Returns PYI_OK, or PYI_OOB with the lowest offending point, its first
+ * offending axis and the reference message text. */
+int orc_geometric(int ndim, const orc_axis *const *axes, int dtype,
+                  const void *data, const pyi_geometric_config *cfg, int64_t n,
+                  const double *x, const double *y, const void *z,
+                  const double *u, void *out, int64_t *oob_index,
+                  int *oob_axis, char *msg, size_t msglen);
+
+/* windowed::pybind::bivariate (pybind/windowed/bivariate.hpp:86-115).
+ * stateless != 0: a fresh cache per point (what the GPU computes);
+ * stateless == 0: the reference's per-thread cache with its "still inside the
+ * central cell" fast path (history dependent). */
+int orc_windowed2d(const orc_axis *const *axes, int dtype, const void *data,
+                   const pyi_windowed_config *cfg, int stateless, int64_t n,
+                   const double *x, const double *y, void *out,
+                   int64_t *oob_index, int *oob_axis, char *msg,
+                   size_t msglen);
+
+/* ---- scalar probes used by the golden-vector tests ------------------------ */
+/* geometric evaluators (math/interpolate/geometric/bivariate.hpp).
+ * cartesian != 0: the Cartesian point type the reference unit tests use;
+ * cartesian == 0: SphericalPoint (the production path). */
+double orc_eval2d_f64(int method, int idw_exp, int cartesian, double x, double y,
+                      double x0, double y0, double x1, double y1, double q00,
+                      double q01, double q10, double q11);
+float orc_eval2d_f32(int method, int idw_exp, int cartesian, float x, float y,
+                     float x0, float y0, float x1, float y1, float q00,
+                     float q01, float q10, float q11);
+/* interpolate/linear.hpp:22-33, nearest.hpp:21-32 (Axis = double / int64) */
+double orc_axis_interp_f64(int method, double x, double x0, double x1, double y0,
+                           double y1);
+double orc_axis_interp_i64(int method, int64_t x, int64_t x0, int64_t x1,
+                           double y0, double y1);
+float orc_axis_interp_i64_f32(int method, int64_t x, int64_t x0, int64_t x1,
+                              float y0, float y1);
+/* windowed evaluators on an explicit window: za is [nx][ny] row-major.
+ * method: pyi_windowed_method. (bivariate/bicubic.hpp, bivariate/bilinear.hpp) */
+double orc_window_eval(int method, const double *xa, int nx, const double *ya,
+                       int ny, const double *za, double x, double y);
+/* natural cubic spline value (derivative == 0) or first derivative at x
+ * (univariate/cspline.hpp, cspline_base.hpp). */
+double orc_cspline(const double *xa, const double *ya, int n, double x,
+                   int derivative);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ORC_ABI_H_ */

@@ -1,0 +1,39 @@
+import importlib
+import os
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for p in (ROOT, os.path.join(ROOT, "oracle"), os.path.dirname(os.path.abspath(__file__))):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
+
+
+@pytest.fixture(scope="session")
+def port():
+    import orc
+    return orc.Oracle("port")
+
+
+@pytest.fixture(scope="session")
+def ref():
+    import orc
+    if not orc.available("reference"):
+        pytest.skip("oracle/_ref/liboracle_ref.so not built (needs /root/reference)")
+    return orc.Oracle("reference")
+
+
+@pytest.fixture(scope="session")
+def synthetic():
+    return importlib.import_module("pangeo-pyinterp_b200.synthetic")
+
+
+@pytest.fixture(scope="session")
+def pyi():
+    """The product package (needs the CUDA library; GPU tests only)."""
+    return importlib.import_module("pangeo-pyinterp_b200")
