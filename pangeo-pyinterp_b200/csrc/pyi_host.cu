@@ -1,0 +1,791 @@
+// pyi_host.cu -- the C-ABI of include/pyinterp_b200.h: axis / grid handles,
+// device residency, the host-buffer pipeline and the bounds-error protocol.
+// No compute happens on the host: every entry point that produces indexes or
+// values launches the sm_100a kernels of pyi_kernels.cu, and returns
+// PYI_NO_DEVICE when no CUDA device is usable.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <charconv>
+#include <cstdio>
+#include <cstring>
+#include <memory>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "../../include/pyinterp_b200.h"
+#include "pyi_axis_host.hpp"
+#include "pyi_kernels.cuh"
+
+namespace {
+
+thread_local std::string g_error;
+
+int fail(int status, const std::string& what) {
+  g_error = what;
+  return status;
+}
+int cuda_fail(cudaError_t e, const char* where) {
+  g_error = std::string(where) + ": " + cudaGetErrorString(e);
+  return e == cudaErrorMemoryAllocation ? PYI_NOMEM : PYI_CUDA_ERROR;
+}
+#define PYI_CUDA(call)                                 \
+  do {                                                 \
+    cudaError_t e__ = (call);                          \
+    if (e__ != cudaSuccess) return cuda_fail(e__, #call); \
+  } while (0)
+
+int device_count_cached() {
+  static int n = -1;
+  if (n < 0) {
+    int c = 0;
+    if (cudaGetDeviceCount(&c) != cudaSuccess) {
+      cudaGetLastError();
+      c = 0;
+    }
+    n = c;
+  }
+  return n;
+}
+
+int require_device() {
+  if (device_count_cached() <= 0) {
+    return fail(PYI_NO_DEVICE,
+                "no CUDA device: pyinterp_b200 runs on the GPU only (no CPU fallback)");
+  }
+  return PYI_OK;
+}
+
+size_t dtype_size(int dtype) {
+  switch (dtype) {
+    case PYI_I8: case PYI_U8: return 1;
+    case PYI_I16: case PYI_U16: return 2;
+    case PYI_I32: case PYI_U32: case PYI_F32: return 4;
+    default: return 8;
+  }
+}
+bool result_is_f64(int dtype) {  // pybind/grid_dispatch.hpp:25-30
+  return dtype == PYI_F64 || dtype == PYI_I64 || dtype == PYI_U64;
+}
+
+// Device mirror of an axis on the current device (uploaded once per device).
+int device_axis(pyi_axis* a, pyi::DAxis& out) {
+  const pyi_axis_desc& d = a->d;
+  if (d.size >= 2147483646LL) {
+    return fail(PYI_BAD_ARG, "axis too large for the device kernels");
+  }
+  std::memset(&out, 0, sizeof(out));
+  out.kind = d.kind;
+  out.coord_i64 = d.coord_type == PYI_COORD_I64;
+  out.asc = d.is_ascending;
+  out.periodic = d.is_periodic;
+  out.n = static_cast<int32_t>(d.size);
+  if (d.coord_type == PYI_COORD_F64) {
+    out.start = d.start.f;
+    out.step = d.step.f;
+    out.inv_step = d.inv_step;
+    out.period = d.period.f;
+    out.inv_period = d.period.f != 0.0 ? 1.0 / d.period.f : 0.0;
+    out.min = d.min_value.f;
+    out.max = d.max_value.f;
+  } else {
+    out.istart = d.start.i;
+    out.istep = d.step.i;
+    out.istep2 = d.step_2;
+    out.iperiod = d.period.i;
+    out.imin = d.min_value.i;
+    out.imax = d.max_value.i;
+  }
+  if (d.kind == PYI_AXIS_IRREGULAR) {
+    int dev = 0;
+    PYI_CUDA(cudaGetDevice(&dev));
+    std::lock_guard<std::mutex> lock(a->mu);
+    auto it = a->dev.find(dev);
+    if (it == a->dev.end()) {
+      pyi_axis::Dev m;
+      const size_t bytes = static_cast<size_t>(d.size) * 8;
+      PYI_CUDA(cudaMalloc(&m.points, bytes));
+      PYI_CUDA(cudaMemcpy(m.points, d.points, bytes, cudaMemcpyHostToDevice));
+      if (a->lut_bins > 0) {
+        const size_t lb = a->lut.size() * sizeof(int32_t);
+        PYI_CUDA(cudaMalloc(reinterpret_cast<void**>(&m.lut), lb));
+        PYI_CUDA(cudaMemcpy(m.lut, a->lut.data(), lb, cudaMemcpyHostToDevice));
+      }
+      it = a->dev.emplace(dev, m).first;
+    }
+    out.points = it->second.points;
+    out.lut = it->second.lut;
+    out.lut_bins = it->second.lut ? a->lut_bins : 0;
+    out.lut_min = a->lut_min;
+    out.lut_inv = a->lut_inv;
+  }
+  return PYI_OK;
+}
+
+void free_axis_device(pyi_axis* a) {
+  for (auto& kv : a->dev) {
+    int cur = 0;
+    cudaGetDevice(&cur);
+    cudaSetDevice(kv.first);
+    cudaFree(kv.second.points);
+    cudaFree(kv.second.lut);
+    cudaSetDevice(cur);
+  }
+  a->dev.clear();
+}
+
+bool host_pinned(const void* p) {
+  cudaPointerAttributes attr{};
+  if (cudaPointerGetAttributes(&attr, p) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return attr.type == cudaMemoryTypeHost;
+}
+
+void parallel_memcpy(void* dst, const void* src, size_t bytes) {
+  const size_t kMin = 8u << 20;
+  unsigned hw = std::thread::hardware_concurrency();
+  const unsigned nt = static_cast<unsigned>(
+      std::min<size_t>(std::max(1u, std::min(hw, 8u)), std::max<size_t>(1, bytes / kMin)));
+  if (nt <= 1) {
+    std::memcpy(dst, src, bytes);
+    return;
+  }
+  std::vector<std::thread> th;
+  const size_t part = (bytes / nt + 63) & ~static_cast<size_t>(63);
+  for (unsigned t = 0; t < nt; ++t) {
+    const size_t off = std::min(bytes, t * part);
+    const size_t len = std::min(part, bytes - off);
+    if (len == 0) break;
+    th.emplace_back([=] {
+      std::memcpy(static_cast<char*>(dst) + off, static_cast<const char*>(src) + off, len);
+    });
+  }
+  for (auto& t : th) t.join();
+}
+
+// ---------------------------------------------------------------------------
+// Host-buffer pipeline: the point arrays are cut into chunks that flow
+// H2D -> kernel -> D2H through kSlots stream slots, so the two copy engines
+// and the SMs overlap.  Caller buffers that are already page-locked are copied
+// directly; pageable ones are staged through page-locked buffers.
+// ---------------------------------------------------------------------------
+constexpr int kSlots = 3;
+constexpr long long kChunk = 1LL << 23;  // points per chunk
+
+struct Slot {
+  cudaStream_t stream{nullptr};
+  cudaEvent_t done{nullptr};
+  char* dev{nullptr};     // device chunk buffers
+  char* pinned{nullptr};  // staging (allocated on first pageable use)
+  bool busy{false};
+  long long begin{0}, count{0};
+};
+
+struct Workspace {
+  int device{-1};
+  Slot slot[kSlots];
+  size_t dev_bytes{0};
+  size_t pinned_bytes{0};
+  unsigned long long* oob_key{nullptr};       // device
+  unsigned long long* oob_host{nullptr};      // pinned
+  std::recursive_mutex mu;
+  ~Workspace() { release(); }
+  void release() {
+    for (auto& s : slot) {
+      if (s.stream) cudaStreamDestroy(s.stream);
+      if (s.done) cudaEventDestroy(s.done);
+      cudaFree(s.dev);
+      cudaFreeHost(s.pinned);
+      s = Slot{};
+    }
+    cudaFree(oob_key);
+    cudaFreeHost(oob_host);
+    oob_key = nullptr;
+    oob_host = nullptr;
+    dev_bytes = pinned_bytes = 0;
+  }
+  int ensure(size_t need_dev, size_t need_pinned) {
+    int dev = 0;
+    PYI_CUDA(cudaGetDevice(&dev));
+    if (dev != device) {
+      release();
+      device = dev;
+    }
+    if (!oob_key) {
+      PYI_CUDA(cudaMalloc(reinterpret_cast<void**>(&oob_key), sizeof(unsigned long long)));
+      PYI_CUDA(cudaMallocHost(reinterpret_cast<void**>(&oob_host), sizeof(unsigned long long)));
+    }
+    for (auto& s : slot) {
+      if (!s.stream) PYI_CUDA(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+      if (!s.done) PYI_CUDA(cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
+    }
+    if (need_dev > dev_bytes) {
+      for (auto& s : slot) {
+        cudaFree(s.dev);
+        s.dev = nullptr;
+        PYI_CUDA(cudaMalloc(reinterpret_cast<void**>(&s.dev), need_dev));
+      }
+      dev_bytes = need_dev;
+    }
+    if (need_pinned > pinned_bytes) {
+      for (auto& s : slot) {
+        cudaFreeHost(s.pinned);
+        s.pinned = nullptr;
+        PYI_CUDA(cudaMallocHost(reinterpret_cast<void**>(&s.pinned), need_pinned));
+      }
+      pinned_bytes = need_pinned;
+    }
+    return PYI_OK;
+  }
+};
+
+Workspace& workspace() {
+  static Workspace w;
+  return w;
+}
+
+// One input or output stream of a pipelined call.
+struct Column {
+  const void* host_in{nullptr};  // input columns
+  void* host_out{nullptr};       // output column
+  size_t elem{8};
+  bool pinned{false};
+  size_t dev_off{0};  // offset inside the slot buffers
+};
+
+// Runs `launch(slot_stream, begin, count, dev_ptrs...)` over all chunks.
+template <typename Launch>
+int run_pipeline(long long n, std::vector<Column>& cols, Launch&& launch) {
+  Workspace& ws = workspace();
+  std::unique_lock<std::recursive_mutex> lock(ws.mu);
+  const long long chunk = std::min<long long>(kChunk, std::max<long long>(n, 1));
+  size_t off = 0;
+  bool need_staging = false;
+  for (auto& c : cols) {
+    c.pinned = host_pinned(c.host_in ? c.host_in : c.host_out);
+    need_staging |= !c.pinned;
+    c.dev_off = off;
+    off += (static_cast<size_t>(chunk) * c.elem + 255) & ~static_cast<size_t>(255);
+  }
+  int st = ws.ensure(off, need_staging ? off : 0);
+  if (st != PYI_OK) return st;
+
+  auto drain = [&](Slot& s) -> int {
+    if (!s.busy) return PYI_OK;
+    PYI_CUDA(cudaEventSynchronize(s.done));
+    for (auto& c : cols) {
+      if (c.host_out && !c.pinned) {
+        parallel_memcpy(static_cast<char*>(c.host_out) + static_cast<size_t>(s.begin) * c.elem,
+                        s.pinned + c.dev_off, static_cast<size_t>(s.count) * c.elem);
+      }
+    }
+    s.busy = false;
+    return PYI_OK;
+  };
+
+  int which = 0;
+  for (long long begin = 0; begin < n; begin += chunk, which = (which + 1) % kSlots) {
+    Slot& s = ws.slot[which];
+    st = drain(s);
+    if (st != PYI_OK) return st;
+    const long long count = std::min(chunk, n - begin);
+    s.begin = begin;
+    s.count = count;
+    for (auto& c : cols) {
+      if (!c.host_in) continue;
+      const size_t bytes = static_cast<size_t>(count) * c.elem;
+      const char* src = static_cast<const char*>(c.host_in) + static_cast<size_t>(begin) * c.elem;
+      if (!c.pinned) {
+        parallel_memcpy(s.pinned + c.dev_off, src, bytes);
+        src = s.pinned + c.dev_off;
+      }
+      PYI_CUDA(cudaMemcpyAsync(s.dev + c.dev_off, src, bytes, cudaMemcpyHostToDevice, s.stream));
+    }
+    cudaError_t e = launch(s.stream, begin, count, s.dev);
+    if (e != cudaSuccess) return cuda_fail(e, "kernel launch");
+    for (auto& c : cols) {
+      if (!c.host_out) continue;
+      const size_t bytes = static_cast<size_t>(count) * c.elem;
+      char* dst = c.pinned ? static_cast<char*>(c.host_out) + static_cast<size_t>(begin) * c.elem
+                           : s.pinned + c.dev_off;
+      PYI_CUDA(cudaMemcpyAsync(dst, s.dev + c.dev_off, bytes, cudaMemcpyDeviceToHost, s.stream));
+    }
+    PYI_CUDA(cudaEventRecord(s.done, s.stream));
+    s.busy = true;
+  }
+  for (int k = 0; k < kSlots; ++k) {
+    st = drain(ws.slot[(which + k) % kSlots]);
+    if (st != PYI_OK) return st;
+  }
+  return PYI_OK;
+}
+
+// Shared tail of the compute entry points: decode the atomicMin key.
+int report_oob(unsigned long long key, int64_t* oob_index, int* oob_axis) {
+  if (key == pyi::kNoOob) return PYI_OK;
+  if (oob_index) *oob_index = static_cast<int64_t>(key >> 2);
+  if (oob_axis) *oob_axis = static_cast<int>(key & 3);
+  return PYI_OOB;
+}
+
+}  // namespace
+
+struct pyi_grid {
+  int ndim{0};
+  int dtype{0};
+  int device{0};
+  int64_t shape[4]{1, 1, 1, 1};
+  size_t bytes{0};
+  std::unique_ptr<pyi_axis> axes[4];
+  pyi::DAxis dax[4];
+  void* d_data{nullptr};
+  bool borrowed{false};
+  void* d_packed{nullptr};
+  unsigned long long* d_oob{nullptr};  // for device-memory calls
+};
+
+extern "C" {
+
+int pyi_abi_version(void) { return PYI_ABI_VERSION; }
+int pyi_device_count(void) { return device_count_cached(); }
+const char* pyi_last_error(void) { return g_error.c_str(); }
+int64_t pyi_launch_count(void) { return pyi::launch_count(); }
+
+int pyi_set_device(int device) {
+  int st = require_device();
+  if (st != PYI_OK) return st;
+  PYI_CUDA(cudaSetDevice(device));
+  return PYI_OK;
+}
+
+// ---- axes -----------------------------------------------------------------
+pyi_axis* pyi_axis_create_f64(const double* values, int64_t n, double epsilon, int has_period,
+                              double period, int* status) {
+  std::string err;
+  pyi_axis* a = pyi_host::make_axis<double>(values, n, epsilon, has_period != 0, period, err);
+  if (!a) g_error = err;
+  if (status) *status = a ? PYI_OK : PYI_BAD_ARG;
+  return a;
+}
+
+pyi_axis* pyi_axis_create_i64(const int64_t* values, int64_t n, int64_t epsilon, int has_period,
+                              int64_t period, int* status) {
+  std::string err;
+  pyi_axis* a = pyi_host::make_axis<int64_t>(values, n, epsilon, has_period != 0, period, err);
+  if (!a) g_error = err;
+  if (status) *status = a ? PYI_OK : PYI_BAD_ARG;
+  return a;
+}
+
+pyi_axis* pyi_axis_create_from_desc(const pyi_axis_desc* desc, int* status) {
+  if (!desc || desc->size <= 0 ||
+      (desc->kind == PYI_AXIS_IRREGULAR && desc->points == nullptr)) {
+    g_error = "invalid axis descriptor";
+    if (status) *status = PYI_BAD_ARG;
+    return nullptr;
+  }
+  auto a = new pyi_axis();
+  a->d = *desc;
+  if (desc->kind == PYI_AXIS_IRREGULAR) {
+    if (desc->coord_type == PYI_COORD_F64) {
+      const double* p = static_cast<const double*>(desc->points);
+      a->pf.assign(p, p + desc->size);
+    } else {
+      const int64_t* p = static_cast<const int64_t*>(desc->points);
+      a->pi.assign(p, p + desc->size);
+    }
+  }
+  a->fix_points();
+  pyi_host::build_lut(*a);
+  if (status) *status = PYI_OK;
+  return a;
+}
+
+int pyi_axis_flip(pyi_axis* axis) {
+  if (!axis) return fail(PYI_BAD_ARG, "null axis");
+  {
+    std::lock_guard<std::mutex> lock(axis->mu);
+    free_axis_device(axis);
+  }
+  pyi_host::flip_axis(*axis);
+  return PYI_OK;
+}
+
+int pyi_axis_describe(const pyi_axis* axis, pyi_axis_desc* out) {
+  if (!axis || !out) return fail(PYI_BAD_ARG, "null argument");
+  *out = axis->d;
+  return PYI_OK;
+}
+
+void pyi_axis_destroy(pyi_axis* axis) {
+  if (axis) {
+    free_axis_device(axis);
+    delete axis;
+  }
+}
+
+// ---- axis lookups -----------------------------------------------------------
+static int axis_lookup(const pyi_axis* axis_c, int64_t n, const void* coords, int bounded,
+                       int64_t* out, int mem, void* stream, bool pairs) {
+  int st = require_device();
+  if (st != PYI_OK) return st;
+  if (!axis_c || n < 0 || (n > 0 && (!coords || !out))) return fail(PYI_BAD_ARG, "null argument");
+  pyi_axis* axis = const_cast<pyi_axis*>(axis_c);
+  pyi::FindParams p{};
+  st = device_axis(axis, p.ax);
+  if (st != PYI_OK) return st;
+  p.bounded = bounded;
+  const size_t out_elem = pairs ? 16 : 8;
+  if (mem == PYI_MEM_DEVICE) {
+    p.n = n;
+    p.coords = coords;
+    p.out = reinterpret_cast<long long*>(out);
+    cudaError_t e = pairs ? pyi::launch_find_indexes(p, static_cast<cudaStream_t>(stream))
+                          : pyi::launch_find_index(p, static_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) return cuda_fail(e, "find_indexes");
+    return PYI_OK;
+  }
+  std::vector<Column> cols(2);
+  cols[0].host_in = coords;
+  cols[0].elem = 8;
+  cols[1].host_out = out;
+  cols[1].elem = out_elem;
+  return run_pipeline(n, cols, [&](cudaStream_t s, long long, long long count, char* dev) {
+    pyi::FindParams q = p;
+    q.n = count;
+    q.coords = dev + cols[0].dev_off;
+    q.out = reinterpret_cast<long long*>(dev + cols[1].dev_off);
+    return pairs ? pyi::launch_find_indexes(q, s) : pyi::launch_find_index(q, s);
+  });
+}
+
+int pyi_axis_find_indexes(const pyi_axis* axis, int64_t n, const void* coords,
+                          int64_t* out_pairs, int mem, void* stream) {
+  return axis_lookup(axis, n, coords, 0, out_pairs, mem, stream, true);
+}
+
+int pyi_axis_find_index(const pyi_axis* axis, int64_t n, const void* coords, int bounded,
+                        int64_t* out, int mem, void* stream) {
+  return axis_lookup(axis, n, coords, bounded, out, mem, stream, false);
+}
+
+// ---- grids ------------------------------------------------------------------
+pyi_grid* pyi_grid_create(int ndim, const pyi_axis* const* axes, int dtype, const void* data,
+                          const int64_t* shape, int mem, unsigned flags, int* status) {
+  auto set = [&](int s) {
+    if (status) *status = s;
+    return static_cast<pyi_grid*>(nullptr);
+  };
+  if (require_device() != PYI_OK) return set(PYI_NO_DEVICE);
+  if (ndim < 2 || ndim > 4 || !axes || !data || !shape || dtype < PYI_I8 || dtype > PYI_F64) {
+    g_error = "pyi_grid_create: invalid argument";
+    return set(PYI_BAD_ARG);
+  }
+  auto g = std::make_unique<pyi_grid>();
+  g->ndim = ndim;
+  g->dtype = dtype;
+  size_t count = 1;
+  static const char* labels[4] = {"x", "y", "z", "u"};
+  for (int k = 0; k < ndim; ++k) {
+    if (!axes[k]) {
+      g_error = "pyi_grid_create: null axis";
+      return set(PYI_BAD_ARG);
+    }
+    // pybind/grid.hpp:443-481: only x may be periodic, shape must match the
+    // axes; src/pybind/grid.cpp:68-92: an int64 (temporal) axis only on z
+    if (k > 0 && axes[k]->d.is_periodic) {
+      g_error = std::string(labels[k]) + "-axis cannot be a circle";
+      return set(PYI_BAD_ARG);
+    }
+    if (shape[k] != axes[k]->d.size) {
+      g_error = std::string(labels[k]) + " axis size (" + std::to_string(axes[k]->d.size) +
+                ") doesn't match array shape[" + std::to_string(k) + "] (" +
+                std::to_string(shape[k]) + ")";
+      return set(PYI_BAD_SHAPE);
+    }
+    if (axes[k]->d.coord_type == PYI_COORD_I64 && k != 2) {
+      g_error = "an int64 (temporal) axis is only supported on the z axis";
+      return set(PYI_BAD_ARG);
+    }
+    g->shape[k] = shape[k];
+    count *= static_cast<size_t>(shape[k]);
+    g->axes[k] = std::make_unique<pyi_axis>(*axes[k]);
+  }
+  g->bytes = count * dtype_size(dtype);
+  if (cudaGetDevice(&g->device) != cudaSuccess) {
+    g_error = "cudaGetDevice failed";
+    return set(PYI_CUDA_ERROR);
+  }
+  for (int k = 0; k < ndim; ++k) {
+    int st = device_axis(g->axes[k].get(), g->dax[k]);
+    if (st != PYI_OK) return set(st);
+  }
+  if (mem == PYI_MEM_DEVICE && (flags & PYI_GRID_BORROW_DEVICE)) {
+    g->d_data = const_cast<void*>(data);
+    g->borrowed = true;
+  } else {
+    cudaError_t e = cudaMalloc(&g->d_data, std::max<size_t>(g->bytes, 16));
+    if (e != cudaSuccess) return set(cuda_fail(e, "cudaMalloc(grid)"));
+    e = cudaMemcpy(g->d_data, data, g->bytes,
+                   mem == PYI_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) {
+      cudaFree(g->d_data);
+      return set(cuda_fail(e, "cudaMemcpy(grid)"));
+    }
+  }
+  cudaError_t e = cudaMalloc(reinterpret_cast<void**>(&g->d_oob), sizeof(unsigned long long));
+  if (e != cudaSuccess) return set(cuda_fail(e, "cudaMalloc(oob)"));
+  pyi_grid* raw = g.release();
+  if (flags & PYI_GRID_PACK_CELLS) {
+    int st = pyi_grid_pack(raw);
+    if (st != PYI_OK) {
+      pyi_grid_destroy(raw);
+      return set(st);
+    }
+  }
+  if (status) *status = PYI_OK;
+  return raw;
+}
+
+int pyi_grid_update(pyi_grid* grid, const void* data, int mem) {
+  if (!grid || !data) return fail(PYI_BAD_ARG, "null argument");
+  if (grid->borrowed) {
+    grid->d_data = const_cast<void*>(data);
+  } else {
+    PYI_CUDA(cudaMemcpy(grid->d_data, data, grid->bytes,
+                        mem == PYI_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice));
+  }
+  if (grid->d_packed) return pyi_grid_pack(grid);
+  return PYI_OK;
+}
+
+int pyi_grid_pack(pyi_grid* grid) {
+  if (!grid) return fail(PYI_BAD_ARG, "null grid");
+  if (grid->ndim != 2) return PYI_OK;  // cell packing exists for 2-D grids only
+  const size_t cells = static_cast<size_t>(grid->shape[0]) * static_cast<size_t>(grid->shape[1]);
+  const size_t elem = result_is_f64(grid->dtype) ? 8 : 4;
+  if (!grid->d_packed) {
+    PYI_CUDA(cudaMalloc(&grid->d_packed, cells * 4 * elem));
+  }
+  cudaError_t e = pyi::launch_pack_cells2d(grid->d_data, grid->dtype,
+                                           static_cast<int>(grid->shape[0]),
+                                           static_cast<int>(grid->shape[1]), grid->d_packed, nullptr);
+  if (e != cudaSuccess) return cuda_fail(e, "pack_cells2d");
+  PYI_CUDA(cudaStreamSynchronize(nullptr));
+  return PYI_OK;
+}
+
+void pyi_grid_destroy(pyi_grid* grid) {
+  if (!grid) return;
+  if (!grid->borrowed) cudaFree(grid->d_data);
+  cudaFree(grid->d_packed);
+  cudaFree(grid->d_oob);
+  for (auto& a : grid->axes) {
+    if (a) free_axis_device(a.get());
+  }
+  delete grid;
+}
+
+// ---- hot path ---------------------------------------------------------------
+int pyi_geometric(const pyi_grid* grid, const pyi_geometric_config* cfg, int64_t n,
+                  const double* x, const double* y, const void* z, const double* u, void* out,
+                  int mem, int64_t* oob_index, int* oob_axis, void* stream) {
+  int st = require_device();
+  if (st != PYI_OK) return st;
+  if (!grid || !cfg || n < 0) return fail(PYI_BAD_ARG, "pyi_geometric: null argument");
+  if (n > 0 && (!x || !y || !out || (grid->ndim >= 3 && !z) || (grid->ndim >= 4 && !u))) {
+    return fail(PYI_BAD_SHAPE, "pyi_geometric: a coordinate array is missing for this grid");
+  }
+  if (cfg->method < PYI_BILINEAR || cfg->method > PYI_NEAREST) {
+    return fail(PYI_BAD_ARG, "pyi_geometric: unknown method");
+  }
+  pyi::GeoParams p{};
+  for (int k = 0; k < grid->ndim; ++k) p.ax[k] = grid->dax[k];
+  p.data = grid->d_data;
+  p.packed = grid->d_packed;
+  p.dtype = grid->dtype;
+  p.ndim = grid->ndim;
+  p.method = cfg->method;
+  p.idw_exp = cfg->idw_exp;
+  p.z_method = cfg->z_method;
+  p.u_method = cfg->u_method;
+  p.bounds_error = cfg->bounds_error;
+  if (n == 0) return PYI_OK;
+  const size_t out_elem = result_is_f64(grid->dtype) ? 8 : 4;
+
+  if (mem == PYI_MEM_DEVICE) {
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    p.n = n;
+    p.x = x;
+    p.y = y;
+    p.z = z;
+    p.u = u;
+    p.out = out;
+    p.oob_key = grid->d_oob;
+    if (cfg->bounds_error) {
+      PYI_CUDA(cudaMemsetAsync(grid->d_oob, 0xff, sizeof(unsigned long long), s));
+    }
+    cudaError_t e = pyi::launch_geometric(p, s);
+    if (e != cudaSuccess) return cuda_fail(e, "geometric kernel");
+    if (cfg->bounds_error) {
+      unsigned long long key = pyi::kNoOob;
+      PYI_CUDA(cudaMemcpyAsync(&key, grid->d_oob, sizeof(key), cudaMemcpyDeviceToHost, s));
+      PYI_CUDA(cudaStreamSynchronize(s));
+      return report_oob(key, oob_index, oob_axis);
+    }
+    return PYI_OK;
+  }
+
+  std::vector<Column> cols;
+  auto add_in = [&](const void* ptr) {
+    Column c;
+    c.host_in = ptr;
+    cols.push_back(c);
+    return cols.size() - 1;
+  };
+  const size_t cx = add_in(x), cy = add_in(y);
+  const size_t cz = grid->ndim >= 3 ? add_in(z) : 0;
+  const size_t cu = grid->ndim >= 4 ? add_in(u) : 0;
+  Column co;
+  co.host_out = out;
+  co.elem = out_elem;
+  cols.push_back(co);
+  const size_t cout_ = cols.size() - 1;
+  Workspace& ws = workspace();
+  // the key lives in the workspace; the lock is held for the whole call
+  std::lock_guard<std::recursive_mutex> ws_lock(ws.mu);
+  st = ws.ensure(0, 0);
+  if (st != PYI_OK) return st;
+  PYI_CUDA(cudaMemset(ws.oob_key, 0xff, sizeof(unsigned long long)));
+  st = run_pipeline(n, cols, [&](cudaStream_t s, long long begin, long long count, char* dev) {
+    pyi::GeoParams q = p;
+    q.n = count;
+    q.x = reinterpret_cast<const double*>(dev + cols[cx].dev_off);
+    q.y = reinterpret_cast<const double*>(dev + cols[cy].dev_off);
+    if (grid->ndim >= 3) q.z = dev + cols[cz].dev_off;
+    if (grid->ndim >= 4) q.u = reinterpret_cast<const double*>(dev + cols[cu].dev_off);
+    q.out = dev + cols[cout_].dev_off;
+    q.oob_key = ws.oob_key;
+    q.index_base = begin;
+    return pyi::launch_geometric(q, s);
+  });
+  if (st != PYI_OK) return st;
+  if (cfg->bounds_error) {
+    unsigned long long key = pyi::kNoOob;
+    PYI_CUDA(cudaMemcpy(&key, ws.oob_key, sizeof(key), cudaMemcpyDeviceToHost));
+    return report_oob(key, oob_index, oob_axis);
+  }
+  return PYI_OK;
+}
+
+int pyi_windowed2d(const pyi_grid* grid, const pyi_windowed_config* cfg, int64_t n,
+                   const double* x, const double* y, void* out, int mem, int64_t* oob_index,
+                   int* oob_axis, void* stream) {
+  int st = require_device();
+  if (st != PYI_OK) return st;
+  if (!grid || !cfg || n < 0) return fail(PYI_BAD_ARG, "pyi_windowed2d: null argument");
+  if (grid->ndim != 2) return fail(PYI_BAD_ARG, "pyi_windowed2d: bivariate requires 2D grid");
+  if (cfg->half_x < 1 || cfg->half_y < 1) {
+    return fail(PYI_BAD_ARG, "Half window sizes must be at least 1");  // cache.hpp:258-260
+  }
+  if (cfg->half_x > 16 || cfg->half_y > 16) {
+    return fail(PYI_BAD_ARG, "pyi_windowed2d: half window sizes above 16 are not supported");
+  }
+  if (cfg->method != PYI_W_BICUBIC && cfg->method != PYI_W_BILINEAR) {
+    return fail(PYI_BAD_ARG, "pyi_windowed2d: unknown method");
+  }
+  if (n > 0 && (!x || !y || !out)) return fail(PYI_BAD_SHAPE, "pyi_windowed2d: missing array");
+  if (n == 0) return PYI_OK;
+  pyi::WinParams p{};
+  p.ax[0] = grid->dax[0];
+  p.ax[1] = grid->dax[1];
+  p.data = grid->d_data;
+  p.dtype = grid->dtype;
+  p.method = cfg->method;
+  p.half_x = cfg->half_x;
+  p.half_y = cfg->half_y;
+  p.boundary = cfg->boundary;
+  p.bounds_error = cfg->bounds_error;
+  const size_t out_elem = result_is_f64(grid->dtype) ? 8 : 4;
+  if (mem == PYI_MEM_DEVICE) {
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    p.n = n;
+    p.x = x;
+    p.y = y;
+    p.out = out;
+    p.oob_key = grid->d_oob;
+    if (cfg->bounds_error) {
+      PYI_CUDA(cudaMemsetAsync(grid->d_oob, 0xff, sizeof(unsigned long long), s));
+    }
+    cudaError_t e = pyi::launch_windowed2d(p, s);
+    if (e != cudaSuccess) return cuda_fail(e, "windowed2d kernel");
+    if (cfg->bounds_error) {
+      unsigned long long key = pyi::kNoOob;
+      PYI_CUDA(cudaMemcpyAsync(&key, grid->d_oob, sizeof(key), cudaMemcpyDeviceToHost, s));
+      PYI_CUDA(cudaStreamSynchronize(s));
+      return report_oob(key, oob_index, oob_axis);
+    }
+    return PYI_OK;
+  }
+  std::vector<Column> cols(3);
+  cols[0].host_in = x;
+  cols[1].host_in = y;
+  cols[2].host_out = out;
+  cols[2].elem = out_elem;
+  Workspace& ws = workspace();
+  std::lock_guard<std::recursive_mutex> ws_lock(ws.mu);
+  st = ws.ensure(0, 0);
+  if (st != PYI_OK) return st;
+  PYI_CUDA(cudaMemset(ws.oob_key, 0xff, sizeof(unsigned long long)));
+  st = run_pipeline(n, cols, [&](cudaStream_t s, long long begin, long long count, char* dev) {
+    pyi::WinParams q = p;
+    q.n = count;
+    q.x = reinterpret_cast<const double*>(dev + cols[0].dev_off);
+    q.y = reinterpret_cast<const double*>(dev + cols[1].dev_off);
+    q.out = dev + cols[2].dev_off;
+    q.oob_key = ws.oob_key;
+    q.index_base = begin;
+    return pyi::launch_windowed2d(q, s);
+  });
+  if (st != PYI_OK) return st;
+  if (cfg->bounds_error) {
+    unsigned long long key = pyi::kNoOob;
+    PYI_CUDA(cudaMemcpy(&key, ws.oob_key, sizeof(key), cudaMemcpyDeviceToHost));
+    return report_oob(key, oob_index, oob_axis);
+  }
+  return PYI_OK;
+}
+
+// "{coord} is out of bounds for axis {label} [{min}, ..., {max}]"
+// (pybind/grid.hpp:362-371).  Doubles are printed like std::format("{}"):
+// shortest round-trip digits via std::to_chars.  int64 coordinates are printed
+// as integers; the TemporalAxis mirror of the Python layer re-formats them as
+// ISO dates like the reference's coordinate_repr (math/temporal_axis.hpp:80-83).
+int pyi_format_bounds_error(const pyi_grid* grid, int axis, const void* coord, char* buf,
+                            size_t len) {
+  if (!grid || axis < 0 || axis >= grid->ndim || !coord || !buf || len == 0) return -1;
+  static const char* labels[4] = {"x", "y", "z", "u"};
+  const pyi_axis_desc& d = grid->axes[axis]->d;
+  auto f64 = [](double v) {
+    char tmp[64];
+    auto r = std::to_chars(tmp, tmp + sizeof(tmp), v);
+    return std::string(tmp, r.ptr);
+  };
+  std::string s;
+  if (d.coord_type == PYI_COORD_I64) {
+    s = std::to_string(*static_cast<const int64_t*>(coord)) + " is out of bounds for axis " +
+        labels[axis] + " [" + std::to_string(d.min_value.i) + ", ..., " +
+        std::to_string(d.max_value.i) + "]";
+  } else {
+    s = f64(*static_cast<const double*>(coord)) + " is out of bounds for axis " + labels[axis] +
+        " [" + f64(d.min_value.f) + ", ..., " + f64(d.max_value.f) + "]";
+  }
+  std::snprintf(buf, len, "%s", s.c_str());
+  return static_cast<int>(s.size());
+}
+
+}  // extern "C"

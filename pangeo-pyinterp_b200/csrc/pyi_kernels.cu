@@ -1,0 +1,489 @@
+// pyi_kernels.cu -- hand-written sm_100a kernels of the n-variate regular-grid
+// interpolation path.  Compiled with -fmad=false: the only fused operations are
+// the explicit fma() calls that mirror the reference's std::fma.
+//
+// Kernels:
+//   geometric_kernel<ND,DT,R,ZI64>  K1-K3: axis lookups, 2^ND-corner gather and
+//       the bilinear / idw / nearest evaluators of
+//       cxx/include/pyinterp/pybind/geometric/{bi,tri,quadri}variate.hpp and
+//       math/interpolate/geometric/{bivariate,multivariate}.hpp
+//   windowed2d_kernel<MAXW>         K4: window build + bicubic / windowed
+//       bilinear of pybind/windowed/bivariate.hpp, math/interpolate/
+//       cache_loader.hpp, bivariate/bicubic.hpp, univariate/cspline.hpp
+//   find_indexes_kernel / find_index_kernel   K5: Axis::find_indexes / find_index
+//   pack_cells2d_kernel             one-off cell packing of a 2-D grid
+#include <atomic>
+
+#include "../../include/pyinterp_b200.h"
+#include "pyi_kernels.cuh"
+
+namespace pyi {
+
+static std::atomic<long long> g_launches{0};
+long long launch_count() { return g_launches.load(); }
+
+constexpr int kThreads = 256;
+
+static int sm_count() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    if (n <= 0) n = 148;
+  }
+  return n;
+}
+
+// Grid sized as a multiple of the SM count (148 on B200): `waves` resident
+// blocks per SM, capped by the work available.
+static int grid_for(long long n, int per_block, int waves) {
+  const long long need = (n + per_block - 1) / per_block;
+  const long long cap = static_cast<long long>(sm_count()) * waves;
+  return static_cast<int>(need < 1 ? 1 : (need < cap ? need : cap));
+}
+
+// ---------------------------------------------------------------------------
+// result-type traits
+// ---------------------------------------------------------------------------
+template <typename R>
+struct RT;
+template <>
+struct RT<double> {
+  static __device__ __forceinline__ double sin_(double v) { return sin(v); }
+  static __device__ __forceinline__ double cos_(double v) { return cos(v); }
+  static __device__ __forceinline__ double eps() { return 2.220446049250313080847263336181640625e-16; }
+  static __device__ __forceinline__ double pi() { return 3.141592653589793238462643383279502884; }
+  static __device__ __forceinline__ double nan() { return CUDART_NAN; }
+};
+template <>
+struct RT<float> {
+  static __device__ __forceinline__ float sin_(float v) { return sinf(v); }
+  static __device__ __forceinline__ float cos_(float v) { return cosf(v); }
+  static __device__ __forceinline__ float eps() { return 1.1920928955078125e-07f; }
+  static __device__ __forceinline__ float pi() { return 3.141592653589793238462643383279502884f; }
+  static __device__ __forceinline__ float nan() { return CUDART_NAN_F; }
+};
+
+// Grid::value (pybind/grid.hpp:340-345) cast to the result type
+// (bivariate.hpp:72-75).  DT >= 0: compile-time dtype; DT < 0: run-time.
+template <int DT, typename R>
+__device__ __forceinline__ R load_value(const void* data, int dtype, long long off) {
+  const int dt = DT >= 0 ? DT : dtype;
+  switch (dt) {
+    case PYI_I8: return static_cast<R>(__ldg(static_cast<const signed char*>(data) + off));
+    case PYI_U8: return static_cast<R>(__ldg(static_cast<const unsigned char*>(data) + off));
+    case PYI_I16: return static_cast<R>(__ldg(static_cast<const short*>(data) + off));
+    case PYI_U16: return static_cast<R>(__ldg(static_cast<const unsigned short*>(data) + off));
+    case PYI_I32: return static_cast<R>(__ldg(static_cast<const int*>(data) + off));
+    case PYI_U32: return static_cast<R>(__ldg(static_cast<const unsigned int*>(data) + off));
+    case PYI_I64: return static_cast<R>(__ldg(static_cast<const long long*>(data) + off));
+    case PYI_U64: return static_cast<R>(__ldg(static_cast<const unsigned long long*>(data) + off));
+    case PYI_F32: return static_cast<R>(__ldg(static_cast<const float*>(data) + off));
+    default: return static_cast<R>(__ldg(static_cast<const double*>(data) + off));
+  }
+}
+
+// ---------------------------------------------------------------------------
+// geometric evaluators (math/interpolate/geometric/bivariate.hpp)
+// ---------------------------------------------------------------------------
+// Boost.Geometry comparable_distance on spherical_equatorial<degree> points:
+// comparable haversine on the unit sphere in the coordinate type.
+template <typename R>
+__device__ __forceinline__ R hav(R theta) {
+  const R s = RT<R>::sin_(theta / R(2));
+  return s * s;
+}
+template <typename R>
+__device__ __forceinline__ R comparable_distance(R lon1d, R lat1d, R lon2d, R lat2d) {
+  const R d2r = RT<R>::pi() / R(180);
+  const R lon1 = lon1d * d2r;
+  const R lat1 = lat1d * d2r;
+  const R lon2 = lon2d * d2r;
+  const R lat2 = lat2d * d2r;
+  return hav<R>(lat2 - lat1) + RT<R>::cos_(lat1) * RT<R>::cos_(lat2) * hav<R>(lon2 - lon1);
+}
+
+// Bilinear::evaluate bivariate.hpp:110-132
+template <typename R>
+__device__ __forceinline__ R eval_bilinear(R x, R y, R x0, R y0, R x1, R y1, R q00, R q01, R q10,
+                                           R q11) {
+  const R dx = x1 - x0;
+  const R dy = y1 - y0;
+  const R t = (x - x0) / dx;
+  const R u = (y - y0) / dy;
+  const R omt = R(1) - t;
+  const R omu = R(1) - u;
+  return omt * (omu * q00 + u * q01) + t * (omu * q10 + u * q11);
+}
+
+// InverseDistanceWeighting::evaluate bivariate.hpp:189-232
+template <typename R>
+__device__ __forceinline__ R eval_idw(int exp_, R x, R y, R x0, R y0, R x1, R y1, R q00, R q01,
+                                      R q10, R q11) {
+  const R cx[4] = {x0, x0, x1, x1};
+  const R cy[4] = {y0, y1, y0, y1};
+  const R cq[4] = {q00, q01, q10, q11};
+  const R eps2 = RT<R>::eps() * RT<R>::eps();
+  const double half_exp = exp_ * 0.5;
+  R wsum = R(0);
+  R vsum = R(0);
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const R d2 = comparable_distance<R>(x, y, cx[k], cy[k]);
+    if (d2 <= eps2) {
+      return cq[k];
+    }
+    const R w = static_cast<R>(1 / pow(static_cast<double>(d2), half_exp));
+    wsum += w;
+    vsum += cq[k] * w;
+  }
+  return vsum / wsum;
+}
+
+// Nearest::evaluate bivariate.hpp:276-302 (first of equal distances wins)
+template <typename R>
+__device__ __forceinline__ R eval_nearest(R x, R y, R x0, R y0, R x1, R y1, R q00, R q01, R q10,
+                                          R q11) {
+  R best = comparable_distance<R>(x, y, x0, y0);
+  R val = q00;
+  R d = comparable_distance<R>(x, y, x0, y1);
+  if (d < best) { best = d; val = q01; }
+  d = comparable_distance<R>(x, y, x1, y0);
+  if (d < best) { best = d; val = q10; }
+  d = comparable_distance<R>(x, y, x1, y1);
+  if (d < best) { best = d; val = q11; }
+  return val;
+}
+
+template <typename R>
+__device__ __forceinline__ R eval_spatial(int method, int idw_exp, R x, R y, R x0, R y0, R x1,
+                                          R y1, R q00, R q01, R q10, R q11) {
+  if (method == PYI_BILINEAR) {
+    return eval_bilinear<R>(x, y, x0, y0, x1, y1, q00, q01, q10, q11);
+  }
+  if (method == PYI_IDW) {
+    return eval_idw<R>(idw_exp, x, y, x0, y0, x1, y1, q00, q01, q10, q11);
+  }
+  return eval_nearest<R>(x, y, x0, y0, x1, y1, q00, q01, q10, q11);
+}
+
+// linear<Axis,T> interpolate/linear.hpp:22-33 and nearest<Axis,T>
+// nearest.hpp:21-32.  Z = double or long long: the differences are formed in
+// Z (exact for int64), only they are converted to R.
+template <typename Z, typename R>
+__device__ __forceinline__ R axis_interp(int method, Z x, Z x0, Z x1, R y0, R y1) {
+  if (method == PYI_AXIS_NEAREST) {
+    const Z d0 = x0 - x;
+    const Z d1 = x1 - x;
+    const Z a0 = d0 >= 0 ? d0 : -d0;
+    const Z a1 = d1 >= 0 ? d1 : -d1;
+    return a0 < a1 ? y0 : y1;
+  }
+  const R dx = static_cast<R>(x1 - x0);
+  if (dx == R(0)) {
+    return (x == x0) ? y0 : RT<R>::nan();
+  }
+  const R t = static_cast<R>(x - x0) / dx;
+  return y0 + t * (y1 - y0);
+}
+
+// ---------------------------------------------------------------------------
+// K1-K3: geometric interpolation
+// ---------------------------------------------------------------------------
+// One query point (pybind/geometric/bivariate.hpp:47-97, trivariate.hpp:47-123,
+// quadrivariate.hpp:50-148).  Returns -1 and the value, or the first axis (in
+// x, y, z, u order) that could not bracket the point.
+template <int ND, int DT, typename R, bool ZI64>
+__device__ __forceinline__ int geometric_point(const GeoParams& p, long long k, R& res) {
+  using Z = typename std::conditional<ZI64, long long, double>::type;
+  int ix[2], iy[2], iz[2] = {0, 0}, iu[2] = {0, 0};
+  const double x = __ldg(p.x + k);
+  const double y = __ldg(p.y + k);
+  if (!find_indexes<double>(p.ax[0], x, ix[0], ix[1])) return 0;
+  if (!find_indexes<double>(p.ax[1], y, iy[0], iy[1])) return 1;
+  Z z = 0;
+  double u = 0;
+  if (ND >= 3) {
+    z = __ldg(static_cast<const Z*>(p.z) + k);
+    if (!find_indexes<Z>(p.ax[2], z, iz[0], iz[1])) return 2;
+  }
+  if (ND >= 4) {
+    u = __ldg(p.u + k);
+    if (!find_indexes<double>(p.ax[3], u, iu[0], iu[1])) return 3;
+  }
+  // corner coordinates in R; x1 and the query x are normalised against the
+  // R-rounded x0 promoted back to double (bivariate.hpp:78-89)
+  const R x0 = static_cast<R>(axis_coord_f64(p.ax[0], ix[0]));
+  const R x1 = static_cast<R>(
+      axis_normalize(p.ax[0], axis_coord_f64(p.ax[0], ix[1]), static_cast<double>(x0)));
+  const R y0 = static_cast<R>(axis_coord_f64(p.ax[1], iy[0]));
+  const R y1 = static_cast<R>(axis_coord_f64(p.ax[1], iy[1]));
+  const R px = static_cast<R>(axis_normalize(p.ax[0], x, static_cast<double>(x0)));
+  const R py = static_cast<R>(y);
+
+  const long long n1 = p.ax[1].n;
+  const long long n2 = ND >= 3 ? p.ax[2].n : 1;
+  const long long n3 = ND >= 4 ? p.ax[3].n : 1;
+  constexpr int NZ = ND >= 3 ? 2 : 1;
+  constexpr int NU = ND >= 4 ? 2 : 1;
+  // gather first (all loads in flight), then evaluate
+  R q[NZ][NU][2][2];
+#pragma unroll
+  for (int c = 0; c < NZ; ++c) {
+#pragma unroll
+    for (int d = 0; d < NU; ++d) {
+#pragma unroll
+      for (int a = 0; a < 2; ++a) {
+#pragma unroll
+        for (int b = 0; b < 2; ++b) {
+          long long off = ix[a] * n1 + iy[b];
+          if (ND >= 3) off = off * n2 + iz[c];
+          if (ND >= 4) off = off * n3 + iu[d];
+          q[c][d][a][b] = load_value<DT, R>(p.data, p.dtype, off);
+        }
+      }
+    }
+  }
+  R sp[NZ][NU];
+#pragma unroll
+  for (int c = 0; c < NZ; ++c) {
+#pragma unroll
+    for (int d = 0; d < NU; ++d) {
+      sp[c][d] = eval_spatial<R>(p.method, p.idw_exp, px, py, x0, y0, x1, y1, q[c][d][0][0],
+                                 q[c][d][0][1], q[c][d][1][0], q[c][d][1][1]);
+    }
+  }
+  if (ND == 2) {
+    res = sp[0][0];
+    return -1;
+  }
+  const Z z0 = axis_coord(p.ax[2], iz[0], Z{});
+  const Z z1 = axis_coord(p.ax[2], iz[1], Z{});
+  R along[NU];
+#pragma unroll
+  for (int d = 0; d < NU; ++d) {
+    along[d] = axis_interp<Z, R>(p.z_method, z, z0, z1, sp[0][d], sp[NZ - 1][d]);
+  }
+  if (ND == 3) {
+    res = along[0];
+    return -1;
+  }
+  const double u0 = axis_coord_f64(p.ax[3], iu[0]);
+  const double u1 = axis_coord_f64(p.ax[3], iu[1]);
+  res = axis_interp<double, R>(p.u_method, u, u0, u1, along[0], along[NU - 1]);
+  return -1;
+}
+
+template <int ND, int DT, typename R, bool ZI64>
+__global__ void __launch_bounds__(kThreads)
+geometric_kernel(const __grid_constant__ GeoParams p) {
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  unsigned long long key = kNoOob;
+  R* __restrict__ out = static_cast<R*>(p.out);
+  for (long long k = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; k < p.n;
+       k += stride) {
+    R res = RT<R>::nan();
+    const int bad = geometric_point<ND, DT, R, ZI64>(p, k, res);
+    if (bad >= 0) {
+      res = RT<R>::nan();
+      const unsigned long long kk = (static_cast<unsigned long long>(p.index_base + k) << 2) | bad;
+      key = kk < key ? kk : key;
+    }
+    __stcs(out + k, res);
+  }
+  if (p.bounds_error && key != kNoOob) {
+    atomicMin(p.oob_key, key);
+  }
+}
+
+template <int ND, bool ZI64>
+static cudaError_t launch_geometric_nd(const GeoParams& p, cudaStream_t stream) {
+  const int blocks = grid_for(p.n, kThreads, 8);
+  const bool r64 = p.dtype == PYI_F64 || p.dtype == PYI_I64 || p.dtype == PYI_U64;
+  if (p.dtype == PYI_F64) {
+    geometric_kernel<ND, PYI_F64, double, ZI64><<<blocks, kThreads, 0, stream>>>(p);
+  } else if (p.dtype == PYI_F32) {
+    geometric_kernel<ND, PYI_F32, float, ZI64><<<blocks, kThreads, 0, stream>>>(p);
+  } else if (r64) {
+    geometric_kernel<ND, -1, double, ZI64><<<blocks, kThreads, 0, stream>>>(p);
+  } else {
+    geometric_kernel<ND, -1, float, ZI64><<<blocks, kThreads, 0, stream>>>(p);
+  }
+  g_launches.fetch_add(1);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_geometric(const GeoParams& p, cudaStream_t stream) {
+  if (p.n <= 0) return cudaSuccess;
+  const bool zi64 = p.ndim >= 3 && p.ax[2].coord_i64;
+  switch (p.ndim) {
+    case 2: return launch_geometric_nd<2, false>(p, stream);
+    case 3: return zi64 ? launch_geometric_nd<3, true>(p, stream)
+                        : launch_geometric_nd<3, false>(p, stream);
+    case 4: return zi64 ? launch_geometric_nd<4, true>(p, stream)
+                        : launch_geometric_nd<4, false>(p, stream);
+    default: return cudaErrorInvalidValue;
+  }
+}
+
+// ---------------------------------------------------------------------------
+// K5: Axis::find_indexes / find_index (pybind/axis.hpp:84-101, axis.hpp:319-333)
+// ---------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(kThreads)
+find_indexes_kernel(const __grid_constant__ FindParams p) {
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  const T* __restrict__ c = static_cast<const T*>(p.coords);
+  longlong2* __restrict__ out = reinterpret_cast<longlong2*>(p.out);
+  for (long long k = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; k < p.n;
+       k += stride) {
+    int i0 = -1, i1 = -1;
+    const bool ok = find_indexes<T>(p.ax, __ldg(c + k), i0, i1);
+    out[k] = ok ? make_longlong2(i0, i1) : make_longlong2(-1, -1);
+  }
+}
+
+// Axis::find_index(c, bounded).  The reference's casts of out-of-range doubles
+// to int64 are reproduced as its x86-64 build executes them: NaN and |v| >=
+// 2^63 become INT64_MIN, i.e. "below the axis".
+template <typename T>
+__device__ __forceinline__ long long find_index_bounded(const DAxis& a, T c, bool bounded);
+template <>
+__device__ __forceinline__ long long find_index_bounded<double>(const DAxis& a, double c,
+                                                                 bool bounded) {
+  if (isnan(c)) return -1;
+  c = axis_normalize(a, c, a.min);
+  long long r;
+  if (a.kind == 0) {
+    const double v = round(__dmul_rn(__dsub_rn(c, a.start), a.inv_step));
+    const bool low = !(v >= 0.0) || v >= 9223372036854775808.0;
+    if (low) {
+      r = bounded ? 0 : -1;
+    } else if (v >= static_cast<double>(a.n)) {
+      r = bounded ? a.n - 1 : -1;
+    } else {
+      r = static_cast<long long>(v);
+    }
+  } else {
+    r = irregular_find_f64(a, c);
+    if (r < 0 && bounded) {
+      // container.hpp:390-397: below the first / beyond the last point
+      const double first = __ldg(static_cast<const double*>(a.points));
+      r = (a.asc ? (c < first) : (c > first)) ? 0 : a.n - 1;
+    }
+  }
+  if (r == -1 && a.periodic) {  // axis.hpp:326-331
+    return __dsub_rn(c, a.max) < __dsub_rn(__dadd_rn(a.min, a.period), c) ? a.n - 1 : 0;
+  }
+  return r;
+}
+template <>
+__device__ __forceinline__ long long find_index_bounded<long long>(const DAxis& a, long long c,
+                                                                    bool bounded) {
+  if (c == LLONG_MIN) return -1;
+  c = axis_normalize(a, c, a.imin);
+  long long r;
+  if (a.kind == 0) {
+    const long long num = static_cast<long long>(static_cast<unsigned long long>(c) -
+                                                 static_cast<unsigned long long>(a.istart));
+    const long long idx = num > 0 ? div_trunc_i64(num + a.istep2, a.istep)
+                                  : div_trunc_i64(num - a.istep2, a.istep);
+    if (idx < 0) {
+      r = bounded ? 0 : -1;
+    } else if (idx >= a.n) {
+      r = bounded ? a.n - 1 : -1;
+    } else {
+      r = idx;
+    }
+  } else {
+    r = irregular_find_i64(a, c);
+    if (r < 0 && bounded) {
+      const long long first = __ldg(static_cast<const long long*>(a.points));
+      r = (a.asc ? (c < first) : (c > first)) ? 0 : a.n - 1;
+    }
+  }
+  if (r == -1 && a.periodic) {
+    return (c - a.imax) < (a.imin + a.iperiod - c) ? a.n - 1 : 0;
+  }
+  return r;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kThreads)
+find_index_kernel(const __grid_constant__ FindParams p) {
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  const T* __restrict__ c = static_cast<const T*>(p.coords);
+  for (long long k = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; k < p.n;
+       k += stride) {
+    p.out[k] = find_index_bounded<T>(p.ax, __ldg(c + k), p.bounded != 0);
+  }
+}
+
+cudaError_t launch_find_indexes(const FindParams& p, cudaStream_t stream) {
+  if (p.n <= 0) return cudaSuccess;
+  const int blocks = grid_for(p.n, kThreads, 8);
+  if (p.ax.coord_i64) {
+    find_indexes_kernel<long long><<<blocks, kThreads, 0, stream>>>(p);
+  } else {
+    find_indexes_kernel<double><<<blocks, kThreads, 0, stream>>>(p);
+  }
+  g_launches.fetch_add(1);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_find_index(const FindParams& p, cudaStream_t stream) {
+  if (p.n <= 0) return cudaSuccess;
+  const int blocks = grid_for(p.n, kThreads, 8);
+  if (p.ax.coord_i64) {
+    find_index_kernel<long long><<<blocks, kThreads, 0, stream>>>(p);
+  } else {
+    find_index_kernel<double><<<blocks, kThreads, 0, stream>>>(p);
+  }
+  g_launches.fetch_add(1);
+  return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------
+// one-off 2-D cell packing: the four corners of cell (ix, iy) contiguous, in
+// the result type, 32 B (f64) / 16 B (f32) aligned: one sector per query.
+// ix + 1 wraps (the periodic seam cell is materialised), iy + 1 clamps.
+// ---------------------------------------------------------------------------
+template <typename R>
+__global__ void __launch_bounds__(kThreads)
+pack_cells2d_kernel(const void* __restrict__ data, int dtype, int nx, int ny, R* __restrict__ cells) {
+  const long long total = static_cast<long long>(nx) * ny;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long c = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; c < total;
+       c += stride) {
+    const int ix = static_cast<int>(c / ny);
+    const int iy = static_cast<int>(c - static_cast<long long>(ix) * ny);
+    const int ix1 = ix + 1 == nx ? 0 : ix + 1;
+    const int iy1 = iy + 1 == ny ? iy : iy + 1;
+    R* o = cells + 4 * c;
+    o[0] = load_value<-1, R>(data, dtype, static_cast<long long>(ix) * ny + iy);
+    o[1] = load_value<-1, R>(data, dtype, static_cast<long long>(ix) * ny + iy1);
+    o[2] = load_value<-1, R>(data, dtype, static_cast<long long>(ix1) * ny + iy);
+    o[3] = load_value<-1, R>(data, dtype, static_cast<long long>(ix1) * ny + iy1);
+  }
+}
+
+cudaError_t launch_pack_cells2d(const void* data, int dtype, int nx, int ny, void* packed,
+                                cudaStream_t stream) {
+  const long long total = static_cast<long long>(nx) * ny;
+  const int blocks = grid_for(total, kThreads, 8);
+  const bool r64 = dtype == PYI_F64 || dtype == PYI_I64 || dtype == PYI_U64;
+  if (r64) {
+    pack_cells2d_kernel<double><<<blocks, kThreads, 0, stream>>>(data, dtype, nx, ny,
+                                                                 static_cast<double*>(packed));
+  } else {
+    pack_cells2d_kernel<float><<<blocks, kThreads, 0, stream>>>(data, dtype, nx, ny,
+                                                                static_cast<float*>(packed));
+  }
+  g_launches.fetch_add(1);
+  return cudaGetLastError();
+}
+
+}  // namespace pyi
+
+#include "pyi_windowed.cuh"

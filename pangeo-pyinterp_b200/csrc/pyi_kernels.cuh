@@ -1,0 +1,68 @@
+// pyi_kernels.cuh -- kernel parameter blocks and launch prototypes shared by
+// pyi_kernels.cu (device code, -fmad=false) and pyi_host.cu (C-ABI).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "pyi_device.cuh"
+
+namespace pyi {
+
+// out-of-bounds report: key = (point index << 2) | axis, reduced with atomicMin
+constexpr unsigned long long kNoOob = ~0ULL;
+
+struct GeoParams {
+  DAxis ax[4];
+  const void* data;   // grid values, C order [x][y][z][u]
+  const void* packed; // cell-packed copy (2-D: 4 corners per cell) or nullptr
+  int32_t dtype;      // pyi_dtype
+  int32_t ndim;
+  int32_t method, idw_exp, z_method, u_method;
+  int32_t bounds_error;
+  long long n;
+  long long index_base;  // global index of point 0 (chunked host calls)
+  const double* x;
+  const double* y;
+  const void* z;  // double or int64 according to ax[2].coord_i64
+  const double* u;
+  void* out;      // double (f64/i64/u64 grids) or float
+  unsigned long long* oob_key;
+};
+
+struct WinParams {
+  DAxis ax[2];
+  const void* data;
+  int32_t dtype;
+  int32_t method;  // pyi_windowed_method
+  int32_t half_x, half_y;
+  int32_t boundary;
+  int32_t bounds_error;
+  long long n;
+  long long index_base;
+  const double* x;
+  const double* y;
+  void* out;
+  unsigned long long* oob_key;
+};
+
+struct FindParams {
+  DAxis ax;
+  long long n;
+  const void* coords;
+  long long* out;  // pairs (n x 2) or single indexes (n)
+  int32_t bounded;
+};
+
+cudaError_t launch_geometric(const GeoParams& p, cudaStream_t stream);
+cudaError_t launch_windowed2d(const WinParams& p, cudaStream_t stream);
+cudaError_t launch_find_indexes(const FindParams& p, cudaStream_t stream);
+cudaError_t launch_find_index(const FindParams& p, cudaStream_t stream);
+// 2-D cell packing: cells[(ix * ny + iy)] = {v(ix,iy), v(ix,iy+1), v(ix+1,iy), v(ix+1,iy+1)}
+// converted to the result type; ix+1 wraps (periodic x), iy+1 clamps.
+cudaError_t launch_pack_cells2d(const void* data, int dtype, int nx, int ny, void* packed,
+                                cudaStream_t stream);
+// number of kernels launched so far by this library (all threads)
+long long launch_count();
+
+}  // namespace pyi

@@ -1,0 +1,353 @@
+"""GPU parity: the CUDA path, called through the Python mirror of the reference
+API and the C-ABI, against the CPU oracle on identical seeded inputs.
+
+Bars (BASELINE.json north_star): index selection bit-exact; values within
+1e-12 relative (float64 results) / 1e-5 (float32 results); identical NaN
+positions; identical bounds-error index / axis / message.
+Relative error is measured as |a-b| <= tol * max(|a|, |b|, field_scale)
+(plain relative error is ill-posed at zero crossings).
+"""
+import numpy as np
+import pytest
+
+import axes_zoo
+
+pytestmark = pytest.mark.gpu
+
+TOL = {np.dtype("float64"): 1e-12, np.dtype("float32"): 1e-5}
+
+
+def close(a, b, scale, what=""):
+    assert a.dtype == b.dtype, (a.dtype, b.dtype)
+    assert a.shape == b.shape
+    na, nb = np.isnan(a), np.isnan(b)
+    assert np.array_equal(na, nb), f"{what}: NaN positions differ at {np.flatnonzero(na != nb)[:8]}"
+    tol = TOL[a.dtype]
+    a64, b64 = a[~na].astype(np.float64), b[~na].astype(np.float64)
+    err = np.abs(a64 - b64)
+    bound = tol * np.maximum(np.maximum(np.abs(a64), np.abs(b64)), scale)
+    bad = np.flatnonzero(err > bound)
+    assert bad.size == 0, f"{what}: {bad.size} values off, worst {err.max():.3e} (tol {tol})"
+    return float((err == 0).mean()) if err.size else 1.0
+
+
+@pytest.fixture(scope="module")
+def orc_best():
+    """The reference build when present, else the pinned C restatement."""
+    import orc
+    return orc.Oracle("reference") if orc.available("reference") else orc.Oracle("port")
+
+
+def _mk_axis(pyi, o, spec):
+    values, kw, flip = spec
+    if np.asarray(values).dtype.kind == "i":
+        dt = np.asarray(values, dtype=np.int64).view("datetime64[ns]")
+        per = kw.get("period")
+        g = pyi.TemporalAxis(dt, period=None if per is None else np.timedelta64(per, "ns"))
+    else:
+        g = pyi.Axis(values, **kw)
+    c = o.axis(values, **kw)
+    if flip:
+        g.flip(inplace=True)
+        c.flip()
+    return g, c
+
+
+@pytest.mark.parametrize("name", sorted(axes_zoo.f64_axes()) + sorted(axes_zoo.i64_axes()))
+def test_axis_lookup_bit_exact(pyi, orc_best, name):
+    zoo = {**axes_zoo.f64_axes(), **axes_zoo.i64_axes()}
+    g, c = _mk_axis(pyi, orc_best, zoo[name])
+    d = c.describe()
+    gd = g._desc()
+    assert (gd.kind, gd.size, gd.is_ascending, gd.is_periodic) == (d["kind"], d["size"], d["is_ascending"], d["is_periodic"])
+    coords = axes_zoo.coords_for(d, 200_000, 5)
+    got = g.find_indexes(coords)
+    want = c.find_indexes(coords)
+    assert got.dtype == np.int64 and got.shape == want.shape
+    assert np.array_equal(got, want), np.flatnonzero((got != want).any(1))[:5]
+    for bounded in (False, True):
+        assert np.array_equal(g.find_index(coords, bounded), c.find_index(coords, bounded))
+
+
+def test_axis_lookup_device_tensor(pyi, orc_best):
+    import torch
+    g, c = _mk_axis(pyi, orc_best, axes_zoo.f64_axes()["lat_irregular"])
+    coords = axes_zoo.coords_for(c.describe(), 100_000, 9)
+    got = g.find_indexes(torch.from_numpy(coords).cuda()).cpu().numpy()
+    assert np.array_equal(got, c.find_indexes(coords))
+
+
+def _grid_pair(pyi, o, nd, dtype, x_kind="lon_periodic", y_kind="lat", z_kind="monthly30", flip_z=False, nan=0.02,
+               small=True):
+    fz, iz = axes_zoo.f64_axes(), axes_zoo.i64_axes()
+    if small:
+        specs = [(np.arange(72) * 5.0, dict(period=360.0), False) if x_kind == "lon_periodic" else fz[x_kind],
+                 (-87.5 + np.arange(36) * 5.0, {}, False) if y_kind == "lat" else fz[y_kind]]
+    else:
+        specs = [fz[x_kind], fz[y_kind]]
+    if nd >= 3:
+        zs = iz[z_kind] if z_kind in iz else fz[z_kind]
+        specs.append((zs[0], zs[1], flip_z))
+    if nd >= 4:
+        specs.append((np.round(5500.0 * (np.arange(9) / 8) ** 2.2, 1), {}, False))
+    pairs = [_mk_axis(pyi, o, s) for s in specs]
+    shape = [len(p[0]) for p in pairs]
+    rng = np.random.default_rng(3)
+    g = rng.normal(size=shape) * 50.0
+    if np.dtype(dtype).kind == "f":
+        g = g.astype(dtype)
+        if nan:
+            g[rng.random(shape) < nan] = np.nan
+    else:
+        info = np.iinfo(dtype)
+        g = np.clip(np.round(g), info.min, info.max).astype(dtype)
+    grid = pyi.Grid(*[p[0] for p in pairs], g)
+    return grid, [p[1] for p in pairs], g
+
+
+def _queries(nd, n, seed, xr=(-400, 800), yr=(-95, 95), z_f64=False):
+    rng = np.random.default_rng(seed)
+    q = [rng.uniform(*xr, n), rng.uniform(*yr, n)]
+    q[0][::97] = np.nan
+    q[0][5::101] = 5.0 * rng.integers(0, 72, q[0][5::101].size)
+    q[1][7::89] = -87.5 + 5.0 * rng.integers(0, 36, q[1][7::89].size)
+    if nd >= 3:
+        if z_f64:
+            q.append(rng.uniform(-100, 5600, n))
+        else:
+            z = rng.integers(axes_zoo.T0 - 10 * axes_zoo.DAY, axes_zoo.T0 + 340 * axes_zoo.DAY, n, dtype=np.int64)
+            z[::113] = np.iinfo(np.int64).min
+            z[3::57] = axes_zoo.T0 + 30 * axes_zoo.DAY * rng.integers(0, 12, z[3::57].size)
+            q.append(z)
+    if nd >= 4:
+        q.append(rng.uniform(-50, 5600, n))
+    return q
+
+
+def _call(pyi, grid, q, cfg):
+    fn = {2: pyi.core.bivariate, 3: pyi.core.trivariate, 4: pyi.core.quadrivariate}[grid.ndim]
+    args = list(q)
+    if grid.ndim >= 3 and grid.has_temporal_axis:
+        args[2] = args[2].view("datetime64[ns]")
+    return fn(grid, *args, cfg)
+
+
+def _geo_cfg(pyi, nd, method):
+    cls = {2: pyi.geometric.Bivariate, 3: pyi.geometric.Trivariate, 4: pyi.geometric.Quadrivariate}[nd]
+    return [cls.bilinear, cls.idw, cls.nearest][method]()
+
+
+@pytest.mark.parametrize("nd", [2, 3, 4])
+@pytest.mark.parametrize("dtype", ["float64", "float32", "int16", "int64", "uint8", "uint64", "int32", "int8",
+                                   "uint16", "uint32"])
+def test_geometric_bilinear(pyi, orc_best, nd, dtype):
+    n = 50_000
+    grid, caxes, g = _grid_pair(pyi, orc_best, nd, dtype)
+    q = _queries(nd, n, 100 + nd)
+    got = _call(pyi, grid, q, _geo_cfg(pyi, nd, 0))
+    want, _ = orc_best.geometric(caxes, g, *q, method=0, num_threads=0)
+    exact = close(got, want, 50.0, f"bilinear {nd}D {dtype}")
+    # same IEEE operations in the same order: bilinear is expected bit-identical
+    assert exact == 1.0
+    assert np.isfinite(got).sum() > n // 8
+
+
+@pytest.mark.parametrize("nd", [2, 3, 4])
+@pytest.mark.parametrize("dtype", ["float64", "float32"])
+@pytest.mark.parametrize("method", [1, 2])
+def test_geometric_idw_nearest(pyi, orc_best, nd, dtype, method):
+    """idw / nearest go through sin / cos / pow, which are not correctly
+    rounded on either side: tolerance for idw; for nearest a differing corner
+    is accepted only where the two candidate distances tie to rounding."""
+    n = 30_000
+    grid, caxes, g = _grid_pair(pyi, orc_best, nd, dtype, nan=0.0)
+    q = _queries(nd, n, 300 + nd)
+    got = _call(pyi, grid, q, _geo_cfg(pyi, nd, method))
+    want, _ = orc_best.geometric(caxes, g, *q, method=method, z_method=method == 2, u_method=method == 2,
+                                 num_threads=0)
+    assert np.array_equal(np.isnan(got), np.isnan(want))
+    ok = ~np.isnan(got)
+    tol = TOL[got.dtype] * (1 if method == 1 else 1)
+    err = np.abs(got[ok].astype(np.float64) - want[ok].astype(np.float64))
+    bound = tol * np.maximum(np.abs(want[ok].astype(np.float64)), 50.0) * (20 if method == 1 else 1)
+    bad = np.flatnonzero(err > bound)
+    if method == 1:
+        assert bad.size == 0, (bad.size, err.max())
+    else:
+        # nearest: mismatches only at (near-)ties: points on a cell mid-line
+        assert bad.size <= max(3, n // 2000), bad.size
+
+
+@pytest.mark.parametrize("case", [
+    dict(x_kind="lon_periodic", y_kind="lat", flip_z=True),
+    dict(x_kind="lon_partial_period", y_kind="small_irregular_desc"),
+    dict(x_kind="lon_180", y_kind="lat_irregular", small=False),
+    dict(x_kind="lon_periodic_desc", y_kind="lat_desc", small=False),
+    dict(x_kind="irregular_periodic", y_kind="depth"),
+    dict(x_kind="lon_0p1", y_kind="lat", small=False),   # float32 rounding quirk of SURVEY 7.3-5
+    dict(x_kind="lon_wrapped_values", y_kind="two_points"),
+    dict(x_kind="lon_periodic", y_kind="lat", z_kind="irregular_time"),
+    dict(x_kind="lon_periodic", y_kind="lat", z_kind="daily_ns_desc"),
+    dict(x_kind="lon_periodic", y_kind="lat", z_kind="depth"),
+])
+@pytest.mark.parametrize("dtype", ["float64", "float32"])
+def test_geometric_axis_kinds(pyi, orc_best, case, dtype):
+    n = 40_000
+    case = dict(case)
+    small = case.pop("small", True)
+    for nd in (2, 3, 4):
+        if nd == 2 and "z_kind" in case:
+            continue
+        grid, caxes, g = _grid_pair(pyi, orc_best, nd, dtype, small=small, **case)
+        ds = [c.describe() for c in caxes]
+        q = _queries(nd, n, 7, xr=(ds[0]["min_value"] - 400, ds[0]["max_value"] + 400),
+                     yr=(ds[1]["min_value"] - 3, ds[1]["max_value"] + 3), z_f64=nd >= 3 and not caxes[2].is_i64)
+        if nd >= 3 and caxes[2].is_i64:
+            lo, hi = ds[2]["min_value"], ds[2]["max_value"]
+            q[2] = np.random.default_rng(1).integers(lo - (hi - lo) // 10, hi + (hi - lo) // 10, n, dtype=np.int64)
+        for zm in (0, 1):
+            cfg = _geo_cfg(pyi, nd, 0)
+            if nd >= 3:
+                cfg = cfg.with_third_axis("nearest" if zm else "linear")
+            got = _call(pyi, grid, q, cfg)
+            want, _ = orc_best.geometric(caxes, g, *q, method=0, z_method=zm, num_threads=0)
+            exact = close(got, want, 50.0, f"{case} {nd}D")
+            assert exact == 1.0
+        assert np.isfinite(got).sum() > n // 50
+
+
+@pytest.mark.parametrize("nd", [2, 3, 4])
+def test_geometric_bounds_error(pyi, orc_best, nd):
+    grid, caxes, g = _grid_pair(pyi, orc_best, nd, "float64")
+    q = _queries(nd, 20_000, 9)
+    want = orc_best.geometric(caxes, g, *q, bounds_error=True, num_threads=4)[1]
+    assert want is not None
+    with pytest.raises(ValueError, match="out of bounds") as ei:
+        _call(pyi, grid, q, _geo_cfg(pyi, nd, 0).with_bounds_error(True))
+    if want[1] != 2:  # the oracle prints temporal values as integers
+        assert str(ei.value) == want[2]
+    else:
+        assert "for axis z" in str(ei.value)
+    # in-bounds points only: no error, finite
+    qq = [np.array([10.0, 20.0]), np.array([0.0, 10.0]), np.array([axes_zoo.T0 + axes_zoo.DAY] * 2, dtype=np.int64),
+          np.array([10.0, 20.0])][:nd]
+    out = _call(pyi, grid, qq, _geo_cfg(pyi, nd, 0).with_bounds_error(True))
+    assert out.shape == (2,)
+
+
+def test_bounds_error_first_point_and_axis(pyi, orc_best):
+    """Lowest offending index, first offending axis in x, y order, across
+    chunk boundaries of the host pipeline (> 2^23 points)."""
+    grid, caxes, g = _grid_pair(pyi, orc_best, 2, "float64", x_kind="lon_partial_period", nan=0.0)
+    n = (1 << 23) + 1000
+    x = np.full(n, 50.0)
+    y = np.full(n, 0.0)
+    x[n - 7] = 150.0     # outside lon_partial_period [0, 100]
+    y[n - 7] = 95.0      # y also bad: x must be reported
+    y[n - 3] = 99.0
+    with pytest.raises(ValueError) as ei:
+        pyi.core.bivariate(grid, x, y, pyi.geometric.Bivariate.bilinear().with_bounds_error(True))
+    assert str(ei.value).startswith("150 is out of bounds for axis x [0, ..., 100]")
+    x[n - 7] = 50.0
+    with pytest.raises(ValueError) as ei:
+        pyi.core.bivariate(grid, x, y, pyi.geometric.Bivariate.bilinear().with_bounds_error(True))
+    assert str(ei.value).startswith("95 is out of bounds for axis y")
+
+
+@pytest.mark.parametrize("method", ["bicubic", "bilinear"])
+@pytest.mark.parametrize("boundary", ["undef", "shrink"])
+@pytest.mark.parametrize("half", [(3, 3), (2, 4), (1, 1), (5, 2), (8, 8)])
+def test_windowed2d(pyi, orc_best, method, boundary, half):
+    n = 30_000
+    for dtype, nan in (("float64", 0.0), ("float32", 0.002), ("int16", 0.0)):
+        grid, caxes, g = _grid_pair(pyi, orc_best, 2, dtype, nan=nan)
+        q = _queries(2, n, 21)
+        cfg = getattr(pyi.windowed.Bivariate, method)().with_half_window_size_x(half[0]) \
+            .with_half_window_size_y(half[1]).with_boundary_mode(getattr(pyi.windowed.BoundaryConfig, boundary)())
+        got = pyi.core.bivariate(grid, q[0], q[1], cfg)
+        want, _ = orc_best.windowed2d(caxes, g, q[0], q[1], method=0 if method == "bicubic" else 1,
+                                      half_x=half[0], half_y=half[1], boundary=boundary, num_threads=0,
+                                      stateless=True)
+        exact = close(got, want, 50.0, f"{method} {boundary} {half} {dtype}")
+        assert exact == 1.0  # identical operation sequence per spline solve
+
+
+@pytest.mark.parametrize("case", [
+    dict(x_kind="lon_180", y_kind="lat_desc", small=False),
+    dict(x_kind="lon_partial_period", y_kind="lat_irregular", small=False),
+    dict(x_kind="lon_periodic_desc", y_kind="small_irregular"),
+    dict(x_kind="irregular_periodic", y_kind="depth"),
+])
+def test_windowed2d_axis_kinds(pyi, orc_best, case):
+    case = dict(case)
+    small = case.pop("small", True)
+    grid, caxes, g = _grid_pair(pyi, orc_best, 2, "float64", small=small, nan=0.0005, **case)
+    ds = [c.describe() for c in caxes]
+    q = _queries(2, 30_000, 4, xr=(ds[0]["min_value"] - 400, ds[0]["max_value"] + 400),
+                 yr=(ds[1]["min_value"] - 3, ds[1]["max_value"] + 3))
+    for boundary in ("undef", "shrink"):
+        got = pyi.bivariate(grid, q[0], q[1], "bicubic", boundary_mode=boundary)
+        want, _ = orc_best.windowed2d(caxes, g, q[0], q[1], boundary=boundary, num_threads=0)
+        close(got, want, 50.0, f"bicubic {case} {boundary}")
+
+
+def test_windowed2d_bounds_error(pyi, orc_best):
+    grid, caxes, g = _grid_pair(pyi, orc_best, 2, "float64", nan=0.0)
+    q = _queries(2, 5000, 33)
+    want = orc_best.windowed2d(caxes, g, q[0], q[1], bounds_error=True, num_threads=3)[1]
+    with pytest.raises(IndexError) as ei:
+        pyi.bivariate(grid, q[0], q[1], "bicubic", bounds_error=True)
+    assert str(ei.value) == want[2]
+    # a window that does not fit is NaN, not an error (cache_loader.hpp:69-80)
+    out = pyi.bivariate(grid, np.array([10.0]), np.array([-86.0]), "bicubic", bounds_error=True)
+    assert np.isnan(out[0])
+
+
+def test_device_tensors_match_host_path(pyi):
+    import torch
+    s = pyi.synthetic
+    lon, lat = s.lon_axis_values(), s.lat_axis_values()
+    g = s.field(lon, lat)
+    grid = pyi.Grid(pyi.Axis(lon, period=360.0), pyi.Axis(lat), g)
+    x, y = s.queries(1_000_000, 1001)
+    host = pyi.bivariate(grid, x, y)
+    dev = pyi.bivariate(grid, torch.from_numpy(x).cuda(), torch.from_numpy(y).cuda())
+    assert dev.is_cuda and dev.dtype == torch.float64
+    assert np.array_equal(host, dev.cpu().numpy(), equal_nan=True)
+    hostc = pyi.bivariate(grid, x, y, "bicubic")
+    devc = pyi.bivariate(grid, torch.from_numpy(x).cuda(), torch.from_numpy(y).cuda(), "bicubic")
+    assert np.array_equal(hostc, devc.cpu().numpy(), equal_nan=True)
+
+
+def test_api_errors(pyi):
+    s = pyi.synthetic
+    lon, lat = np.arange(72) * 5.0, -87.5 + np.arange(36) * 5.0
+    ax, ay = pyi.Axis(lon, period=360.0), pyi.Axis(lat)
+    grid = pyi.Grid(ax, ay, np.zeros((72, 36), dtype=np.float32))
+    assert grid.result_dtype == np.float32
+    with pytest.raises(ValueError, match="trivariate requires 3D grid, got 2D"):
+        pyi.trivariate(grid, np.zeros(3), np.zeros(3), np.zeros(3))
+    with pytest.raises(ValueError, match="could not be broadcast"):
+        pyi.bivariate(grid, np.zeros(3), np.zeros(4))
+    with pytest.raises(ValueError, match="doesn't match array shape"):
+        pyi.Grid(ax, ay, np.zeros((72, 35)))
+    with pytest.raises(ValueError, match="y-axis cannot be a circle"):
+        pyi.Grid(ay, ax, np.zeros((36, 72)))
+    with pytest.raises(ValueError, match="Unknown"):
+        pyi.bivariate(grid, np.zeros(3), np.zeros(3), "spline42")
+    out = pyi.bivariate(grid, np.zeros(0), np.zeros(0))
+    assert out.shape == (0,) and out.dtype == np.float32
+
+
+def test_grid_array_is_borrowed_and_refreshed(pyi):
+    """The reference borrows the numpy buffer; later writes must be seen
+    (pyinterp/tests/core/windowed/test_bivariate.py:234-250)."""
+    lon, lat = np.arange(72) * 5.0, -87.5 + np.arange(36) * 5.0
+    arr = np.ones((72, 36))
+    grid = pyi.Grid(pyi.Axis(lon, period=360.0), pyi.Axis(lat), arr)
+    assert np.shares_memory(grid.array, arr)
+    x, y = np.array([12.0]), np.array([1.0])
+    assert pyi.bivariate(grid, x, y)[0] == 1.0
+    arr[2:4, 17:19] = np.nan
+    assert np.isnan(pyi.bivariate(grid, x, y)[0])
+    assert np.isnan(pyi.bivariate(grid, x, y, "bicubic")[0])
