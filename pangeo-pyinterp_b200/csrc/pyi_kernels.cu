@@ -314,8 +314,13 @@ static cudaError_t launch_geometric_nd(const GeoParams& p, cudaStream_t stream) 
   return cudaGetLastError();
 }
 
+// K1 fast path (pyi_fast2d.cuh)
+static bool fast2d_eligible(const GeoParams& p);
+static cudaError_t launch_fast2d(const GeoParams& p, cudaStream_t stream);
+
 cudaError_t launch_geometric(const GeoParams& p, cudaStream_t stream) {
   if (p.n <= 0) return cudaSuccess;
+  if (fast2d_eligible(p)) return launch_fast2d(p, stream);
   const bool zi64 = p.ndim >= 3 && p.ax[2].coord_i64;
   switch (p.ndim) {
     case 2: return launch_geometric_nd<2, false>(p, stream);
@@ -486,4 +491,5 @@ cudaError_t launch_pack_cells2d(const void* data, int dtype, int nx, int ny, voi
 
 }  // namespace pyi
 
+#include "pyi_fast2d.cuh"
 #include "pyi_windowed.cuh"

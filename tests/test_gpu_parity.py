@@ -213,7 +213,69 @@ def test_geometric_axis_kinds(pyi, orc_best, case, dtype):
             want, _ = orc_best.geometric(caxes, g, *q, method=0, z_method=zm, num_threads=0)
             exact = close(got, want, 50.0, f"{case} {nd}D")
             assert exact == 1.0
-        assert np.isfinite(got).sum() > n // 50
+        assert np.isfinite(got).sum() > n // 100
+
+
+@pytest.mark.parametrize("lat_kind", ["regular", "irregular"])
+@pytest.mark.parametrize("dtype", ["float64", "float32", "int16"])
+def test_bilinear2d_fast_path_full_grid(pyi, orc_best, lat_kind, dtype):
+    """BASELINE configs 1 / 5: the 0.25 degree global grid (regular or
+    irregular latitude) through the cell-packed fast kernel, host and device
+    entry, with adversarial coordinates: exact nodes, the seam cell, the last
+    node, far-away longitudes, +-inf, NaN, odd sizes and unaligned device
+    pointers (which take the generic kernel) -- all bit-identical."""
+    import torch
+    s = pyi.synthetic
+    lon = s.lon_axis_values()
+    lat = s.lat_axis_values() if lat_kind == "regular" else s.irregular_lat_values()
+    g = s.field(lon, lat)
+    if dtype == "int16":
+        g = np.round(g * 1000).astype(np.int16)
+    else:
+        g = g.astype(dtype)
+        g[::37, ::11] = np.nan
+    grid = pyi.Grid(pyi.Axis(lon, period=360.0), pyi.Axis(lat), g)
+    cax = [orc_best.axis(lon, period=360.0), orc_best.axis(lat)]
+    assert cax[1].describe()["kind"] == (0 if lat_kind == "regular" else 1)
+    n = 400_001
+    rng = np.random.default_rng(11)
+    x = rng.uniform(-720.0, 1080.0, n)
+    y = rng.uniform(lat[0] - 0.5, lat[-1] + 0.5, n)
+    x[0::53] = lon[rng.integers(0, lon.size, x[0::53].size)]              # exact nodes
+    x[1::53] = lon[rng.integers(0, lon.size, x[1::53].size)] - 360.0
+    x[2::53] = rng.uniform(359.75, 360.0, x[2::53].size)                  # seam cell
+    x[3::53] = np.nextafter(lon[rng.integers(0, lon.size, x[3::53].size)], 1e9)
+    x[4::53] = np.nextafter(lon[rng.integers(0, lon.size, x[4::53].size)], -1e9)
+    x[5::5003] = np.inf
+    x[6::5003] = -np.inf
+    x[7::5003] = np.nan
+    x[8::5003] = rng.uniform(-1e18, 1e18, x[8::5003].size)
+    x[9::5003] = 1e300
+    y[10::47] = lat[rng.integers(0, lat.size, y[10::47].size)]
+    y[11::47] = np.nextafter(lat[rng.integers(0, lat.size, y[11::47].size)], 1e9)
+    y[12::47] = np.nextafter(lat[rng.integers(0, lat.size, y[12::47].size)], -1e9)
+    y[13::4999] = np.nan
+    y[14::4999] = np.inf
+    y[15::4999] = lat[-1]
+    y[16::4999] = lat[0]
+    want, _ = orc_best.geometric(cax, g, x, y, method=0, num_threads=0)
+    got = pyi.bivariate(grid, x, y)
+    assert close(got, want, 1.0, "host") == 1.0
+    xd, yd = torch.from_numpy(x).cuda(), torch.from_numpy(y).cuda()
+    assert close(pyi.bivariate(grid, xd, yd).cpu().numpy(), want, 1.0, "device") == 1.0
+    # unaligned views (8-byte offset): the vectorised kernel is not eligible
+    got_u = pyi.bivariate(grid, xd[1:], yd[1:]).cpu().numpy()
+    assert close(got_u, want[1:], 1.0, "device unaligned") == 1.0
+    assert np.isfinite(got).sum() > n // 2
+    # bounds_error: lowest offending point, first offending axis
+    cfg = pyi.geometric.Bivariate.bilinear().with_bounds_error(True)
+    werr = orc_best.geometric(cax, g, x, y, method=0, bounds_error=True, num_threads=4)[1]
+    with pytest.raises(ValueError) as ei:
+        pyi.core.bivariate(grid, x, y, cfg)
+    assert str(ei.value) == werr[2]
+    with pytest.raises(ValueError) as ei:
+        pyi.core.bivariate(grid, xd, yd, cfg)
+    assert str(ei.value) == werr[2]
 
 
 @pytest.mark.parametrize("nd", [2, 3, 4])
