@@ -33,6 +33,12 @@ struct DAxis {
   const void* points;     // irregular: n values
   const int32_t* lut;     // irregular f64: lut_bins + 1 lower-bound indexes
   double lut_min, lut_inv; // bin(c) = (c - lut_min) * lut_inv
+  // fast-path constants (pyi_fast2d.cuh), computed on the host with the
+  // reference's expressions
+  double hi;            // fl(min + period)
+  double seam_c1;       // periodic: normalize(node(0), min = node(n-1)), math/axis.hpp:294-301
+  double seam_c1_f32;   // same against the float-rounded node(n-1) (float results)
+  int32_t fast_ok;      // ascending f64 axis with moderate magnitudes and spacings
 };
 
 // ---------------------------------------------------------------------------

@@ -70,6 +70,43 @@ bool result_is_f64(int dtype) {  // pybind/grid_dispatch.hpp:25-30
   return dtype == PYI_F64 || dtype == PYI_I64 || dtype == PYI_U64;
 }
 
+// normalize_period(x, min, period) exactly as math.hpp:104-123 (this file is
+// compiled with -ffp-contract=off: no fused operations on the host).
+double host_normalize(double x, double min, double period) {
+  if (period != 0.0 && (x >= min + period || x < min)) {
+    double r = std::remainder(x - min, period);
+    if (r != 0.0 && (std::signbit(r) != std::signbit(period))) r += period;
+    return r + min;
+  }
+  return x;
+}
+
+// Per-axis constants of the bilinear fast path (pyi_fast2d.cuh).
+void fast_constants(const pyi_axis* a, pyi::DAxis& out) {
+  const pyi_axis_desc& d = a->d;
+  out.hi = out.seam_c1 = out.seam_c1_f32 = 0.0;
+  out.fast_ok = 0;
+  if (d.coord_type != PYI_COORD_F64 || !d.is_ascending || d.size < 2) return;
+  const double lim = 1099511627776.0;  // 2^40, the kernel's sane() bound
+  auto moderate = [&](double v) { return std::fabs(v) < lim; };
+  auto spacing_ok = [](double h) { return h > 1e-30 && h < 1e30; };
+  bool ok = moderate(d.min_value.f) && moderate(d.max_value.f) && moderate(d.period.f);
+  if (d.kind == PYI_AXIS_REGULAR) {
+    ok = ok && spacing_ok(d.step.f);
+    const volatile double last = d.start.f + static_cast<double>(d.size - 1) * d.step.f;
+    if (d.is_periodic && d.period.f > 0.0) {
+      out.seam_c1 = host_normalize(d.start.f, last, d.period.f);
+      const double last32 = static_cast<double>(static_cast<float>(last));
+      out.seam_c1_f32 = host_normalize(d.start.f, last32, d.period.f);
+      ok = ok && out.seam_c1 > last && out.seam_c1_f32 > last32;
+    }
+  } else {
+    for (size_t k = 0; ok && k + 1 < a->pf.size(); ++k) ok = spacing_ok(a->pf[k + 1] - a->pf[k]);
+  }
+  out.hi = d.min_value.f + d.period.f;
+  out.fast_ok = ok ? 1 : 0;
+}
+
 // Device mirror of an axis on the current device (uploaded once per device).
 int device_axis(pyi_axis* a, pyi::DAxis& out) {
   const pyi_axis_desc& d = a->d;
@@ -98,6 +135,7 @@ int device_axis(pyi_axis* a, pyi::DAxis& out) {
     out.imin = d.min_value.i;
     out.imax = d.max_value.i;
   }
+  fast_constants(a, out);
   if (d.kind == PYI_AXIS_IRREGULAR) {
     int dev = 0;
     PYI_CUDA(cudaGetDevice(&dev));

@@ -195,21 +195,17 @@ __device__ __forceinline__ R axis_interp(int method, Z x, Z x0, Z x1, R y0, R y1
 // quadrivariate.hpp:50-148).  Returns -1 and the value, or the first axis (in
 // x, y, z, u order) that could not bracket the point.
 template <int ND, int DT, typename R, bool ZI64>
-__device__ __forceinline__ int geometric_point(const GeoParams& p, long long k, R& res) {
+__device__ __forceinline__ int geometric_eval(
+    const GeoParams& p, double x, double y,
+    typename std::conditional<ZI64, long long, double>::type z, double u, R& res) {
   using Z = typename std::conditional<ZI64, long long, double>::type;
   int ix[2], iy[2], iz[2] = {0, 0}, iu[2] = {0, 0};
-  const double x = __ldg(p.x + k);
-  const double y = __ldg(p.y + k);
   if (!find_indexes<double>(p.ax[0], x, ix[0], ix[1])) return 0;
   if (!find_indexes<double>(p.ax[1], y, iy[0], iy[1])) return 1;
-  Z z = 0;
-  double u = 0;
   if (ND >= 3) {
-    z = __ldg(static_cast<const Z*>(p.z) + k);
     if (!find_indexes<Z>(p.ax[2], z, iz[0], iz[1])) return 2;
   }
   if (ND >= 4) {
-    u = __ldg(p.u + k);
     if (!find_indexes<double>(p.ax[3], u, iu[0], iu[1])) return 3;
   }
   // corner coordinates in R; x1 and the query x are normalised against the
@@ -283,8 +279,11 @@ geometric_kernel(const __grid_constant__ GeoParams p) {
   R* __restrict__ out = static_cast<R*>(p.out);
   for (long long k = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; k < p.n;
        k += stride) {
+    using Z = typename std::conditional<ZI64, long long, double>::type;
     R res = RT<R>::nan();
-    const int bad = geometric_point<ND, DT, R, ZI64>(p, k, res);
+    const Z z = ND >= 3 ? __ldg(static_cast<const Z*>(p.z) + k) : Z(0);
+    const double u = ND >= 4 ? __ldg(p.u + k) : 0.0;
+    const int bad = geometric_eval<ND, DT, R, ZI64>(p, __ldg(p.x + k), __ldg(p.y + k), z, u, res);
     if (bad >= 0) {
       res = RT<R>::nan();
       const unsigned long long kk = (static_cast<unsigned long long>(p.index_base + k) << 2) | bad;
