@@ -13,6 +13,7 @@
 //   find_indexes_kernel / find_index_kernel   K5: Axis::find_indexes / find_index
 //   pack_cells2d_kernel             one-off cell packing of a 2-D grid
 #include <atomic>
+#include <cstdlib>
 
 #include "../../include/pyinterp_b200.h"
 #include "pyi_kernels.cuh"
