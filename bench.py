@@ -56,6 +56,20 @@ def default_points(workload: str) -> int:
             "quadrivariate": 100_000_000}[workload]
 
 
+def ncu_traffic(workload, n):
+    """DRAM bytes per launch from the committed `ncu --set full` capture of the
+    workload's kernel (profiles/roofline_traffic.json: bytes per point measured
+    under ncu), scaled to this launch's point count; None when no capture."""
+    path = os.path.join(ROOT, "profiles", "roofline_traffic.json")
+    try:
+        with open(path) as f:
+            e = json.load(f)[workload]
+        return {"bytes_per_launch": e["dram_bytes_per_point"] * n, "dram_bytes_per_point": e["dram_bytes_per_point"],
+                "source": e["source"]}
+    except Exception:
+        return None
+
+
 def peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(path):
@@ -171,24 +185,58 @@ def run_reference_arm(args):
 # clocks
 # ---------------------------------------------------------------------------
 class ClockSampler:
+    """Samples SM clock and throttle reasons DURING the timed region: NVML in
+    this process every 5 ms (nvidia-smi as a subprocess is too slow for a
+    70 ms region); falls back to nvidia-smi when NVML is unavailable."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
 
     def __init__(self, index):
         self.index, self.samples, self.stop = index, [], threading.Event()
+        self.max_mhz, self.nvml, self.handle = None, None, None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = index
+            if vis:
+                ids = [v.strip() for v in vis.split(",") if v.strip()]
+                if index < len(ids) and ids[index].isdigit():
+                    phys = int(ids[index])
+            self.handle = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.handle, pynvml.NVML_CLOCK_SM))
+            self.nvml = pynvml
+        except Exception:
+            self.nvml = None
         self.thread = threading.Thread(target=self._loop, daemon=True)
+
+    def _sample_nvml(self):
+        n = self.nvml
+        mhz = float(n.nvmlDeviceGetClockInfo(self.handle, n.NVML_CLOCK_SM))
+        r = int(n.nvmlDeviceGetCurrentClocksEventReasons(self.handle)) if hasattr(
+            n, "nvmlDeviceGetCurrentClocksEventReasons") else int(n.nvmlDeviceGetCurrentClocksThrottleReasons(self.handle))
+        flags = [bool(r & 0x8), bool(r & 0x40), bool(r & 0x20), bool(r & 0x4)]
+        self.samples.append((mhz, flags))
+
+    def _sample_smi(self):
+        out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                              "-i", str(self.index)], capture_output=True, text=True, timeout=5).stdout
+        f = [s.strip() for s in out.strip().split(",")]
+        if len(f) >= 6:
+            self.max_mhz = float(f[1])
+            self.samples.append((float(f[0]), [v.lower().startswith("active") for v in f[2:6]]))
 
     def _loop(self):
         while not self.stop.is_set():
             try:
-                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                      "-i", str(self.index)], capture_output=True, text=True, timeout=5).stdout
-                f = [s.strip() for s in out.strip().split(",")]
-                if len(f) >= 6:
-                    self.samples.append(f)
+                if self.nvml is not None:
+                    self._sample_nvml()
+                else:
+                    self._sample_smi()
             except Exception:
                 pass
-            self.stop.wait(0.2)
+            self.stop.wait(0.005 if self.nvml is not None else 0.2)
 
     def __enter__(self):
         self.thread.start()
@@ -201,11 +249,10 @@ class ClockSampler:
     def summary(self):
         if not self.samples:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unavailable"]}
-        mhz = sorted(float(s[0]) for s in self.samples)
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = [n for k, n in enumerate(names) if any(s[2 + k].lower().startswith("active") for s in self.samples)]
-        return {"sm_mhz": mhz[len(mhz) // 2], "sm_max_mhz": float(self.samples[0][1]), "reasons": reasons,
-                "samples": len(mhz)}
+        mhz = sorted(s[0] for s in self.samples)
+        reasons = [n for k, n in enumerate(self.NAMES) if any(s[1][k] for s in self.samples)]
+        return {"sm_mhz": mhz[len(mhz) // 2], "sm_max_mhz": self.max_mhz, "reasons": reasons,
+                "samples": len(mhz), "source": "nvml" if self.nvml is not None else "nvidia-smi"}
 
 
 # ---------------------------------------------------------------------------
@@ -364,6 +411,7 @@ def main():
         bpp = BYTES_PER_POINT[args.workload]
         k_ms = sum(kernel_ms) / len(kernel_ms)
         achieved = n * bpp / (k_ms / 1e3) / 1e9
+        tr = ncu_traffic(args.workload, n)
         line = {
             "metric": METRIC, "value": value, "unit": METRIC, "n_gpus": world, "steps": args.steps,
             "warmup": max(3, args.warmup), "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
@@ -375,7 +423,8 @@ def main():
             "e2e": {"value": e2e_value, "unit": METRIC, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "frac": achieved / peak, "traffic": (tr or {}).get("bytes_per_launch"), "traffic_detail": tr,
+                         "peak_source": peak_src,
                          "bytes_per_point": bpp, "kernel_ms": k_ms},
             "clocks": clk.summary(),
         }

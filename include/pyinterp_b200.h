@@ -172,7 +172,9 @@ pyi_grid *pyi_grid_create(int ndim, const pyi_axis *const *axes, int dtype,
 /* Re-upload the array (the reference borrows the caller's numpy buffer, which
  * may be mutated between calls). Rebuilds the packed copy if there is one. */
 int pyi_grid_update(pyi_grid *grid, const void *data, int mem);
-/* Build (or rebuild) the cell-packed copy. */
+/* Build (or rebuild) the cell-packed copy (2^ndim corners per cell, result
+ * type). Skipped, with PYI_OK, when it would take more than half of the free
+ * device memory: the kernels then gather from the plain C-order array. */
 int pyi_grid_pack(pyi_grid *grid);
 void pyi_grid_destroy(pyi_grid *grid);
 

@@ -365,7 +365,7 @@ class Grid:
         handles = (_P * len(axes))(*[a._h for a in axes])
         shp = (C.c_int64 * len(axes))(*self._shape)
         st = C.c_int(0)
-        flags = _abi.PYI_GRID_PACK_CELLS if (pack_cells and len(axes) == 2) else _abi.PYI_GRID_DEFAULT
+        flags = _abi.PYI_GRID_PACK_CELLS if pack_cells else _abi.PYI_GRID_DEFAULT
         if dev_ctx is not None:
             with dev_ctx:
                 self._h = lib.pyi_grid_create(len(axes), handles, _abi.DTYPES[dtype_name], ptr, shp, mem,

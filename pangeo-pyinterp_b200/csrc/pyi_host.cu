@@ -603,16 +603,26 @@ int pyi_grid_update(pyi_grid* grid, const void* data, int mem) {
 
 int pyi_grid_pack(pyi_grid* grid) {
   if (!grid) return fail(PYI_BAD_ARG, "null grid");
-  if (grid->ndim != 2) return PYI_OK;  // cell packing exists for 2-D grids only
-  const size_t cells = static_cast<size_t>(grid->shape[0]) * static_cast<size_t>(grid->shape[1]);
-  const size_t elem = result_is_f64(grid->dtype) ? 8 : 4;
-  if (!grid->d_packed) {
-    PYI_CUDA(cudaMalloc(&grid->d_packed, cells * 4 * elem));
+  size_t cells = 1;
+  int shape[4] = {1, 1, 1, 1};
+  for (int k = 0; k < grid->ndim; ++k) {
+    cells *= static_cast<size_t>(grid->shape[k]);
+    shape[k] = static_cast<int>(grid->shape[k]);
   }
-  cudaError_t e = pyi::launch_pack_cells2d(grid->d_data, grid->dtype,
-                                           static_cast<int>(grid->shape[0]),
-                                           static_cast<int>(grid->shape[1]), grid->d_packed, nullptr);
-  if (e != cudaSuccess) return cuda_fail(e, "pack_cells2d");
+  const size_t elem = result_is_f64(grid->dtype) ? 8 : 4;
+  const size_t bytes = (cells << grid->ndim) * elem;
+  if (!grid->d_packed) {
+    // The packed copy is 2^ndim x the grid (in the result type).  It is an
+    // optimisation: when it would not leave room for the query streams the
+    // kernels keep reading the plain C-order array.
+    size_t free_b = 0, total_b = 0;
+    PYI_CUDA(cudaMemGetInfo(&free_b, &total_b));
+    if (bytes > free_b / 2) return PYI_OK;
+    PYI_CUDA(cudaMalloc(&grid->d_packed, std::max<size_t>(bytes, 64)));
+  }
+  cudaError_t e = pyi::launch_pack_cells(grid->d_data, grid->dtype, grid->ndim, shape,
+                                         grid->d_packed, nullptr);
+  if (e != cudaSuccess) return cuda_fail(e, "pack_cells");
   PYI_CUDA(cudaStreamSynchronize(nullptr));
   return PYI_OK;
 }

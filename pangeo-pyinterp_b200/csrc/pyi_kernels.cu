@@ -195,7 +195,17 @@ __device__ __forceinline__ R axis_interp(int method, Z x, Z x0, Z x1, R y0, R y1
 // One query point (pybind/geometric/bivariate.hpp:47-97, trivariate.hpp:47-123,
 // quadrivariate.hpp:50-148).  Returns -1 and the value, or the first axis (in
 // x, y, z, u order) that could not bracket the point.
-template <int ND, int DT, typename R, bool ZI64>
+// Cell index and orientation of a bracket pair on one axis for the cell-packed
+// copy: a pair is either (k, k+1) / the periodic seam (n-1, 0) -> cell k, or
+// the same pair reversed (descending axes, axis.hpp:759-777) -> cell of the
+// lower index with the two corners exchanged.
+__device__ __forceinline__ int cell_of(const DAxis& a, int i0, int i1, bool& swapped) {
+  const bool fwd = (i1 == i0 + 1) || (a.periodic && i0 == a.n - 1 && i1 == 0);
+  swapped = !fwd;
+  return fwd ? i0 : i1;
+}
+
+template <int ND, int DT, typename R, bool ZI64, bool PACKED = false>
 __device__ __forceinline__ int geometric_eval(
     const GeoParams& p, double x, double y,
     typename std::conditional<ZI64, long long, double>::type z, double u, R& res) {
@@ -226,18 +236,99 @@ __device__ __forceinline__ int geometric_eval(
   constexpr int NU = ND >= 4 ? 2 : 1;
   // gather first (all loads in flight), then evaluate
   R q[NZ][NU][2][2];
+  if (PACKED) {
+    // one aligned run of 2^ND values: corner (a, b, c, d) at ((a*2 + b)*NZ + c)*NU + d
+    bool sx, sy, sz = false, su = false;
+    long long cell = static_cast<long long>(cell_of(p.ax[0], ix[0], ix[1], sx)) * n1 +
+                     cell_of(p.ax[1], iy[0], iy[1], sy);
+    if (ND >= 3) cell = cell * n2 + cell_of(p.ax[2], iz[0], iz[1], sz);
+    if (ND >= 4) cell = cell * n3 + cell_of(p.ax[3], iu[0], iu[1], su);
+    constexpr int NV = 4 * NZ * NU;
+    constexpr int NQ = NV * static_cast<int>(sizeof(R)) / 16;
+    union {
+      uint4 w[NQ];
+      R v[NV];
+    } buf;
+    const uint4* src = reinterpret_cast<const uint4*>(static_cast<const R*>(p.packed) + cell * NV);
 #pragma unroll
-  for (int c = 0; c < NZ; ++c) {
+    for (int k = 0; k < NQ; ++k) {
+      asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                   : "=r"(buf.w[k].x), "=r"(buf.w[k].y), "=r"(buf.w[k].z), "=r"(buf.w[k].w)
+                   : "l"(src + k));
+    }
 #pragma unroll
-    for (int d = 0; d < NU; ++d) {
+    for (int a = 0; a < 2; ++a) {
 #pragma unroll
-      for (int a = 0; a < 2; ++a) {
+      for (int b = 0; b < 2; ++b) {
 #pragma unroll
-        for (int b = 0; b < 2; ++b) {
-          long long off = ix[a] * n1 + iy[b];
-          if (ND >= 3) off = off * n2 + iz[c];
-          if (ND >= 4) off = off * n3 + iu[d];
-          q[c][d][a][b] = load_value<DT, R>(p.data, p.dtype, off);
+        for (int c = 0; c < NZ; ++c) {
+#pragma unroll
+          for (int d = 0; d < NU; ++d) q[c][d][a][b] = buf.v[((a * 2 + b) * NZ + c) * NU + d];
+        }
+      }
+    }
+    if (sx | sy | sz | su) {  // reversed pairs (descending axes): exchange corners
+#pragma unroll
+      for (int c = 0; c < NZ; ++c) {
+#pragma unroll
+        for (int d = 0; d < NU; ++d) {
+#pragma unroll
+          for (int b = 0; b < 2; ++b) {
+            const R t0 = q[c][d][0][b], t1 = q[c][d][1][b];
+            q[c][d][0][b] = sx ? t1 : t0;
+            q[c][d][1][b] = sx ? t0 : t1;
+          }
+#pragma unroll
+          for (int a = 0; a < 2; ++a) {
+            const R t0 = q[c][d][a][0], t1 = q[c][d][a][1];
+            q[c][d][a][0] = sy ? t1 : t0;
+            q[c][d][a][1] = sy ? t0 : t1;
+          }
+        }
+      }
+      if (ND >= 3) {
+#pragma unroll
+        for (int d = 0; d < NU; ++d) {
+#pragma unroll
+          for (int a = 0; a < 2; ++a) {
+#pragma unroll
+            for (int b = 0; b < 2; ++b) {
+              const R t0 = q[0][d][a][b], t1 = q[NZ - 1][d][a][b];
+              q[0][d][a][b] = sz ? t1 : t0;
+              q[NZ - 1][d][a][b] = sz ? t0 : t1;
+            }
+          }
+        }
+      }
+      if (ND >= 4) {
+#pragma unroll
+        for (int c = 0; c < NZ; ++c) {
+#pragma unroll
+          for (int a = 0; a < 2; ++a) {
+#pragma unroll
+            for (int b = 0; b < 2; ++b) {
+              const R t0 = q[c][0][a][b], t1 = q[c][NU - 1][a][b];
+              q[c][0][a][b] = su ? t1 : t0;
+              q[c][NU - 1][a][b] = su ? t0 : t1;
+            }
+          }
+        }
+      }
+    }
+  } else {
+#pragma unroll
+    for (int c = 0; c < NZ; ++c) {
+#pragma unroll
+      for (int d = 0; d < NU; ++d) {
+#pragma unroll
+        for (int a = 0; a < 2; ++a) {
+#pragma unroll
+          for (int b = 0; b < 2; ++b) {
+            long long off = ix[a] * n1 + iy[b];
+            if (ND >= 3) off = off * n2 + iz[c];
+            if (ND >= 4) off = off * n3 + iu[d];
+            q[c][d][a][b] = load_value<DT, R>(p.data, p.dtype, off);
+          }
         }
       }
     }
@@ -272,7 +363,7 @@ __device__ __forceinline__ int geometric_eval(
   return -1;
 }
 
-template <int ND, int DT, typename R, bool ZI64>
+template <int ND, int DT, typename R, bool ZI64, bool PACKED>
 __global__ void __launch_bounds__(kThreads)
 geometric_kernel(const __grid_constant__ GeoParams p) {
   const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
@@ -284,7 +375,7 @@ geometric_kernel(const __grid_constant__ GeoParams p) {
     R res = RT<R>::nan();
     const Z z = ND >= 3 ? __ldg(static_cast<const Z*>(p.z) + k) : Z(0);
     const double u = ND >= 4 ? __ldg(p.u + k) : 0.0;
-    const int bad = geometric_eval<ND, DT, R, ZI64>(p, __ldg(p.x + k), __ldg(p.y + k), z, u, res);
+    const int bad = geometric_eval<ND, DT, R, ZI64, PACKED>(p, __ldg(p.x + k), __ldg(p.y + k), z, u, res);
     if (bad >= 0) {
       res = RT<R>::nan();
       const unsigned long long kk = (static_cast<unsigned long long>(p.index_base + k) << 2) | bad;
@@ -301,14 +392,21 @@ template <int ND, bool ZI64>
 static cudaError_t launch_geometric_nd(const GeoParams& p, cudaStream_t stream) {
   const int blocks = grid_for(p.n, kThreads, 8);
   const bool r64 = p.dtype == PYI_F64 || p.dtype == PYI_I64 || p.dtype == PYI_U64;
-  if (p.dtype == PYI_F64) {
-    geometric_kernel<ND, PYI_F64, double, ZI64><<<blocks, kThreads, 0, stream>>>(p);
+  if (p.packed != nullptr) {
+    // cell-packed copy (already in the result type): one aligned run per point
+    if (r64) {
+      geometric_kernel<ND, -1, double, ZI64, true><<<blocks, kThreads, 0, stream>>>(p);
+    } else {
+      geometric_kernel<ND, -1, float, ZI64, true><<<blocks, kThreads, 0, stream>>>(p);
+    }
+  } else if (p.dtype == PYI_F64) {
+    geometric_kernel<ND, PYI_F64, double, ZI64, false><<<blocks, kThreads, 0, stream>>>(p);
   } else if (p.dtype == PYI_F32) {
-    geometric_kernel<ND, PYI_F32, float, ZI64><<<blocks, kThreads, 0, stream>>>(p);
+    geometric_kernel<ND, PYI_F32, float, ZI64, false><<<blocks, kThreads, 0, stream>>>(p);
   } else if (r64) {
-    geometric_kernel<ND, -1, double, ZI64><<<blocks, kThreads, 0, stream>>>(p);
+    geometric_kernel<ND, -1, double, ZI64, false><<<blocks, kThreads, 0, stream>>>(p);
   } else {
-    geometric_kernel<ND, -1, float, ZI64><<<blocks, kThreads, 0, stream>>>(p);
+    geometric_kernel<ND, -1, float, ZI64, false><<<blocks, kThreads, 0, stream>>>(p);
   }
   g_launches.fetch_add(1);
   return cudaGetLastError();
@@ -450,40 +548,65 @@ cudaError_t launch_find_index(const FindParams& p, cudaStream_t stream) {
 }
 
 // ---------------------------------------------------------------------------
-// one-off 2-D cell packing: the four corners of cell (ix, iy) contiguous, in
-// the result type, 32 B (f64) / 16 B (f32) aligned: one sector per query.
-// ix + 1 wraps (the periodic seam cell is materialised), iy + 1 clamps.
+// one-off cell packing: the 2^ND corners of cell (ix, iy[, iz[, iu]]) contiguous
+// in the result type, corner (a, b, c, d) at ((a*2 + b)*NZ + c)*NU + d: a 2-D
+// f64 / 3-D f32 cell is exactly one 32-byte sector, a 4-D f32 cell one 64-byte
+// line.  ix + 1 wraps (the periodic seam cell is materialised), the other axes
+// clamp (their last cell is never addressed by a valid bracket).  One thread
+// per output element: coalesced stores.
 // ---------------------------------------------------------------------------
 template <typename R>
 __global__ void __launch_bounds__(kThreads)
-pack_cells2d_kernel(const void* __restrict__ data, int dtype, int nx, int ny, R* __restrict__ cells) {
-  const long long total = static_cast<long long>(nx) * ny;
+pack_cells_kernel(const void* __restrict__ data, int dtype, int ndim, int nx, int ny, int nz, int nu,
+                  R* __restrict__ cells) {
+  const int corners = 1 << ndim;
+  const long long total = static_cast<long long>(nx) * ny * nz * nu * corners;
   const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
-  for (long long c = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; c < total;
-       c += stride) {
+  for (long long e = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; e < total;
+       e += stride) {
+    int corner = static_cast<int>(e & (corners - 1));
+    long long c = e >> ndim;
+    int d = 0, cc = 0;
+    int iu = 0, iz = 0;
+    if (ndim >= 4) {
+      d = corner & 1;
+      corner >>= 1;
+      iu = static_cast<int>(c % nu);
+      c /= nu;
+    }
+    if (ndim >= 3) {
+      cc = corner & 1;
+      corner >>= 1;
+      iz = static_cast<int>(c % nz);
+      c /= nz;
+    }
+    const int b = corner & 1;
+    const int a = corner >> 1;
+    const int iy = static_cast<int>(c % ny);
     const int ix = static_cast<int>(c / ny);
-    const int iy = static_cast<int>(c - static_cast<long long>(ix) * ny);
-    const int ix1 = ix + 1 == nx ? 0 : ix + 1;
-    const int iy1 = iy + 1 == ny ? iy : iy + 1;
-    R* o = cells + 4 * c;
-    o[0] = load_value<-1, R>(data, dtype, static_cast<long long>(ix) * ny + iy);
-    o[1] = load_value<-1, R>(data, dtype, static_cast<long long>(ix) * ny + iy1);
-    o[2] = load_value<-1, R>(data, dtype, static_cast<long long>(ix1) * ny + iy);
-    o[3] = load_value<-1, R>(data, dtype, static_cast<long long>(ix1) * ny + iy1);
+    const int jx = (ix + a == nx) ? 0 : ix + a;
+    const int jy = (iy + b == ny) ? iy : iy + b;
+    const int jz = (iz + cc == nz) ? iz : iz + cc;
+    const int ju = (iu + d == nu) ? iu : iu + d;
+    const long long off = ((static_cast<long long>(jx) * ny + jy) * nz + jz) * nu + ju;
+    cells[e] = load_value<-1, R>(data, dtype, off);
   }
 }
 
-cudaError_t launch_pack_cells2d(const void* data, int dtype, int nx, int ny, void* packed,
-                                cudaStream_t stream) {
-  const long long total = static_cast<long long>(nx) * ny;
+cudaError_t launch_pack_cells(const void* data, int dtype, int ndim, const int* shape, void* packed,
+                              cudaStream_t stream) {
+  const int nx = shape[0], ny = shape[1];
+  const int nz = ndim >= 3 ? shape[2] : 1;
+  const int nu = ndim >= 4 ? shape[3] : 1;
+  const long long total = (static_cast<long long>(nx) * ny * nz * nu) << ndim;
   const int blocks = grid_for(total, kThreads, 8);
   const bool r64 = dtype == PYI_F64 || dtype == PYI_I64 || dtype == PYI_U64;
   if (r64) {
-    pack_cells2d_kernel<double><<<blocks, kThreads, 0, stream>>>(data, dtype, nx, ny,
-                                                                 static_cast<double*>(packed));
+    pack_cells_kernel<double><<<blocks, kThreads, 0, stream>>>(data, dtype, ndim, nx, ny, nz, nu,
+                                                               static_cast<double*>(packed));
   } else {
-    pack_cells2d_kernel<float><<<blocks, kThreads, 0, stream>>>(data, dtype, nx, ny,
-                                                                static_cast<float*>(packed));
+    pack_cells_kernel<float><<<blocks, kThreads, 0, stream>>>(data, dtype, ndim, nx, ny, nz, nu,
+                                                              static_cast<float*>(packed));
   }
   g_launches.fetch_add(1);
   return cudaGetLastError();

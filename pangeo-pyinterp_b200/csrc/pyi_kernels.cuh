@@ -15,7 +15,7 @@ constexpr unsigned long long kNoOob = ~0ULL;
 struct GeoParams {
   DAxis ax[4];
   const void* data;   // grid values, C order [x][y][z][u]
-  const void* packed; // cell-packed copy (2-D: 4 corners per cell) or nullptr
+  const void* packed; // cell-packed copy (2^ndim corners per cell, result type) or nullptr
   int32_t dtype;      // pyi_dtype
   int32_t ndim;
   int32_t method, idw_exp, z_method, u_method;
@@ -58,10 +58,10 @@ cudaError_t launch_geometric(const GeoParams& p, cudaStream_t stream);
 cudaError_t launch_windowed2d(const WinParams& p, cudaStream_t stream);
 cudaError_t launch_find_indexes(const FindParams& p, cudaStream_t stream);
 cudaError_t launch_find_index(const FindParams& p, cudaStream_t stream);
-// 2-D cell packing: cells[(ix * ny + iy)] = {v(ix,iy), v(ix,iy+1), v(ix+1,iy), v(ix+1,iy+1)}
-// converted to the result type; ix+1 wraps (periodic x), iy+1 clamps.
-cudaError_t launch_pack_cells2d(const void* data, int dtype, int nx, int ny, void* packed,
-                                cudaStream_t stream);
+// cell packing (2-D .. 4-D): the 2^ndim corners of every cell contiguous, in the
+// result type; x + 1 wraps (periodic seam cell), the other axes clamp.
+cudaError_t launch_pack_cells(const void* data, int dtype, int ndim, const int* shape, void* packed,
+                              cudaStream_t stream);
 // number of kernels launched so far by this library (all threads)
 long long launch_count();
 

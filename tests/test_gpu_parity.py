@@ -78,7 +78,7 @@ def test_axis_lookup_device_tensor(pyi, orc_best):
 
 
 def _grid_pair(pyi, o, nd, dtype, x_kind="lon_periodic", y_kind="lat", z_kind="monthly30", flip_z=False, nan=0.02,
-               small=True):
+               small=True, pack_cells=True):
     fz, iz = axes_zoo.f64_axes(), axes_zoo.i64_axes()
     if small:
         specs = [(np.arange(72) * 5.0, dict(period=360.0), False) if x_kind == "lon_periodic" else fz[x_kind],
@@ -101,7 +101,7 @@ def _grid_pair(pyi, o, nd, dtype, x_kind="lon_periodic", y_kind="lat", z_kind="m
     else:
         info = np.iinfo(dtype)
         g = np.clip(np.round(g), info.min, info.max).astype(dtype)
-    grid = pyi.Grid(*[p[0] for p in pairs], g)
+    grid = pyi.Grid(*[p[0] for p in pairs], g, pack_cells=pack_cells)
     return grid, [p[1] for p in pairs], g
 
 
@@ -176,6 +176,31 @@ def test_geometric_idw_nearest(pyi, orc_best, nd, dtype, method):
     else:
         # nearest: mismatches only at (near-)ties: points on a cell mid-line
         assert bad.size <= max(3, n // 2000), bad.size
+
+
+@pytest.mark.parametrize("nd", [2, 3, 4])
+@pytest.mark.parametrize("dtype", ["float64", "float32", "int16", "uint64"])
+@pytest.mark.parametrize("case", [dict(), dict(x_kind="lon_periodic_desc", y_kind="lat_desc", small=False, flip_z=True),
+                                  dict(x_kind="irregular_periodic", y_kind="small_irregular_desc")])
+def test_plain_layout_matches_packed_and_oracle(pyi, orc_best, nd, dtype, case):
+    """The kernels gather either from the cell-packed copy (default) or, when it
+    does not fit, from the caller's C-order array: both must give the oracle's
+    bits, for every method."""
+    n = 20_000
+    case = dict(case)
+    small = case.pop("small", True)
+    plain, caxes, g = _grid_pair(pyi, orc_best, nd, dtype, small=small, pack_cells=False, **case)
+    packed, _, _ = _grid_pair(pyi, orc_best, nd, dtype, small=small, pack_cells=True, **case)
+    ds = [c.describe() for c in caxes]
+    q = _queries(nd, n, 11, xr=(ds[0]["min_value"] - 400, ds[0]["max_value"] + 400),
+                 yr=(ds[1]["min_value"] - 3, ds[1]["max_value"] + 3))
+    for method in (0, 1, 2):
+        cfg = _geo_cfg(pyi, nd, method)
+        a = _call(pyi, plain, q, cfg)
+        b = _call(pyi, packed, q, cfg)
+        assert np.array_equal(a, b, equal_nan=True), (nd, dtype, method)
+    want, _ = orc_best.geometric(caxes, g, *q, method=0, num_threads=0)
+    assert close(_call(pyi, plain, q, _geo_cfg(pyi, nd, 0)), want, 50.0, "plain layout") == 1.0
 
 
 @pytest.mark.parametrize("case", [
