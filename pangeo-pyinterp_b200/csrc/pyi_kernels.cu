@@ -244,17 +244,28 @@ __device__ __forceinline__ int geometric_eval(
     if (ND >= 3) cell = cell * n2 + cell_of(p.ax[2], iz[0], iz[1], sz);
     if (ND >= 4) cell = cell * n3 + cell_of(p.ax[3], iu[0], iu[1], su);
     constexpr int NV = 4 * NZ * NU;
-    constexpr int NQ = NV * static_cast<int>(sizeof(R)) / 16;
+    constexpr int BYTES = NV * static_cast<int>(sizeof(R));
     union {
-      uint4 w[NQ];
+      unsigned long long w[BYTES / 8];
       R v[NV];
     } buf;
-    const uint4* src = reinterpret_cast<const uint4*>(static_cast<const R*>(p.packed) + cell * NV);
+    const char* src = reinterpret_cast<const char*>(static_cast<const R*>(p.packed) + cell * NV);
+    if (BYTES >= 32) {
+      // The memory system serves a fixed number of load REQUESTS per second for
+      // scattered lines (measured: profiles/r1_gather_probe.txt), so a 32-byte
+      // cell is read with ONE 256-bit load, not two 128-bit ones; .L2::64B keeps
+      // the DRAM fill at 64 bytes instead of the whole 128-byte line.
 #pragma unroll
-    for (int k = 0; k < NQ; ++k) {
-      asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
-                   : "=r"(buf.w[k].x), "=r"(buf.w[k].y), "=r"(buf.w[k].z), "=r"(buf.w[k].w)
-                   : "l"(src + k));
+      for (int k = 0; k < BYTES / 32; ++k) {
+        asm volatile("ld.global.nc.L1::no_allocate.L2::64B.v4.u64 {%0,%1,%2,%3}, [%4];"
+                     : "=l"(buf.w[4 * k]), "=l"(buf.w[4 * k + 1]), "=l"(buf.w[4 * k + 2]),
+                       "=l"(buf.w[4 * k + 3])
+                     : "l"(src + 32 * k));
+      }
+    } else {  // 2-D float cells: 16 bytes
+      asm volatile("ld.global.nc.L1::no_allocate.v2.u64 {%0,%1}, [%2];"
+                   : "=l"(buf.w[0]), "=l"(buf.w[1])
+                   : "l"(src));
     }
 #pragma unroll
     for (int a = 0; a < 2; ++a) {
