@@ -38,7 +38,10 @@ struct DAxis {
   double hi;            // fl(min + period)
   double seam_c1;       // periodic: normalize(node(0), min = node(n-1)), math/axis.hpp:294-301
   double seam_c1_f32;   // same against the float-rounded node(n-1) (float results)
-  int32_t fast_ok;      // ascending f64 axis with moderate magnitudes and spacings
+  int32_t fast_ok;      // ascending f64 axis with moderate magnitudes and spacings, or an
+                        // ascending regular i64 axis with |start|, span < 2^61 (then
+                        // inv_step = 1.0 / step and ispan = (n - 1) * step)
+  long long ispan;
 };
 
 // ---------------------------------------------------------------------------

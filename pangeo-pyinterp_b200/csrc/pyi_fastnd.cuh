@@ -1,0 +1,282 @@
+// pyi_fastnd.cuh -- K2 / K3 fast path: trivariate / quadrivariate with the
+// bilinear spatial evaluator and linear or nearest z / u interpolation, float
+// results (every grid dtype except f64 / i64 / u64), ascending axes, reading
+// the cell-packed copy.  Included by pyi_kernels.cu after pyi_fast2d.cuh.
+//
+// What is computed is trivariate_single / quadrivariate_single
+// (pybind/geometric/trivariate.hpp:47-123, quadrivariate.hpp:50-148) with
+// geometric::trivariate / quadrivariate (math/interpolate/geometric/
+// multivariate.hpp:133-153, 271-306), Bilinear::evaluate
+// (geometric/bivariate.hpp:110-132) and linear / nearest
+// (interpolate/linear.hpp:22-33, nearest.hpp:21-32): same roundings, same
+// operation order.  As in pyi_fast2d.cuh the brackets are GUESSED with a floor
+// and VERIFIED against the reference's own node values; a verified bracket is
+// the reference's bracket, anything else is re-done by the generic code
+// (geometric_eval) behind a non-inlined call.  The generic path costs ~1100
+// instructions per 4-D point (ncu, profiles/), this one a few hundred, and the
+// kernels are instruction-bound once the gather is one request per cell.
+//
+//   x  regular ascending f64, with or without period
+//   y  regular or irregular ascending f64, no period
+//   z  regular ascending i64 (TemporalAxis), or regular / irregular ascending f64
+//   u  regular or irregular ascending f64
+#pragma once
+
+namespace pyi {
+
+constexpr int kNdMaxIrregular = 256;  // z / u points staged in shared memory
+constexpr int kNdMaxLut = 4 * kNdMaxIrregular + 1;
+
+// Verified bracket on a regular ascending int64 axis (|start|, span < 2^61, so
+// the wrapped difference below is in [0, span) only for coordinates inside the
+// axis).  k = floor((z - start) / step) estimated in double and corrected by
+// at most one step with exact integer arithmetic; d0 = z - node(k), exact.
+// Regular<int64>::find_index rounds to the nearest node and Axis::find_indexes
+// steps by the sign of z - node (container.hpp:588-615, axis.hpp:745-766): for
+// an ascending axis that is the pair (k, k + 1) with node(k) <= z < node(k+1).
+// The last node itself ((n-2, n-1), axis.hpp:748-757) is left to the generic code.
+__device__ __forceinline__ void bracket_regular_i64(const DAxis& a, long long z, int& k,
+                                                    long long& d0, bool& ok) {
+  const long long num = static_cast<long long>(static_cast<unsigned long long>(z) -
+                                               static_cast<unsigned long long>(a.istart));
+  const bool inside = num >= 0 && num < a.ispan;
+  const long long nn = inside ? num : 0;
+  int kk = __double2int_rd(__dmul_rn(static_cast<double>(nn), a.inv_step));
+  long long d = nn - static_cast<long long>(kk) * a.istep;
+  if (d < 0) {
+    kk -= 1;
+    d += a.istep;
+  } else if (d >= a.istep) {
+    kk += 1;
+    d -= a.istep;
+  }
+  ok = ok && inside && d >= 0 && d < a.istep &&
+       static_cast<unsigned>(kk) < static_cast<unsigned>(a.n - 1);
+  k = ok ? kk : 0;
+  d0 = d;
+}
+
+// regular or irregular ascending f64 axis without period (uniform branch)
+__device__ __forceinline__ RegBracket bracket_f64(const DAxis& a, const double* sp, const int* slut,
+                                                  double c, bool& ok) {
+  if (a.kind != 0) return bracket_irregular(a, sp, slut, c, ok);
+  return bracket_regular<false>(a, c, 0.0, ok);
+}
+
+// linear<Z, float> / nearest<Z, float> on a verified bracket z0 <= z < z1.
+// f64 axis: dl = fl(z - z0), c1 = z1.
+__device__ __forceinline__ float axis_mix_f64(int method, double z, const RegBracket& b, float y0,
+                                              float y1) {
+  if (method == PYI_AXIS_NEAREST) {
+    // |z0 - z| < |z1 - z| ? y0 : y1 ; |z0 - z| == dl exactly
+    return b.dl < __dsub_rn(b.c1, z) ? y0 : y1;
+  }
+  const float dx = static_cast<float>(__dsub_rn(b.c1, b.c0));
+  const float t = __fdiv_rn(static_cast<float>(b.dl), dx);
+  return y0 + t * (y1 - y0);
+}
+// i64 axis: d0 = z - z0 and step = z1 - z0, exact
+__device__ __forceinline__ float axis_mix_i64(int method, long long d0, long long step, float y0,
+                                              float y1) {
+  if (method == PYI_AXIS_NEAREST) {
+    return d0 < step - d0 ? y0 : y1;
+  }
+  const float dx = static_cast<float>(step);
+  const float t = __fdiv_rn(static_cast<float>(d0), dx);
+  return y0 + t * (y1 - y0);
+}
+
+// The generic code, out of line (reads the packed copy with its own loads).
+template <int ND, bool ZI64>
+__device__ __noinline__ float slow_point_nd(const GeoParams& p, double x, double y,
+                                            typename ZOf<ZI64>::type z, double u, long long index) {
+  float res;
+  const int bad = geometric_eval<ND, -1, float, ZI64, true>(p, x, y, z, u, res);
+  if (bad < 0) return res;
+  if (p.bounds_error) {
+    atomicMin(p.oob_key, (static_cast<unsigned long long>(p.index_base + index) << 2) | bad);
+  }
+  return CUDART_NAN_F;
+}
+
+__device__ __forceinline__ void stage_axis(const DAxis& a, double* sp, int* slut) {
+  if (a.kind == 0 || a.coord_i64) return;
+  const double* gp = static_cast<const double*>(a.points);
+  for (int i = threadIdx.x; i < a.n; i += blockDim.x) sp[i] = __ldg(gp + i);
+  for (int i = threadIdx.x; i <= a.lut_bins; i += blockDim.x) slut[i] = __ldg(a.lut + i);
+}
+
+// One point per thread and iteration; whole warps iterate together so that
+// lane pairs can share the line requests of 64-byte cells (4-D).
+template <int ND, bool ZI64>
+__global__ void __launch_bounds__(kFastThreads, 3)
+bilinear_nd_fast_kernel(const __grid_constant__ GeoParams p) {
+  using Z = typename ZOf<ZI64>::type;
+  __shared__ double s_y[kFastMaxIrregular];
+  __shared__ int s_ylut[kFastMaxLut];
+  __shared__ double s_z[kNdMaxIrregular];
+  __shared__ int s_zlut[kNdMaxLut];
+  __shared__ double s_u[ND >= 4 ? kNdMaxIrregular : 1];
+  __shared__ int s_ulut[ND >= 4 ? kNdMaxLut : 1];
+  stage_axis(p.ax[1], s_y, s_ylut);
+  stage_axis(p.ax[2], s_z, s_zlut);
+  if (ND >= 4) stage_axis(p.ax[3], s_u, s_ulut);
+  __syncthreads();
+
+  const DAxis& ax = p.ax[0];
+  const DAxis& ay = p.ax[1];
+  const DAxis& az = p.ax[2];
+  const bool per = ax.period != 0.0;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  const unsigned lane = threadIdx.x & 31u;
+  float* __restrict__ out = static_cast<float*>(p.out);
+  const Z* __restrict__ zs = static_cast<const Z*>(p.z);
+
+  long long k = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  // software pipeline: the coordinates of the next iteration are in flight
+  double x = 0.0, y = 0.0, u = 0.0;
+  Z z = Z(0);
+  if (k < p.n) {
+    x = __ldcs(p.x + k);
+    y = __ldcs(p.y + k);
+    z = __ldcs(zs + k);
+    if (ND >= 4) u = __ldcs(p.u + k);
+  }
+  while (k - lane < p.n) {  // warp-uniform bound
+    const bool active = k < p.n;
+    const long long kn = k + stride;
+    double xn = 0.0, yn = 0.0, un = 0.0;
+    Z zn = Z(0);
+    if (kn < p.n) {
+      xn = __ldcs(p.x + kn);
+      yn = __ldcs(p.y + kn);
+      zn = __ldcs(zs + kn);
+      if (ND >= 4) un = __ldcs(p.u + kn);
+    }
+    // ---- brackets ---------------------------------------------------------
+    bool ok = active && sane(x) && sane(y);
+    double c = x;
+    if (per) {
+      const double cn = norm_fast(x, ax.min, ax.period, ax.inv_period);
+      c = outside_period(ax, x) ? cn : x;
+    }
+    const RegBracket bx = per ? bracket_regular<true>(ax, c, ax.seam_c1_f32, ok)
+                              : bracket_regular<false>(ax, c, 0.0, ok);
+    const RegBracket by = bracket_f64(ay, s_y, s_ylut, y, ok);
+    RegBracket bz;
+    int kz = 0;
+    long long dz = 0;
+    if (ZI64) {
+      bracket_regular_i64(az, static_cast<long long>(z), kz, dz, ok);
+    } else {
+      ok = ok && sane(static_cast<double>(z));
+      bz = bracket_f64(az, s_z, s_zlut, static_cast<double>(z), ok);
+      kz = bz.k;
+    }
+    RegBracket bu;
+    if (ND >= 4) {
+      ok = ok && sane(u);
+      bu = bracket_f64(p.ax[3], s_u, s_ulut, u, ok);
+    }
+    // float results: x1 is normalised against the float-rounded x0
+    // (bivariate.hpp:78-89); the seam constant already is, any other cell
+    // needing it leaves the hot path
+    const float x0 = static_cast<float>(bx.c0);
+    const double x0d = static_cast<double>(x0);
+    const double hi0 = per ? __dadd_rn(x0d, ax.period) : 0.0;
+    if (per) ok = ok && (bx.k == ax.n - 1 || !(bx.c1 >= hi0 || bx.c1 < x0d));
+    // ---- gather (in flight while the weights are computed) ------------------
+    CellRef r;
+    r.sx = r.sy = r.sz = r.su = false;
+    r.cell = (static_cast<long long>(bx.k) * ay.n + by.k) * az.n + kz;
+    if (ND >= 4) r.cell = r.cell * p.ax[3].n + bu.k;
+    if (!ok) r.cell = 0;  // always a legal address
+    Corners<ND, float> q;
+    if constexpr (ND >= 4) {
+      geo_gather_group<ND, float>(p, r, q);
+    } else {
+      geo_gather_packed<ND, float>(p, r, q);
+    }
+    // ---- weights (Bilinear::evaluate, geometric/bivariate.hpp:110-132) -------
+    double px = x;
+    if (per) {
+      const bool out2 = x >= hi0 || x < x0d;
+      const double pn = norm_fast(x, x0d, ax.period, ax.inv_period);
+      px = out2 ? pn : x;
+    }
+    const float y0 = static_cast<float>(by.c0);
+    const float dx = static_cast<float>(bx.c1) - x0;
+    const float dy = static_cast<float>(by.c1) - y0;
+    const float t = __fdiv_rn(static_cast<float>(px) - x0, dx);
+    const float w = __fdiv_rn(static_cast<float>(y) - y0, dy);
+    const float omt = 1.0f - t;
+    const float omw = 1.0f - w;
+    constexpr int NU = Corners<ND, float>::NU;
+    float sp[2][NU];
+#pragma unroll
+    for (int cz = 0; cz < 2; ++cz) {
+#pragma unroll
+      for (int d = 0; d < NU; ++d) {
+        sp[cz][d] = omt * (omw * q.q[cz][d][0][0] + w * q.q[cz][d][0][1]) +
+                    t * (omw * q.q[cz][d][1][0] + w * q.q[cz][d][1][1]);
+      }
+    }
+    float along[NU];
+#pragma unroll
+    for (int d = 0; d < NU; ++d) {
+      along[d] = ZI64 ? axis_mix_i64(p.z_method, dz, az.istep, sp[0][d], sp[1][d])
+                      : axis_mix_f64(p.z_method, static_cast<double>(z), bz, sp[0][d], sp[1][d]);
+    }
+    float res = along[0];
+    if (ND >= 4) res = axis_mix_f64(p.u_method, u, bu, along[0], along[NU - 1]);
+    if (!ok && active) res = slow_point_nd<ND, ZI64>(p, x, y, z, u, k);  // rare
+    if (active) __stcs(out + k, res);
+    k = kn;
+    x = xn;
+    y = yn;
+    z = zn;
+    u = un;
+  }
+}
+
+// Eligibility of the N-D fast path (everything else runs the generic kernels).
+static bool axis_f64_fast(const DAxis& a, int max_irregular) {
+  if (!a.fast_ok || a.coord_i64 || a.n < 2 || a.period != 0.0) return false;
+  if (a.kind != 0 && (a.n > max_irregular || a.lut_bins <= 0 || a.lut_bins + 1 > 4 * max_irregular + 1)) {
+    return false;
+  }
+  return true;
+}
+
+static bool fastnd_eligible(const GeoParams& p) {
+  if (p.ndim < 3 || p.method != PYI_BILINEAR || p.packed == nullptr) return false;
+  if (p.dtype == PYI_F64 || p.dtype == PYI_I64 || p.dtype == PYI_U64) return false;  // float results
+  const DAxis& ax = p.ax[0];
+  if (!ax.fast_ok || ax.coord_i64 || ax.kind != 0 || ax.n < 2) return false;
+  if (ax.period != 0.0 && !(ax.period > 0.0 && ax.step < ax.period)) return false;
+  if (!axis_f64_fast(p.ax[1], kFastMaxIrregular)) return false;
+  const DAxis& az = p.ax[2];
+  if (az.coord_i64) {
+    if (!az.fast_ok || az.kind != 0) return false;
+  } else if (!axis_f64_fast(az, kNdMaxIrregular)) {
+    return false;
+  }
+  if (p.ndim >= 4 && !axis_f64_fast(p.ax[3], kNdMaxIrregular)) return false;
+  return true;
+}
+
+static cudaError_t launch_fastnd(const GeoParams& p, cudaStream_t stream) {
+  const int blocks = grid_for(p.n, kFastThreads, 3);
+  const bool zi64 = p.ax[2].coord_i64 != 0;
+  if (p.ndim == 3) {
+    if (zi64) bilinear_nd_fast_kernel<3, true><<<blocks, kFastThreads, 0, stream>>>(p);
+    else bilinear_nd_fast_kernel<3, false><<<blocks, kFastThreads, 0, stream>>>(p);
+  } else {
+    if (zi64) bilinear_nd_fast_kernel<4, true><<<blocks, kFastThreads, 0, stream>>>(p);
+    else bilinear_nd_fast_kernel<4, false><<<blocks, kFastThreads, 0, stream>>>(p);
+  }
+  g_launches.fetch_add(1);
+  return cudaGetLastError();
+}
+
+}  // namespace pyi

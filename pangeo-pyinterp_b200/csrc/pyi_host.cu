@@ -86,6 +86,18 @@ void fast_constants(const pyi_axis* a, pyi::DAxis& out) {
   const pyi_axis_desc& d = a->d;
   out.hi = out.seam_c1 = out.seam_c1_f32 = 0.0;
   out.fast_ok = 0;
+  out.ispan = 0;
+  if (d.coord_type == PYI_COORD_I64) {
+    // regular ascending int64 (temporal) axis without period: pyi_fastnd.cuh
+    const long long lim = 1LL << 61;
+    if (d.kind != PYI_AXIS_REGULAR || !d.is_ascending || d.size < 2 || d.period.i != 0) return;
+    if (d.step.i <= 0 || d.start.i <= -lim || d.start.i >= lim) return;
+    if (d.step.i >= lim / (d.size - 1)) return;
+    out.ispan = (d.size - 1) * d.step.i;
+    out.inv_step = 1.0 / static_cast<double>(d.step.i);
+    out.fast_ok = 1;
+    return;
+  }
   if (d.coord_type != PYI_COORD_F64 || !d.is_ascending || d.size < 2) return;
   const double lim = 1099511627776.0;  // 2^40, the kernel's sane() bound
   auto moderate = [&](double v) { return std::fabs(v) < lim; };

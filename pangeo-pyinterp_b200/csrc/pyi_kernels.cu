@@ -190,214 +190,11 @@ __device__ __forceinline__ R axis_interp(int method, Z x, Z x0, Z x1, R y0, R y1
 }
 
 // ---------------------------------------------------------------------------
-// K1-K3: geometric interpolation
+// K1-K3: geometric interpolation (pyi_geometric.cuh)
 // ---------------------------------------------------------------------------
-// One query point (pybind/geometric/bivariate.hpp:47-97, trivariate.hpp:47-123,
-// quadrivariate.hpp:50-148).  Returns -1 and the value, or the first axis (in
-// x, y, z, u order) that could not bracket the point.
-// Cell index and orientation of a bracket pair on one axis for the cell-packed
-// copy: a pair is either (k, k+1) / the periodic seam (n-1, 0) -> cell k, or
-// the same pair reversed (descending axes, axis.hpp:759-777) -> cell of the
-// lower index with the two corners exchanged.
-__device__ __forceinline__ int cell_of(const DAxis& a, int i0, int i1, bool& swapped) {
-  const bool fwd = (i1 == i0 + 1) || (a.periodic && i0 == a.n - 1 && i1 == 0);
-  swapped = !fwd;
-  return fwd ? i0 : i1;
-}
-
-template <int ND, int DT, typename R, bool ZI64, bool PACKED = false>
-__device__ __forceinline__ int geometric_eval(
-    const GeoParams& p, double x, double y,
-    typename std::conditional<ZI64, long long, double>::type z, double u, R& res) {
-  using Z = typename std::conditional<ZI64, long long, double>::type;
-  int ix[2], iy[2], iz[2] = {0, 0}, iu[2] = {0, 0};
-  if (!find_indexes<double>(p.ax[0], x, ix[0], ix[1])) return 0;
-  if (!find_indexes<double>(p.ax[1], y, iy[0], iy[1])) return 1;
-  if (ND >= 3) {
-    if (!find_indexes<Z>(p.ax[2], z, iz[0], iz[1])) return 2;
-  }
-  if (ND >= 4) {
-    if (!find_indexes<double>(p.ax[3], u, iu[0], iu[1])) return 3;
-  }
-  // corner coordinates in R; x1 and the query x are normalised against the
-  // R-rounded x0 promoted back to double (bivariate.hpp:78-89)
-  const R x0 = static_cast<R>(axis_coord_f64(p.ax[0], ix[0]));
-  const R x1 = static_cast<R>(
-      axis_normalize(p.ax[0], axis_coord_f64(p.ax[0], ix[1]), static_cast<double>(x0)));
-  const R y0 = static_cast<R>(axis_coord_f64(p.ax[1], iy[0]));
-  const R y1 = static_cast<R>(axis_coord_f64(p.ax[1], iy[1]));
-  const R px = static_cast<R>(axis_normalize(p.ax[0], x, static_cast<double>(x0)));
-  const R py = static_cast<R>(y);
-
-  const long long n1 = p.ax[1].n;
-  const long long n2 = ND >= 3 ? p.ax[2].n : 1;
-  const long long n3 = ND >= 4 ? p.ax[3].n : 1;
-  constexpr int NZ = ND >= 3 ? 2 : 1;
-  constexpr int NU = ND >= 4 ? 2 : 1;
-  // gather first (all loads in flight), then evaluate
-  R q[NZ][NU][2][2];
-  if (PACKED) {
-    // one aligned run of 2^ND values: corner (a, b, c, d) at ((a*2 + b)*NZ + c)*NU + d
-    bool sx, sy, sz = false, su = false;
-    long long cell = static_cast<long long>(cell_of(p.ax[0], ix[0], ix[1], sx)) * n1 +
-                     cell_of(p.ax[1], iy[0], iy[1], sy);
-    if (ND >= 3) cell = cell * n2 + cell_of(p.ax[2], iz[0], iz[1], sz);
-    if (ND >= 4) cell = cell * n3 + cell_of(p.ax[3], iu[0], iu[1], su);
-    constexpr int NV = 4 * NZ * NU;
-    constexpr int BYTES = NV * static_cast<int>(sizeof(R));
-    union {
-      unsigned long long w[BYTES / 8];
-      R v[NV];
-    } buf;
-    const char* src = reinterpret_cast<const char*>(static_cast<const R*>(p.packed) + cell * NV);
-    if (BYTES >= 32) {
-      // The memory system serves a fixed number of load REQUESTS per second for
-      // scattered lines (measured: profiles/r1_gather_probe.txt), so a 32-byte
-      // cell is read with ONE 256-bit load, not two 128-bit ones; .L2::64B keeps
-      // the DRAM fill at 64 bytes instead of the whole 128-byte line.
-#pragma unroll
-      for (int k = 0; k < BYTES / 32; ++k) {
-        asm volatile("ld.global.nc.L1::no_allocate.L2::64B.v4.u64 {%0,%1,%2,%3}, [%4];"
-                     : "=l"(buf.w[4 * k]), "=l"(buf.w[4 * k + 1]), "=l"(buf.w[4 * k + 2]),
-                       "=l"(buf.w[4 * k + 3])
-                     : "l"(src + 32 * k));
-      }
-    } else {  // 2-D float cells: 16 bytes
-      asm volatile("ld.global.nc.L1::no_allocate.v2.u64 {%0,%1}, [%2];"
-                   : "=l"(buf.w[0]), "=l"(buf.w[1])
-                   : "l"(src));
-    }
-#pragma unroll
-    for (int a = 0; a < 2; ++a) {
-#pragma unroll
-      for (int b = 0; b < 2; ++b) {
-#pragma unroll
-        for (int c = 0; c < NZ; ++c) {
-#pragma unroll
-          for (int d = 0; d < NU; ++d) q[c][d][a][b] = buf.v[((a * 2 + b) * NZ + c) * NU + d];
-        }
-      }
-    }
-    if (sx | sy | sz | su) {  // reversed pairs (descending axes): exchange corners
-#pragma unroll
-      for (int c = 0; c < NZ; ++c) {
-#pragma unroll
-        for (int d = 0; d < NU; ++d) {
-#pragma unroll
-          for (int b = 0; b < 2; ++b) {
-            const R t0 = q[c][d][0][b], t1 = q[c][d][1][b];
-            q[c][d][0][b] = sx ? t1 : t0;
-            q[c][d][1][b] = sx ? t0 : t1;
-          }
-#pragma unroll
-          for (int a = 0; a < 2; ++a) {
-            const R t0 = q[c][d][a][0], t1 = q[c][d][a][1];
-            q[c][d][a][0] = sy ? t1 : t0;
-            q[c][d][a][1] = sy ? t0 : t1;
-          }
-        }
-      }
-      if (ND >= 3) {
-#pragma unroll
-        for (int d = 0; d < NU; ++d) {
-#pragma unroll
-          for (int a = 0; a < 2; ++a) {
-#pragma unroll
-            for (int b = 0; b < 2; ++b) {
-              const R t0 = q[0][d][a][b], t1 = q[NZ - 1][d][a][b];
-              q[0][d][a][b] = sz ? t1 : t0;
-              q[NZ - 1][d][a][b] = sz ? t0 : t1;
-            }
-          }
-        }
-      }
-      if (ND >= 4) {
-#pragma unroll
-        for (int c = 0; c < NZ; ++c) {
-#pragma unroll
-          for (int a = 0; a < 2; ++a) {
-#pragma unroll
-            for (int b = 0; b < 2; ++b) {
-              const R t0 = q[c][0][a][b], t1 = q[c][NU - 1][a][b];
-              q[c][0][a][b] = su ? t1 : t0;
-              q[c][NU - 1][a][b] = su ? t0 : t1;
-            }
-          }
-        }
-      }
-    }
-  } else {
-#pragma unroll
-    for (int c = 0; c < NZ; ++c) {
-#pragma unroll
-      for (int d = 0; d < NU; ++d) {
-#pragma unroll
-        for (int a = 0; a < 2; ++a) {
-#pragma unroll
-          for (int b = 0; b < 2; ++b) {
-            long long off = ix[a] * n1 + iy[b];
-            if (ND >= 3) off = off * n2 + iz[c];
-            if (ND >= 4) off = off * n3 + iu[d];
-            q[c][d][a][b] = load_value<DT, R>(p.data, p.dtype, off);
-          }
-        }
-      }
-    }
-  }
-  R sp[NZ][NU];
-#pragma unroll
-  for (int c = 0; c < NZ; ++c) {
-#pragma unroll
-    for (int d = 0; d < NU; ++d) {
-      sp[c][d] = eval_spatial<R>(p.method, p.idw_exp, px, py, x0, y0, x1, y1, q[c][d][0][0],
-                                 q[c][d][0][1], q[c][d][1][0], q[c][d][1][1]);
-    }
-  }
-  if (ND == 2) {
-    res = sp[0][0];
-    return -1;
-  }
-  const Z z0 = axis_coord(p.ax[2], iz[0], Z{});
-  const Z z1 = axis_coord(p.ax[2], iz[1], Z{});
-  R along[NU];
-#pragma unroll
-  for (int d = 0; d < NU; ++d) {
-    along[d] = axis_interp<Z, R>(p.z_method, z, z0, z1, sp[0][d], sp[NZ - 1][d]);
-  }
-  if (ND == 3) {
-    res = along[0];
-    return -1;
-  }
-  const double u0 = axis_coord_f64(p.ax[3], iu[0]);
-  const double u1 = axis_coord_f64(p.ax[3], iu[1]);
-  res = axis_interp<double, R>(p.u_method, u, u0, u1, along[0], along[NU - 1]);
-  return -1;
-}
-
-template <int ND, int DT, typename R, bool ZI64, bool PACKED>
-__global__ void __launch_bounds__(kThreads)
-geometric_kernel(const __grid_constant__ GeoParams p) {
-  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
-  unsigned long long key = kNoOob;
-  R* __restrict__ out = static_cast<R*>(p.out);
-  for (long long k = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; k < p.n;
-       k += stride) {
-    using Z = typename std::conditional<ZI64, long long, double>::type;
-    R res = RT<R>::nan();
-    const Z z = ND >= 3 ? __ldg(static_cast<const Z*>(p.z) + k) : Z(0);
-    const double u = ND >= 4 ? __ldg(p.u + k) : 0.0;
-    const int bad = geometric_eval<ND, DT, R, ZI64, PACKED>(p, __ldg(p.x + k), __ldg(p.y + k), z, u, res);
-    if (bad >= 0) {
-      res = RT<R>::nan();
-      const unsigned long long kk = (static_cast<unsigned long long>(p.index_base + k) << 2) | bad;
-      key = kk < key ? kk : key;
-    }
-    __stcs(out + k, res);
-  }
-  if (p.bounds_error && key != kNoOob) {
-    atomicMin(p.oob_key, key);
-  }
-}
+}  // namespace pyi
+#include "pyi_geometric.cuh"
+namespace pyi {
 
 template <int ND, bool ZI64>
 static cudaError_t launch_geometric_nd(const GeoParams& p, cudaStream_t stream) {
@@ -405,10 +202,19 @@ static cudaError_t launch_geometric_nd(const GeoParams& p, cudaStream_t stream) 
   const bool r64 = p.dtype == PYI_F64 || p.dtype == PYI_I64 || p.dtype == PYI_U64;
   if (p.packed != nullptr) {
     // cell-packed copy (already in the result type): one aligned run per point
+    // cells of 64 / 128 bytes are read by lane pairs / quads (one request per cell)
     if (r64) {
-      geometric_kernel<ND, -1, double, ZI64, true><<<blocks, kThreads, 0, stream>>>(p);
+      if constexpr (ND >= 3) {
+        geometric_group_kernel<ND, double, ZI64><<<blocks, kThreads, 0, stream>>>(p);
+      } else {
+        geometric_kernel<ND, -1, double, ZI64, true><<<blocks, kThreads, 0, stream>>>(p);
+      }
     } else {
-      geometric_kernel<ND, -1, float, ZI64, true><<<blocks, kThreads, 0, stream>>>(p);
+      if constexpr (ND >= 4) {
+        geometric_group_kernel<ND, float, ZI64><<<blocks, kThreads, 0, stream>>>(p);
+      } else {
+        geometric_kernel<ND, -1, float, ZI64, true><<<blocks, kThreads, 0, stream>>>(p);
+      }
     }
   } else if (p.dtype == PYI_F64) {
     geometric_kernel<ND, PYI_F64, double, ZI64, false><<<blocks, kThreads, 0, stream>>>(p);
@@ -426,10 +232,14 @@ static cudaError_t launch_geometric_nd(const GeoParams& p, cudaStream_t stream) 
 // K1 fast path (pyi_fast2d.cuh)
 static bool fast2d_eligible(const GeoParams& p);
 static cudaError_t launch_fast2d(const GeoParams& p, cudaStream_t stream);
+// K2 / K3 fast path (pyi_fastnd.cuh)
+static bool fastnd_eligible(const GeoParams& p);
+static cudaError_t launch_fastnd(const GeoParams& p, cudaStream_t stream);
 
 cudaError_t launch_geometric(const GeoParams& p, cudaStream_t stream) {
   if (p.n <= 0) return cudaSuccess;
   if (fast2d_eligible(p)) return launch_fast2d(p, stream);
+  if (fastnd_eligible(p)) return launch_fastnd(p, stream);
   const bool zi64 = p.ndim >= 3 && p.ax[2].coord_i64;
   switch (p.ndim) {
     case 2: return launch_geometric_nd<2, false>(p, stream);
@@ -626,4 +436,5 @@ cudaError_t launch_pack_cells(const void* data, int dtype, int ndim, const int* 
 }  // namespace pyi
 
 #include "pyi_fast2d.cuh"
+#include "pyi_fastnd.cuh"
 #include "pyi_windowed.cuh"
