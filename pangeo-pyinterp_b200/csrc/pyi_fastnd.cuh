@@ -229,7 +229,21 @@ bilinear_nd_fast_kernel(const __grid_constant__ GeoParams p) {
     }
     float res = along[0];
     if (ND >= 4) res = axis_mix_f64(p.u_method, u, bu, along[0], along[NU - 1]);
-    if (!ok && active) res = slow_point_nd<ND, ZI64>(p, x, y, z, u, k);  // rare
+    if (!ok && active) {
+      // a finite coordinate beyond the ends of an axis that does not wrap (or
+      // a NaT / out-of-range time) cannot be bracketed: NaN; with bounds_error,
+      // and for anything else, the generic code decides
+      bool far = sane(x) && sane(y) && (beyond_ends(ax, c) || beyond_ends(ay, y));
+      if (ZI64) {
+        const long long num = static_cast<long long>(static_cast<unsigned long long>(z) -
+                                                     static_cast<unsigned long long>(az.istart));
+        far = far || num < 0 || num > az.ispan;
+      } else {
+        far = far || (sane(static_cast<double>(z)) && beyond_ends(az, static_cast<double>(z)));
+      }
+      if (ND >= 4) far = far || (sane(u) && beyond_ends(p.ax[3], u));
+      res = (far && !p.bounds_error) ? CUDART_NAN_F : slow_point_nd<ND, ZI64>(p, x, y, z, u, k);
+    }
     if (active) __stcs(out + k, res);
     k = kn;
     x = xn;

@@ -106,6 +106,12 @@ void fast_constants(const pyi_axis* a, pyi::DAxis& out) {
   if (d.kind == PYI_AXIS_REGULAR) {
     ok = ok && spacing_ok(d.step.f);
     const volatile double last = d.start.f + static_cast<double>(d.size - 1) * d.step.f;
+    // the kernels resolve "beyond the ends" without the generic code: that
+    // needs min / max to be the end nodes and the nearest-node rounding of the
+    // last node to be exact (container.hpp:553-563 is monotone in c)
+    const volatile double q_last = (last - d.start.f) * d.inv_step;
+    ok = ok && d.min_value.f == d.start.f && d.max_value.f == last &&
+         std::round(q_last) == static_cast<double>(d.size - 1);
     if (d.is_periodic && d.period.f > 0.0) {
       out.seam_c1 = host_normalize(d.start.f, last, d.period.f);
       const double last32 = static_cast<double>(static_cast<float>(last));
@@ -114,6 +120,7 @@ void fast_constants(const pyi_axis* a, pyi::DAxis& out) {
     }
   } else {
     for (size_t k = 0; ok && k + 1 < a->pf.size(); ++k) ok = spacing_ok(a->pf[k + 1] - a->pf[k]);
+    ok = ok && d.min_value.f == a->pf.front() && d.max_value.f == a->pf.back();
   }
   out.hi = d.min_value.f + d.period.f;
   out.fast_ok = ok ? 1 : 0;
