@@ -285,6 +285,9 @@ def main():
         torch.empty(case["grid"].shape, dtype=torch.from_numpy(case["grid"][:1]).dtype, device=dev)
     bcast_ms = None
     if world > 1:
+        # communicator set-up is a one-off of the process group, not of the grid
+        warm = torch.zeros(1, device=dev)
+        dist.all_reduce(warm)
         torch.cuda.synchronize()
         t0 = time.perf_counter()
         pyi.dist.broadcast_grid_array(t_arr)
