@@ -12,20 +12,14 @@
 //       cache_loader.hpp, bivariate/bicubic.hpp, univariate/cspline.hpp
 //   find_indexes_kernel / find_index_kernel   K5: Axis::find_indexes / find_index
 //   pack_cells2d_kernel             one-off cell packing of a 2-D grid
-#include <atomic>
-#include <cstdlib>
-
-#include "../../include/pyinterp_b200.h"
-#include "pyi_kernels.cuh"
+#include "pyi_common.cuh"
 
 namespace pyi {
 
-static std::atomic<long long> g_launches{0};
+std::atomic<long long> g_launches{0};
 long long launch_count() { return g_launches.load(); }
 
-constexpr int kThreads = 256;
-
-static int sm_count() {
+int sm_count() {
   static int n = 0;
   if (n == 0) {
     int dev = 0;
@@ -36,9 +30,7 @@ static int sm_count() {
   return n;
 }
 
-// Grid sized as a multiple of the SM count (148 on B200): `waves` resident
-// blocks per SM, capped by the work available.
-static int grid_for(long long n, int per_block, int waves) {
+int grid_for(long long n, int per_block, int waves) {
   const long long need = (n + per_block - 1) / per_block;
   const long long cap = static_cast<long long>(sm_count()) * waves;
   return static_cast<int>(need < 1 ? 1 : (need < cap ? need : cap));
@@ -65,25 +57,6 @@ struct RT<float> {
   static __device__ __forceinline__ float pi() { return 3.141592653589793238462643383279502884f; }
   static __device__ __forceinline__ float nan() { return CUDART_NAN_F; }
 };
-
-// Grid::value (pybind/grid.hpp:340-345) cast to the result type
-// (bivariate.hpp:72-75).  DT >= 0: compile-time dtype; DT < 0: run-time.
-template <int DT, typename R>
-__device__ __forceinline__ R load_value(const void* data, int dtype, long long off) {
-  const int dt = DT >= 0 ? DT : dtype;
-  switch (dt) {
-    case PYI_I8: return static_cast<R>(__ldg(static_cast<const signed char*>(data) + off));
-    case PYI_U8: return static_cast<R>(__ldg(static_cast<const unsigned char*>(data) + off));
-    case PYI_I16: return static_cast<R>(__ldg(static_cast<const short*>(data) + off));
-    case PYI_U16: return static_cast<R>(__ldg(static_cast<const unsigned short*>(data) + off));
-    case PYI_I32: return static_cast<R>(__ldg(static_cast<const int*>(data) + off));
-    case PYI_U32: return static_cast<R>(__ldg(static_cast<const unsigned int*>(data) + off));
-    case PYI_I64: return static_cast<R>(__ldg(static_cast<const long long*>(data) + off));
-    case PYI_U64: return static_cast<R>(__ldg(static_cast<const unsigned long long*>(data) + off));
-    case PYI_F32: return static_cast<R>(__ldg(static_cast<const float*>(data) + off));
-    default: return static_cast<R>(__ldg(static_cast<const double*>(data) + off));
-  }
-}
 
 // ---------------------------------------------------------------------------
 // geometric evaluators (math/interpolate/geometric/bivariate.hpp)
@@ -437,4 +410,3 @@ cudaError_t launch_pack_cells(const void* data, int dtype, int ndim, const int* 
 
 #include "pyi_fast2d.cuh"
 #include "pyi_fastnd.cuh"
-#include "pyi_windowed.cuh"

@@ -345,7 +345,8 @@ windowed2d_kernel(const __grid_constant__ WinParams p) {
     double res;
     const int bad = windowed_point<MAXW>(p, __ldg(p.x + k), __ldg(p.y + k), res);
     if (bad >= 0) {
-      const unsigned long long kk = (static_cast<unsigned long long>(k) << 2) | bad;
+      const unsigned long long kk =
+          (static_cast<unsigned long long>(p.index_base + k) << 2) | bad;
       key = kk < key ? kk : key;
     }
     __stcs(out + k, static_cast<R>(res));
@@ -368,8 +369,13 @@ static cudaError_t launch_windowed_w(const WinParams& p, cudaStream_t stream) {
   return cudaGetLastError();
 }
 
+static cudaError_t launch_bicubic6_fast(const WinParams& p, cudaStream_t stream);  // pyi_fastwin.cuh
+
 cudaError_t launch_windowed2d(const WinParams& p, cudaStream_t stream) {
   if (p.n <= 0) return cudaSuccess;
+  if (p.method == PYI_W_BICUBIC && p.half_x == 3 && p.half_y == 3 && !force_generic()) {
+    return launch_bicubic6_fast(p, stream);
+  }
   const int w = 2 * (p.half_x > p.half_y ? p.half_x : p.half_y);
   if (w <= 6) return launch_windowed_w<6>(p, stream);
   if (w <= 12) return launch_windowed_w<12>(p, stream);

@@ -438,3 +438,88 @@ def test_grid_array_is_borrowed_and_refreshed(pyi):
     arr[2:4, 17:19] = np.nan
     assert np.isnan(pyi.bivariate(grid, x, y)[0])
     assert np.isnan(pyi.bivariate(grid, x, y, "bicubic")[0])
+
+
+def _bicubic_both(pyi, grid, x, y, **kw):
+    """6 x 6 bicubic through the fast kernel and through the generic one."""
+    import os
+    fast = pyi.bivariate(grid, x, y, "bicubic", **kw)
+    os.environ["PYINTERP_B200_GENERIC"] = "1"
+    try:
+        generic = pyi.bivariate(grid, x, y, "bicubic", **kw)
+    finally:
+        del os.environ["PYINTERP_B200_GENERIC"]
+    return fast, generic
+
+
+@pytest.mark.parametrize("boundary", ["undef", "shrink"])
+def test_bicubic6_fast_path_full_grid(pyi, orc_best, boundary):
+    """The register-resident 6 x 6 bicubic kernel (pyi_fastwin.cuh) on the 0.25
+    degree grid: bit-identical to the generic kernel and to the oracle."""
+    s = pyi.synthetic
+    lon, lat = s.lon_axis_values(), s.lat_axis_values()
+    g = s.field(lon, lat)
+    grid = pyi.Grid(pyi.Axis(lon, period=360.0), pyi.Axis(lat), g)
+    x, y = s.queries(400_000, 1002)
+    rng = np.random.default_rng(8)
+    x[::53] = rng.choice(lon, x[::53].size)          # on a node: bracket (k-1, k)
+    y[::59] = rng.choice(lat, y[::59].size)
+    x[1::1013] = np.nan
+    x[2::1017] = np.inf
+    y[3::1019] = 1e300
+    fast, generic = _bicubic_both(pyi, grid, x, y, boundary_mode=boundary)
+    assert np.array_equal(fast, generic, equal_nan=True)
+    caxes = [orc_best.axis(lon, period=360.0), orc_best.axis(lat)]
+    want, _ = orc_best.windowed2d(caxes, g, x, y, boundary=boundary, num_threads=0, stateless=True)
+    assert np.array_equal(fast, want, equal_nan=True)
+    assert np.isfinite(fast).mean() > 0.95
+
+
+@pytest.mark.parametrize("dtype", ["float64", "float32", "int32", "uint8"])
+def test_bicubic6_fast_path_awkward_values(pyi, orc_best, dtype):
+    """Values for which the short division of the fast path is not proven
+    (huge, tiny, subnormal, infinite, NaN) take the generic code; zeros and
+    constant patches stay on the fast path.  Irregular and non-periodic axes."""
+    rng = np.random.default_rng(12)
+    lon = np.sort(rng.uniform(0, 360, 200))
+    lat = np.degrees(np.arcsin(np.linspace(-0.999, 0.999, 90)))
+    g = rng.normal(size=(200, 90)) * 30
+    if dtype == "float64":
+        g[rng.random(g.shape) < 0.01] = 1e250
+        g[rng.random(g.shape) < 0.01] = 1e-305
+        g[rng.random(g.shape) < 0.01] = 5e-324
+        g[rng.random(g.shape) < 0.005] = np.inf
+        g[rng.random(g.shape) < 0.005] = np.nan
+    g[rng.random(g.shape) < 0.2] = 0.0
+    g[40:60, 20:40] = 7.0
+    g = g.astype(dtype)
+    for kw in (dict(period=360.0), {}):
+        grid = pyi.Grid(pyi.Axis(lon, **kw), pyi.Axis(lat), g)
+        x = rng.uniform(-200, 500, 100_000)
+        y = rng.uniform(-91, 91, 100_000)
+        fast, generic = _bicubic_both(pyi, grid, x, y)
+        assert np.array_equal(fast, generic, equal_nan=True)
+        caxes = [orc_best.axis(lon, **kw), orc_best.axis(lat)]
+        want, _ = orc_best.windowed2d(caxes, g, x, y, num_threads=0, stateless=True)
+        assert np.array_equal(fast, want, equal_nan=True)
+
+
+def test_windowed2d_bounds_error_in_late_chunk(pyi, orc_best):
+    """Host buffers are processed in chunks; the reported index is global."""
+    s = pyi.synthetic
+    lon, lat = s.lon_axis_values(144), s.lat_axis_values(72)
+    g = s.field(lon, lat)
+    grid = pyi.Grid(pyi.Axis(lon, period=360.0), pyi.Axis(lat), g)
+    n = 20_000_000
+    x = np.full(n, 10.0)
+    y = np.full(n, 1.0)
+    y[n - 5] = 95.0
+    for method, half in (("bicubic", 3), ("bicubic", 2), ("bilinear", 3)):
+        cfg = getattr(pyi.windowed.Bivariate, method)().with_half_window_size_x(half) \
+            .with_half_window_size_y(half).with_bounds_error(True)
+        with pytest.raises(IndexError) as ei:
+            pyi.core.bivariate(grid, x, y, cfg)
+        assert str(ei.value).startswith("95 is out of bounds for axis y"), str(ei.value)
+    import torch
+    with pytest.raises(IndexError):
+        pyi.bivariate(grid, torch.from_numpy(x).cuda(), torch.from_numpy(y).cuda(), "bicubic", bounds_error=True)
