@@ -63,6 +63,22 @@ typedef enum pyi_geometric_method { PYI_BILINEAR = 0, PYI_IDW = 1, PYI_NEAREST =
 typedef enum pyi_axis_method { PYI_AXIS_LINEAR = 0, PYI_AXIS_NEAREST = 1 } pyi_axis_method;
 /* windowed 2-D evaluators on the path: bivariate/bicubic.hpp, bivariate/bilinear.hpp */
 typedef enum pyi_windowed_method { PYI_W_BICUBIC = 0, PYI_W_BILINEAR = 1 } pyi_windowed_method;
+/* every fitting model of the windowed path (config/windowed.hpp:21-56,
+ * math/interpolate/factory.hpp:27-36,77-80): the two bivariate evaluators keep
+ * the values of pyi_windowed_method, the others are the univariate models the
+ * reference applies along y then along x (bivariate/spline.hpp:62-84). */
+typedef enum pyi_spatial_method {
+  PYI_S_BICUBIC = 0,
+  PYI_S_BILINEAR = 1,
+  PYI_S_AKIMA = 2,
+  PYI_S_AKIMA_PERIODIC = 3,
+  PYI_S_C_SPLINE = 4,
+  PYI_S_C_SPLINE_NOT_A_KNOT = 5,
+  PYI_S_C_SPLINE_PERIODIC = 6,
+  PYI_S_LINEAR = 7,
+  PYI_S_STEFFEN = 8,
+  PYI_S_POLYNOMIAL = 9
+} pyi_spatial_method;
 /* the two boundary modes the reference exposes, config/windowed.hpp:88-98 */
 typedef enum pyi_boundary { PYI_BOUNDARY_UNDEF = 0, PYI_BOUNDARY_SHRINK = 1 } pyi_boundary;
 /* where caller buffers live */
@@ -126,6 +142,22 @@ typedef struct pyi_windowed_config {
   int32_t bounds_error;
   int32_t num_threads;
 } pyi_windowed_config;
+
+/* config/windowed.hpp Univariate / Bivariate / Trivariate / Quadrivariate in
+ * one POD: spatial model and window, third / fourth axis methods
+ * (config/windowed.hpp:560-640), and the value-or-derivative switch of the 1-D
+ * drivers (pybind/windowed/univariate.hpp:47-120). */
+typedef struct pyi_windowed_nd_config {
+  int32_t method;       /* pyi_spatial_method; 1-D grids: univariate models only */
+  int32_t half_x;       /* half_window_size (1-D) / half_window_size_x */
+  int32_t half_y;
+  int32_t boundary;     /* pyi_boundary */
+  int32_t bounds_error;
+  int32_t num_threads;
+  int32_t z_method;     /* pyi_axis_method (3-D / 4-D) */
+  int32_t u_method;     /* pyi_axis_method (4-D) */
+  int32_t derivative;   /* 1-D only: 0 value, 1 first derivative */
+} pyi_windowed_nd_config;
 
 typedef struct pyi_axis pyi_axis; /* opaque */
 typedef struct pyi_grid pyi_grid; /* opaque */
@@ -202,6 +234,17 @@ int pyi_geometric(const pyi_grid *grid, const pyi_geometric_config *cfg,
 int pyi_windowed2d(const pyi_grid *grid, const pyi_windowed_config *cfg,
                    int64_t n, const double *x, const double *y, void *out,
                    int mem, int64_t *oob_index, int *oob_axis, void *stream);
+
+/* Windowed interpolation on 1-D .. 4-D grids with every fitting model:
+ * windowed::pybind::univariate / univariate_derivative / bivariate /
+ * trivariate / quadrivariate (pybind/windowed/univariate.hpp:122-190,
+ * bivariate.hpp:86-115, trivariate.hpp:136-165, quadrivariate.hpp:162-197).
+ * y is unused for 1-D grids, z for < 3-D, u for < 4-D.  z is int64 when axis 2
+ * is temporal.  Errors and memory spaces as pyi_windowed2d. */
+int pyi_windowed(const pyi_grid *grid, const pyi_windowed_nd_config *cfg,
+                 int64_t n, const double *x, const double *y, const void *z,
+                 const double *u, void *out, int mem, int64_t *oob_index,
+                 int *oob_axis, void *stream);
 
 /* Reference text "{coord} is out of bounds for axis {x|y|z|u} [{min}, ...,
  * {max}]" (pybind/grid.hpp:367-370). `coord` points to a double or an int64

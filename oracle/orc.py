@@ -21,6 +21,7 @@ if _ROOT not in sys.path:
     sys.path.insert(0, _ROOT)
 _abi = importlib.import_module("pangeo-pyinterp_b200._abi")
 AxisDesc, GeometricConfig, WindowedConfig = _abi.AxisDesc, _abi.GeometricConfig, _abi.WindowedConfig
+WindowedNdConfig = _abi.WindowedNdConfig
 
 PATHS = {
     "port": os.path.join(_HERE, "liboracle.so"),
@@ -46,6 +47,10 @@ _SIG = {
     "orc_windowed2d": (C.c_int, [C.POINTER(_P), C.c_int, _P, C.POINTER(WindowedConfig), C.c_int,
                                  C.c_int64, _P, _P, _P, C.POINTER(C.c_int64), C.POINTER(C.c_int),
                                  C.c_char_p, C.c_size_t]),
+    "orc_windowed_nd": (C.c_int, [C.c_int, C.POINTER(_P), C.c_int, _P, C.POINTER(WindowedNdConfig), C.c_int,
+                                  C.c_int64, _P, _P, _P, _P, _P, C.POINTER(C.c_int64), C.POINTER(C.c_int),
+                                  C.c_char_p, C.c_size_t]),
+    "orc_univariate": (C.c_double, [C.c_int, _P, _P, C.c_int, C.c_double, C.c_int]),
     "orc_eval2d_f64": (C.c_double, [C.c_int, C.c_int, C.c_int] + [C.c_double] * 10),
     "orc_eval2d_f32": (C.c_float, [C.c_int, C.c_int, C.c_int] + [C.c_float] * 10),
     "orc_axis_interp_f64": (C.c_double, [C.c_int] + [C.c_double] * 5),
@@ -198,6 +203,38 @@ class Oracle:
             return out, (oi.value, oa.value, msg.value.decode())
         assert st == 0, st
         return out, None
+
+    def windowed_nd(self, axes, data, x, y=None, z=None, u=None, method="bicubic", half_x=3, half_y=3,
+                    boundary="undef", bounds_error=False, num_threads=1, stateless=True, z_method=0,
+                    u_method=0, derivative=False):
+        """windowed::pybind::{uni,bi,tri,quadri}variate with any fitting model."""
+        data = np.ascontiguousarray(data)
+        nd = data.ndim
+        assert nd == len(axes)
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        y = None if y is None else np.ascontiguousarray(y, dtype=np.float64)
+        if z is not None:
+            z = np.ascontiguousarray(z, dtype=np.int64 if axes[2].is_i64 else np.float64)
+        u = None if u is None else np.ascontiguousarray(u, dtype=np.float64)
+        out = np.empty(x.size, dtype=_abi.result_dtype(data.dtype.name))
+        m = _abi.SPATIAL_METHODS[method] if isinstance(method, str) else int(method)
+        cfg = WindowedNdConfig(m, half_x, half_y, BOUNDARY[boundary], int(bounds_error), num_threads,
+                               z_method, u_method, int(derivative))
+        oi, oa = C.c_int64(-1), C.c_int(-1)
+        msg = C.create_string_buffer(512)
+        st = self.lib.orc_windowed_nd(nd, self._axes(axes), _abi.DTYPES[data.dtype.name], _ptr(data),
+                                      C.byref(cfg), int(stateless), x.size, _ptr(x), _ptr(y), _ptr(z),
+                                      _ptr(u), _ptr(out), C.byref(oi), C.byref(oa), msg, 512)
+        if st == _abi.PYI_OOB:
+            return out, (oi.value, oa.value, msg.value.decode())
+        assert st == 0, st
+        return out, None
+
+    def univariate(self, method, xa, ya, x, derivative=False):
+        xa = np.ascontiguousarray(xa, dtype=np.float64)
+        ya = np.ascontiguousarray(ya, dtype=np.float64)
+        m = _abi.SPATIAL_METHODS[method] if isinstance(method, str) else int(method)
+        return self.lib.orc_univariate(m, _ptr(xa), _ptr(ya), xa.size, x, int(derivative))
 
     def window_eval(self, method, xa, ya, za, x, y):
         xa = np.ascontiguousarray(xa, dtype=np.float64)

@@ -89,6 +89,22 @@ int orc_windowed2d(const orc_axis *const *axes, int dtype, const void *data,
                    int64_t *oob_index, int *oob_axis, char *msg,
                    size_t msglen);
 
+/* windowed::pybind::univariate / univariate_derivative / bivariate /
+ * trivariate / quadrivariate with every fitting model
+ * (pybind/windowed/*.hpp, math/interpolate/factory.hpp).  Reference build only
+ * (liboracle_ref.so); the plain-C library returns PYI_BAD_ARG for the models
+ * it does not restate. */
+int orc_windowed_nd(int ndim, const orc_axis *const *axes, int dtype,
+                    const void *data, const pyi_windowed_nd_config *cfg,
+                    int stateless, int64_t n, const double *x, const double *y,
+                    const void *z, const double *u, void *out,
+                    int64_t *oob_index, int *oob_axis, char *msg,
+                    size_t msglen);
+/* One univariate model on explicit nodes: value or derivative at x
+ * (math/interpolate/univariate/*.hpp). method: pyi_spatial_method >= 2. */
+double orc_univariate(int method, const double *xa, const double *ya, int n,
+                      double x, int derivative);
+
 /* ---- scalar probes used by the golden-vector tests ------------------------ */
 /* geometric evaluators (math/interpolate/geometric/bivariate.hpp).
  * cartesian != 0: the Cartesian point type the reference unit tests use;

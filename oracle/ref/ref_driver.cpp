@@ -820,3 +820,367 @@ extern "C" double orc_cspline(const double* xa, const double* ya, int n,
   ref::Vector<double> vy = Eigen::Map<const ref::Vector<double>>(ya, n);
   return derivative ? s.derivative(vx, vy, x) : s(vx, vy, x);
 }
+
+// ---------------------------------------------------------------------------
+// windowed N-D driver (1-D .. 4-D, every fitting model): the reference's
+// InterpolationCache, factory(), Univariate / BivariateBase interpolators,
+// linear() and nearest() used unmodified; restated over a duck grid (GCC 13):
+//   - load_cache_generic                 math/interpolate/cache_loader.hpp:46-172
+//   - univariate_single / _derivative    pybind/windowed/univariate.hpp:47-120
+//   - bivariate_single                   pybind/windowed/bivariate.hpp:46-76
+//   - trivariate_single                  pybind/windowed/trivariate.hpp:66-123
+//   - quadrivariate_single               pybind/windowed/quadrivariate.hpp:50-148
+// ---------------------------------------------------------------------------
+#include "pyinterp/math/interpolate/factory.hpp"
+
+namespace {
+
+// Grid::value (pybind/grid.hpp:340-345) cast to the cache's double
+// (cache_loader.hpp:150-153), any dtype.
+auto fetch_f64(const void* data, int dtype, int64_t off) -> double {
+  switch (dtype) {
+    case PYI_I8: return static_cast<double>(static_cast<const int8_t*>(data)[off]);
+    case PYI_U8: return static_cast<double>(static_cast<const uint8_t*>(data)[off]);
+    case PYI_I16: return static_cast<double>(static_cast<const int16_t*>(data)[off]);
+    case PYI_U16: return static_cast<double>(static_cast<const uint16_t*>(data)[off]);
+    case PYI_I32: return static_cast<double>(static_cast<const int32_t*>(data)[off]);
+    case PYI_U32: return static_cast<double>(static_cast<const uint32_t*>(data)[off]);
+    case PYI_I64: return static_cast<double>(static_cast<const int64_t*>(data)[off]);
+    case PYI_U64: return static_cast<double>(static_cast<const uint64_t*>(data)[off]);
+    case PYI_F32: return static_cast<double>(static_cast<const float*>(data)[off]);
+    default: return static_cast<const double*>(data)[off];
+  }
+}
+
+template <typename ZT>
+struct AnyGrid {
+  const ref::math::Axis<double>* ax{};
+  const ref::math::Axis<double>* ay{};
+  const ref::math::Axis<ZT>* az{};
+  const ref::math::Axis<double>* au{};
+  const void* data{};
+  int dtype{};
+  int64_t n1{1}, n2{1}, n3{1};
+};
+
+template <typename A, typename C>
+auto bounds_text(const A& a, int axis, const C& c) -> std::string {
+  return std::format("{} is out of bounds for axis {} [{}, ..., {}]",
+                     a.coordinate_repr(c), kLabels[axis],
+                     a.coordinate_repr(a.min_value()),
+                     a.coordinate_repr(a.max_value()));
+}
+
+template <typename ZT, size_t ND>
+struct CacheOf;
+template <typename ZT>
+struct CacheOf<ZT, 1> {
+  using type = itp::InterpolationCache<double, double>;
+};
+template <typename ZT>
+struct CacheOf<ZT, 2> {
+  using type = itp::InterpolationCache<double, double, double>;
+};
+template <typename ZT>
+struct CacheOf<ZT, 3> {
+  using type = itp::InterpolationCache<double, double, double, ZT>;
+};
+template <typename ZT>
+struct CacheOf<ZT, 4> {
+  using type = itp::InterpolationCache<double, double, double, ZT, double>;
+};
+
+using Window = std::pair<std::vector<int64_t>, std::pair<int64_t, int64_t>>;
+
+// cache_loader.hpp:46-172
+template <typename ZT, size_t ND>
+auto load_window_nd(const AnyGrid<ZT>& g, double xq, double yq, ZT zq, double uq,
+                    ref::math::axis::Boundary boundary, bool bounds_error,
+                    typename CacheOf<ZT, ND>::type& cache,
+                    std::optional<std::string>& err, int& err_axis) -> bool {
+  std::array<Window, ND> w;
+  auto find = [&](auto dim, const auto& axis, const auto& val) -> bool {
+    constexpr size_t I = decltype(dim)::value;
+    auto r = axis.find_indexes(val, cache.template half_window<I>(), boundary);
+    if (!r) {
+      if (bounds_error && !axis.contains(val)) {
+        err = bounds_text(axis, static_cast<int>(I), val);
+        err_axis = static_cast<int>(I);
+      }
+      return false;
+    }
+    w[I] = std::move(*r);
+    return true;
+  };
+  if (!find(std::integral_constant<size_t, 0>{}, *g.ax, xq)) return false;
+  if constexpr (ND >= 2) {
+    if (!find(std::integral_constant<size_t, 1>{}, *g.ay, yq)) return false;
+  }
+  if constexpr (ND >= 3) {
+    if (!find(std::integral_constant<size_t, 2>{}, *g.az, zq)) return false;
+  }
+  if constexpr (ND >= 4) {
+    if (!find(std::integral_constant<size_t, 3>{}, *g.au, uq)) return false;
+  }
+  std::array<size_t, ND> npts;
+  bool resized = false;
+  for (size_t i = 0; i < ND; ++i) {
+    npts[i] = w[i].first.size();
+    resized = resized || npts[i] != cache.points_per_dim(i);
+  }
+  if (resized) cache.resize(std::move(npts));
+  const double period = g.ax->is_periodic() ? g.ax->period().value() : 0.0;
+  for (size_t k = 0; k < w[0].first.size(); ++k) {
+    auto raw = (*g.ax)(w[0].first[k]);
+    if (period != 0.0) raw = ref::math::normalize_period_half(raw, xq, period);
+    cache.template set_coord<0>(k, raw);
+  }
+  if constexpr (ND >= 2) {
+    for (size_t k = 0; k < w[1].first.size(); ++k)
+      cache.template set_coord<1>(k, (*g.ay)(w[1].first[k]));
+  }
+  if constexpr (ND >= 3) {
+    for (size_t k = 0; k < w[2].first.size(); ++k)
+      cache.template set_coord<2>(k, (*g.az)(w[2].first[k]));
+  }
+  if constexpr (ND >= 4) {
+    for (size_t k = 0; k < w[3].first.size(); ++k)
+      cache.template set_coord<3>(k, (*g.au)(w[3].first[k]));
+  }
+  auto& flat = cache.values_flat();
+  size_t pos = 0;
+  const std::vector<int64_t> one{0};
+  const auto& wy = ND >= 2 ? w[ND >= 2 ? 1 : 0].first : one;
+  const auto& wz = ND >= 3 ? w[ND >= 3 ? 2 : 0].first : one;
+  const auto& wu = ND >= 4 ? w[ND >= 4 ? 3 : 0].first : one;
+  for (int64_t i : w[0].first)
+    for (int64_t j : wy)
+      for (int64_t k : wz)
+        for (int64_t l : wu)
+          flat[pos++] = fetch_f64(g.data, g.dtype, ((i * g.n1 + j) * g.n2 + k) * g.n3 + l);
+  std::array<std::pair<int64_t, int64_t>, ND> brackets;
+  for (size_t i = 0; i < ND; ++i) brackets[i] = w[i].second;
+  cache.finalize(brackets);
+  return cache.is_valid();
+}
+
+auto to_univariate_method(int m) -> itp::univariate::Method {
+  using M = itp::univariate::Method;
+  switch (m) {
+    case PYI_S_AKIMA: return M::kAkima;
+    case PYI_S_AKIMA_PERIODIC: return M::kAkimaPeriodic;
+    case PYI_S_C_SPLINE: return M::kCSpline;
+    case PYI_S_C_SPLINE_NOT_A_KNOT: return M::kCSplineNotAKnot;
+    case PYI_S_C_SPLINE_PERIODIC: return M::kCSplinePeriodic;
+    case PYI_S_LINEAR: return M::kLinear;
+    case PYI_S_STEFFEN: return M::kSteffen;
+    default: return M::kPolynomial;
+  }
+}
+
+// config::windowed::Spatial::factory (config/windowed.hpp:118-123)
+auto make_spatial(int method) -> std::unique_ptr<itp::BivariateBase<double>> {
+  if (method == PYI_S_BICUBIC) return itp::factory<double>(itp::bivariate::Method::kBicubic);
+  if (method == PYI_S_BILINEAR) return itp::factory<double>(itp::bivariate::Method::kBilinear);
+  return itp::factory<double>(to_univariate_method(method));
+}
+
+template <typename ZT, size_t ND, typename R>
+struct PointState {
+  using Cache = typename CacheOf<ZT, ND>::type;
+  Cache cache;
+  std::unique_ptr<itp::Univariate<double>> uni;
+  std::array<std::unique_ptr<itp::BivariateBase<double>>, 4> spatial;
+  explicit PointState(const pyi_windowed_nd_config* cfg)
+      : cache(static_cast<size_t>(cfg->half_x),
+              static_cast<size_t>(ND >= 2 ? cfg->half_y : 1)) {
+    if constexpr (ND == 1) {
+      uni = itp::univariate::factory<double>(to_univariate_method(cfg->method));
+    } else {
+      for (size_t k = 0; k < (size_t{1} << (ND - 2)); ++k) spatial[k] = make_spatial(cfg->method);
+    }
+  }
+};
+
+template <typename ZT, size_t ND, typename R>
+auto window_point_nd(const AnyGrid<ZT>& g, double x, double y, ZT z, double u,
+                     const pyi_windowed_nd_config* cfg, PointState<ZT, ND, R>& st)
+    -> std::optional<R> {
+  auto& cache = st.cache;
+  bool success = true;
+  bool was_updated = false;
+  std::optional<std::string> err;
+  int err_axis = -1;
+  bool inside = cache.has_domain();
+  if (inside) {
+    if constexpr (ND == 1) inside = cache.contains(x);
+    if constexpr (ND == 2) inside = cache.contains(x, y);
+    if constexpr (ND == 3) inside = cache.contains(x, y, z);
+    if constexpr (ND == 4) inside = cache.contains(x, y, z, u);
+  }
+  if (!inside) {
+    was_updated = true;
+    success = load_window_nd<ZT, ND>(g, x, y, z, u, to_ref_boundary(cfg->boundary),
+                                     cfg->bounds_error != 0, cache, err, err_axis);
+  }
+  if (!success) {
+    if (err.has_value()) throw WinError(err_axis, *err);
+    return std::nullopt;
+  }
+  if (!cache.is_valid()) return std::nullopt;
+  if constexpr (ND == 1) {
+    const auto xa = cache.template coords_as_eigen<0>();
+    const double r = cfg->derivative ? st.uni->derivative(xa, cache.vector(), x)
+                                     : (*st.uni)(xa, cache.vector(), x);
+    return static_cast<R>(r);
+  } else {
+    const auto xa = cache.template coords_as_eigen<0>();
+    const auto ya = cache.template coords_as_eigen<1>();
+    const bool zlin = cfg->z_method != PYI_AXIS_NEAREST;
+    const bool ulin = cfg->u_method != PYI_AXIS_NEAREST;
+    if constexpr (ND == 2) {
+      if (was_updated) st.spatial[0]->prepare(xa, ya, cache.matrix());
+      return static_cast<R>((*st.spatial[0])(x, y));
+    } else if constexpr (ND == 3) {
+      if (was_updated) {
+        st.spatial[0]->prepare(xa, ya, cache.matrix(0));
+        st.spatial[1]->prepare(xa, ya, cache.matrix(1));
+      }
+      const auto z0 = cache.template coord<2>(0);
+      const auto z1 = cache.template coord<2>(1);
+      const auto f0 = (*st.spatial[0])(x, y);
+      const auto f1 = (*st.spatial[1])(x, y);
+      return static_cast<R>(zlin ? itp::linear(z, z0, z1, f0, f1)
+                                 : itp::nearest(z, z0, z1, f0, f1));
+    } else {
+      if (was_updated) {
+        st.spatial[0]->prepare(xa, ya, cache.matrix(0, 0));
+        st.spatial[1]->prepare(xa, ya, cache.matrix(0, 1));
+        st.spatial[2]->prepare(xa, ya, cache.matrix(1, 0));
+        st.spatial[3]->prepare(xa, ya, cache.matrix(1, 1));
+      }
+      const auto z0 = cache.template coord<2>(0);
+      const auto z1 = cache.template coord<2>(1);
+      const auto u0 = cache.template coord<3>(0);
+      const auto u1 = cache.template coord<3>(1);
+      const auto f00 = (*st.spatial[0])(x, y);
+      const auto f01 = (*st.spatial[1])(x, y);
+      const auto f10 = (*st.spatial[2])(x, y);
+      const auto f11 = (*st.spatial[3])(x, y);
+      R f0;
+      R f1;
+      if (zlin) {
+        f0 = static_cast<R>(itp::linear(z, z0, z1, f00, f10));
+        f1 = static_cast<R>(itp::linear(z, z0, z1, f01, f11));
+      } else {
+        f0 = static_cast<R>(itp::nearest(z, z0, z1, f00, f10));
+        f1 = static_cast<R>(itp::nearest(z, z0, z1, f01, f11));
+      }
+      return static_cast<R>(ulin ? itp::linear(u, u0, u1, f0, f1)
+                                 : itp::nearest(u, u0, u1, f0, f1));
+    }
+  }
+}
+
+template <typename ZT, size_t ND, typename R>
+auto windowed_nd_typed(const AnyGrid<ZT>& g, const pyi_windowed_nd_config* cfg,
+                       int stateless, int64_t n, const double* x, const double* y,
+                       const ZT* z, const double* u, R* o, const OobOut& oob) -> int {
+  std::fill(o, o + n, std::numeric_limits<R>::quiet_NaN());
+  try {
+    ref::parallel_for(
+        n,
+        [&](const int64_t start, const int64_t end) {
+          auto st = std::make_unique<PointState<ZT, ND, R>>(cfg);
+          for (int64_t k = start; k < end; ++k) {
+            if (stateless) st = std::make_unique<PointState<ZT, ND, R>>(cfg);
+            try {
+              auto r = window_point_nd<ZT, ND, R>(g, x[k], ND >= 2 ? y[k] : 0.0,
+                                                  ND >= 3 ? z[k] : ZT{}, ND >= 4 ? u[k] : 0.0,
+                                                  cfg, *st);
+              if (r.has_value()) o[k] = *r;
+            } catch (WinError& e) {
+              e.index = k;
+              throw;
+            }
+          }
+        },
+        cfg->num_threads);
+  } catch (const WinError& e) {
+    if (oob.index) *oob.index = e.index;
+    if (oob.axis) *oob.axis = e.axis;
+    set_err(oob.msg, oob.msglen, e.what());
+    return PYI_OOB;
+  }
+  return PYI_OK;
+}
+
+template <typename ZT, size_t ND>
+auto windowed_nd_z(const orc_axis* const* axes, int dtype, const void* data,
+                   const pyi_windowed_nd_config* cfg, int stateless, int64_t n,
+                   const double* x, const double* y, const void* z, const double* u,
+                   void* out, const OobOut& oob) -> int {
+  AnyGrid<ZT> g;
+  g.ax = axes[0]->f.get();
+  g.data = data;
+  g.dtype = dtype;
+  if constexpr (ND >= 2) {
+    g.ay = axes[1]->f.get();
+    g.n1 = g.ay->size();
+  }
+  if constexpr (ND >= 3) {
+    if constexpr (std::is_same_v<ZT, int64_t>) {
+      g.az = axes[2]->i.get();
+    } else {
+      g.az = axes[2]->f.get();
+    }
+    g.n2 = g.az->size();
+  }
+  if constexpr (ND >= 4) {
+    g.au = axes[3]->f.get();
+    g.n3 = g.au->size();
+  }
+  const bool r64 = dtype == PYI_F64 || dtype == PYI_I64 || dtype == PYI_U64;
+  if (r64) {
+    return windowed_nd_typed<ZT, ND, double>(g, cfg, stateless, n, x, y,
+                                             static_cast<const ZT*>(z), u,
+                                             static_cast<double*>(out), oob);
+  }
+  return windowed_nd_typed<ZT, ND, float>(g, cfg, stateless, n, x, y,
+                                          static_cast<const ZT*>(z), u,
+                                          static_cast<float*>(out), oob);
+}
+
+}  // namespace
+
+extern "C" int orc_windowed_nd(int ndim, const orc_axis* const* axes, int dtype,
+                               const void* data, const pyi_windowed_nd_config* cfg,
+                               int stateless, int64_t n, const double* x,
+                               const double* y, const void* z, const double* u,
+                               void* out, int64_t* oob_index, int* oob_axis,
+                               char* msg, size_t msglen) {
+  const OobOut oob{oob_index, oob_axis, msg, msglen};
+  if (cfg->half_x < 1 || (ndim >= 2 && cfg->half_y < 1)) return PYI_BAD_ARG;
+  if (cfg->method < PYI_S_BICUBIC || cfg->method > PYI_S_POLYNOMIAL) return PYI_BAD_ARG;
+  if (ndim == 1 && cfg->method < PYI_S_AKIMA) return PYI_BAD_ARG;
+  if (dtype < PYI_I8 || dtype > PYI_F64) return PYI_BAD_ARG;
+  const bool zi = ndim >= 3 && axes[2]->coord_type == PYI_COORD_I64;
+#define ORC_ND(ZT, ND) \
+  windowed_nd_z<ZT, ND>(axes, dtype, data, cfg, stateless, n, x, y, z, u, out, oob)
+  switch (ndim) {
+    case 1: return ORC_ND(double, 1);
+    case 2: return ORC_ND(double, 2);
+    case 3: return zi ? ORC_ND(int64_t, 3) : ORC_ND(double, 3);
+    case 4: return zi ? ORC_ND(int64_t, 4) : ORC_ND(double, 4);
+    default: return PYI_BAD_ARG;
+  }
+#undef ORC_ND
+}
+
+extern "C" double orc_univariate(int method, const double* xa, const double* ya,
+                                 int n, double x, int derivative) {
+  auto f = itp::univariate::factory<double>(to_univariate_method(method));
+  ref::Vector<double> vx = Eigen::Map<const ref::Vector<double>>(xa, n);
+  ref::Vector<double> vy = Eigen::Map<const ref::Vector<double>>(ya, n);
+  return derivative ? f->derivative(vx, vy, x) : (*f)(vx, vy, x);
+}

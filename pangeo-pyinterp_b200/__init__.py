@@ -11,12 +11,13 @@ or interpolation raises without one.
 from . import _abi, config, core, dist, synthetic
 from .config import geometric, windowed
 from .core import Axis, Grid, TemporalAxis
-from .regular_grid_interpolator import bivariate, quadrivariate, trivariate
+from .regular_grid_interpolator import (bivariate, quadrivariate, trivariate, univariate,
+                                        univariate_derivative)
 
-Grid2D = Grid3D = Grid4D = Grid  # pyinterp/__init__.py:92-95
+Grid1D = Grid2D = Grid3D = Grid4D = Grid  # pyinterp/__init__.py:92-95
 
-__all__ = ["Axis", "TemporalAxis", "Grid", "Grid2D", "Grid3D", "Grid4D", "bivariate", "trivariate",
-           "quadrivariate", "geometric", "windowed", "config", "core", "dist", "synthetic", "device_count",
+__all__ = ["Axis", "TemporalAxis", "Grid", "Grid1D", "Grid2D", "Grid3D", "Grid4D", "bivariate", "trivariate",
+           "quadrivariate", "univariate", "univariate_derivative", "geometric", "windowed", "config", "core", "dist", "synthetic", "device_count",
            "launch_count"]
 
 

@@ -17,6 +17,11 @@ PYI_COORD_F64, PYI_COORD_I64 = 0, 1
 PYI_BILINEAR, PYI_IDW, PYI_NEAREST = 0, 1, 2
 PYI_AXIS_LINEAR, PYI_AXIS_NEAREST = 0, 1
 PYI_W_BICUBIC, PYI_W_BILINEAR = 0, 1
+#: pyi_spatial_method: every fitting model of the windowed path
+SPATIAL_METHODS = {
+    "bicubic": 0, "bilinear": 1, "akima": 2, "akima_periodic": 3, "c_spline": 4,
+    "c_spline_not_a_knot": 5, "c_spline_periodic": 6, "linear": 7, "steffen": 8, "polynomial": 9,
+}
 PYI_BOUNDARY_UNDEF, PYI_BOUNDARY_SHRINK = 0, 1
 PYI_MEM_HOST, PYI_MEM_DEVICE = 0, 1
 PYI_GRID_DEFAULT, PYI_GRID_PACK_CELLS, PYI_GRID_BORROW_DEVICE = 0, 1, 2
@@ -77,6 +82,20 @@ class WindowedConfig(C.Structure):
     ]
 
 
+class WindowedNdConfig(C.Structure):
+    _fields_ = [
+        ("method", C.c_int32),
+        ("half_x", C.c_int32),
+        ("half_y", C.c_int32),
+        ("boundary", C.c_int32),
+        ("bounds_error", C.c_int32),
+        ("num_threads", C.c_int32),
+        ("z_method", C.c_int32),
+        ("u_method", C.c_int32),
+        ("derivative", C.c_int32),
+    ]
+
+
 #: every symbol include/pyinterp_b200.h declares: name -> (restype, argtypes)
 _P = C.c_void_p
 _I64P = C.POINTER(C.c_int64)
@@ -102,6 +121,8 @@ SIGNATURES = {
                                 C.c_int, _I64P, _IP, _P]),
     "pyi_windowed2d": (C.c_int, [_P, C.POINTER(WindowedConfig), C.c_int64, _P, _P, _P, C.c_int,
                                  _I64P, _IP, _P]),
+    "pyi_windowed": (C.c_int, [_P, C.POINTER(WindowedNdConfig), C.c_int64, _P, _P, _P, _P, _P, C.c_int,
+                               _I64P, _IP, _P]),
     "pyi_format_bounds_error": (C.c_int, [_P, C.c_int, _P, C.c_char_p, C.c_size_t]),
     "pyi_launch_count": (C.c_int64, []),
 }

@@ -3,9 +3,8 @@
 (cxx/include/pyinterp/config/{common,geometric,windowed}.hpp,
 cxx/src/pybind/config.cpp): immutable, ``with_*`` methods return a copy.
 
-Only what the hot path consumes is mirrored: the geometric methods
-(bilinear / idw / nearest) for 2-4 D and the windowed bivariate methods this
-build runs on the GPU (bicubic, windowed bilinear).
+The geometric methods (bilinear / idw / nearest) for 2-4 D and every windowed
+fitting model (bicubic, bilinear and the univariate family) for 1-4 D.
 """
 from __future__ import annotations
 
@@ -117,27 +116,46 @@ class BoundaryConfig:
         return cls(_abi.PYI_BOUNDARY_SHRINK)
 
 
-class _WBivariate(_Common):
-    """config/windowed.hpp: method, half window sizes (default 3 / 3,
-    :244-247), boundary mode."""
+_AXIS_METHODS = {"linear": _abi.PYI_AXIS_LINEAR, "nearest": _abi.PYI_AXIS_NEAREST}
+_UNIVARIATE_MODELS = ("akima", "akima_periodic", "c_spline", "c_spline_not_a_knot",
+                      "c_spline_periodic", "linear", "polynomial", "steffen")
+_SPATIAL_MODELS = _UNIVARIATE_MODELS + ("bilinear", "bicubic")
 
-    _GPU_METHODS = {"bicubic": _abi.PYI_W_BICUBIC, "bilinear": _abi.PYI_W_BILINEAR}
 
-    def __init__(self):
-        self._method = _abi.PYI_W_BICUBIC
+class AxisConfig:
+    """config/common.hpp AxisConfig: linear / nearest along the third and
+    fourth axes."""
+
+    def __init__(self, method: int = _abi.PYI_AXIS_LINEAR):
+        self.method = method
+
+    @classmethod
+    def linear(cls):
+        return cls(_abi.PYI_AXIS_LINEAR)
+
+    @classmethod
+    def nearest(cls):
+        return cls(_abi.PYI_AXIS_NEAREST)
+
+
+class _Windowed(_Common):
+    """config/windowed.hpp: fitting model (factories :404-436), half window
+    sizes (default 3 / 3, :244-247), boundary mode, third / fourth axis
+    methods (default linear, :392-401)."""
+
+    _ndim = 2
+    _models = _SPATIAL_MODELS
+
+    def __init__(self, model: str = "bicubic"):
+        if model not in self._models:
+            raise ValueError(f"Unknown fitting model: {model}")  # config/windowed.hpp:54-55
+        self._method = _abi.SPATIAL_METHODS[model]
         self._half_x = 3
         self._half_y = 3
         self._boundary = _abi.PYI_BOUNDARY_UNDEF
-
-    @classmethod
-    def bicubic(cls):
-        return cls()
-
-    @classmethod
-    def bilinear(cls):
-        c = cls()
-        c._method = _abi.PYI_W_BILINEAR
-        return c
+        self._z_method = _abi.PYI_AXIS_LINEAR
+        self._u_method = _abi.PYI_AXIS_LINEAR
+        self._derivative = 0
 
     def with_boundary_mode(self, config: BoundaryConfig):
         c = self._clone()
@@ -159,22 +177,70 @@ class _WBivariate(_Common):
         return c
 
     def _pod(self) -> _abi.WindowedConfig:
+        """POD of pyi_windowed2d (bicubic / bilinear on 2-D grids)."""
         return _abi.WindowedConfig(self._method, self._half_x, self._half_y, self._boundary,
                                    int(self._bounds_error), self._num_threads)
 
+    def _pod_nd(self) -> _abi.WindowedNdConfig:
+        return _abi.WindowedNdConfig(self._method, self._half_x, self._half_y, self._boundary,
+                                     int(self._bounds_error), self._num_threads, self._z_method,
+                                     self._u_method, self._derivative)
 
-def _unsupported(name):
+
+def _model_factory(name):
     def factory(cls):
-        raise NotImplementedError(
-            f"windowed method '{name}' is outside this build's GPU path "
-            "(SURVEY.md 8f: next); available: bicubic, bilinear")
+        return cls(name)
+    factory.__name__ = name
     return classmethod(factory)
 
 
-for _name in ("akima", "akima_periodic", "c_spline", "c_spline_not_a_knot", "c_spline_periodic",
-              "linear", "polynomial", "steffen"):
-    setattr(_WBivariate, _name, _unsupported(_name))
+class _WUnivariate(_Windowed):
+    """config/windowed.hpp Univariate / UnivariateMethod (:156-222,:313-352):
+    univariate models only, default linear, one half window size."""
+
+    _ndim = 1
+    _models = _UNIVARIATE_MODELS
+
+    def __init__(self, model: str = "linear"):
+        super().__init__(model)
+        self._half_y = 1
+
+    def with_half_window_size(self, size: int):
+        if int(size) < 1:
+            raise ValueError("half_window_size must be at least 1")
+        c = self._clone()
+        c._half_x = int(size)
+        return c
+
+
+class _WBivariate(_Windowed):
+    _ndim = 2
+
+
+class _WTrivariate(_Windowed):
+    _ndim = 3
+
+    def with_third_axis(self, config: AxisConfig):
+        c = self._clone()
+        c._z_method = config.method
+        return c
+
+
+class _WQuadrivariate(_WTrivariate):
+    _ndim = 4
+
+    def with_fourth_axis(self, config: AxisConfig):
+        c = self._clone()
+        c._u_method = config.method
+        return c
+
+
+for _cls in (_WUnivariate, _WBivariate, _WTrivariate, _WQuadrivariate):
+    for _name in _cls._models:
+        setattr(_cls, _name, _model_factory(_name))
 
 geometric = types.SimpleNamespace(Bivariate=_GBivariate, Trivariate=_GTrivariate,
                                   Quadrivariate=_GQuadrivariate)
-windowed = types.SimpleNamespace(Bivariate=_WBivariate, BoundaryConfig=BoundaryConfig)
+windowed = types.SimpleNamespace(Univariate=_WUnivariate, Bivariate=_WBivariate,
+                                 Trivariate=_WTrivariate, Quadrivariate=_WQuadrivariate,
+                                 BoundaryConfig=BoundaryConfig, AxisConfig=AxisConfig)

@@ -329,8 +329,8 @@ class Grid:
     """
 
     def __init__(self, *args, resident: bool = False, pack_cells: bool = True):
-        if len(args) < 3 or len(args) > 5:
-            raise ValueError("Grid(x, y[, z[, u]], array): 2 to 4 axes and an array are required")
+        if len(args) < 2 or len(args) > 5:
+            raise ValueError("Grid(x[, y[, z[, u]]], array): 1 to 4 axes and an array are required")
         *axes, array = args
         for a in axes:
             if not isinstance(a, Axis):
@@ -406,6 +406,8 @@ class Grid:
 
     @property
     def y(self):
+        if len(self._axes) < 2:
+            raise AttributeError("grid has no y axis")
         return self._axes[1]
 
     @property
@@ -473,6 +475,8 @@ def _run(grid: Grid, cfg, coords: list, windowed: bool):
     names = ["x", "y", "z", "u"][:nd]
     on_device = any(_is_torch_cuda(c) for c in coords)
     oi, oa = C.c_int64(-1), C.c_int(-1)
+    # 2-D bicubic / bilinear keep the dedicated entry point (and its fast kernel)
+    two_d_entry = windowed and nd == 2 and cfg._method <= _abi.PYI_W_BILINEAR
     grid._before_call()
     if on_device:
         import torch
@@ -491,19 +495,24 @@ def _run(grid: Grid, cfg, coords: list, windowed: bool):
                           device=cs[0].device)
         ptrs = [c.data_ptr() for c in cs] + [None] * (4 - nd)
         stream = torch.cuda.current_stream(cs[0].device).cuda_stream
-        pod = cfg._pod()
         with torch.cuda.device(cs[0].device):
-            if windowed:
+            if windowed and two_d_entry:
+                pod = cfg._pod()
                 st = lib.pyi_windowed2d(grid._h, C.byref(pod), n, ptrs[0], ptrs[1], out.data_ptr(),
                                         _abi.PYI_MEM_DEVICE, C.byref(oi), C.byref(oa), stream)
+            elif windowed:
+                pod = cfg._pod_nd()
+                st = lib.pyi_windowed(grid._h, C.byref(pod), n, ptrs[0], ptrs[1], ptrs[2], ptrs[3],
+                                      out.data_ptr(), _abi.PYI_MEM_DEVICE, C.byref(oi), C.byref(oa),
+                                      stream)
             else:
+                pod = cfg._pod()
                 st = lib.pyi_geometric(grid._h, C.byref(pod), n, ptrs[0], ptrs[1], ptrs[2], ptrs[3],
                                        out.data_ptr(), _abi.PYI_MEM_DEVICE, C.byref(oi), C.byref(oa), stream)
         if st == _abi.PYI_OOB:
             bad = cs[oa.value][oi.value].item()
     else:
-        cs = [np.ascontiguousarray(coords[0], dtype=np.float64),
-              np.ascontiguousarray(coords[1], dtype=np.float64)]
+        cs = [np.ascontiguousarray(c, dtype=np.float64) for c in coords[:min(nd, 2)]]
         if nd >= 3:
             if grid.has_temporal_axis:
                 cs.append(grid._axes[2].cast_to_int64(coords[2]))  # grid_dispatch.hpp:190-195
@@ -515,11 +524,16 @@ def _run(grid: Grid, cfg, coords: list, windowed: bool):
         n = cs[0].size
         out = _host_result(n, grid.result_dtype)
         ptrs = [_np_ptr(c) for c in cs] + [None] * (4 - nd)
-        pod = cfg._pod()
-        if windowed:
+        if windowed and two_d_entry:
+            pod = cfg._pod()
             st = lib.pyi_windowed2d(grid._h, C.byref(pod), n, ptrs[0], ptrs[1], _np_ptr(out),
                                     _abi.PYI_MEM_HOST, C.byref(oi), C.byref(oa), None)
+        elif windowed:
+            pod = cfg._pod_nd()
+            st = lib.pyi_windowed(grid._h, C.byref(pod), n, ptrs[0], ptrs[1], ptrs[2], ptrs[3],
+                                  _np_ptr(out), _abi.PYI_MEM_HOST, C.byref(oi), C.byref(oa), None)
         else:
+            pod = cfg._pod()
             st = lib.pyi_geometric(grid._h, C.byref(pod), n, ptrs[0], ptrs[1], ptrs[2], ptrs[3],
                                    _np_ptr(out), _abi.PYI_MEM_HOST, C.byref(oi), C.byref(oa), None)
         if st == _abi.PYI_OOB:
@@ -541,9 +555,9 @@ def _dispatch(grid: Grid, nd: int, name: str, coords: list, cfg):
         raise ValueError(f"{name} requires {nd}D grid, got {grid.ndim}D")
     if isinstance(cfg, _config._Geometric):
         return _run(grid, cfg, coords, windowed=False)
-    if isinstance(cfg, _config._WBivariate):
-        if nd != 2:
-            raise NotImplementedError("windowed interpolation is available for 2D grids only")
+    if isinstance(cfg, _config._Windowed):
+        if cfg._ndim != nd:
+            raise TypeError(f"{name} takes a {nd}-D windowed configuration")
         return _run(grid, cfg, coords, windowed=True)
     raise TypeError(f"unsupported configuration object {type(cfg).__name__}")
 
@@ -562,3 +576,15 @@ def trivariate(grid: Grid, x, y, z, config=None):
 def quadrivariate(grid: Grid, x, y, z, u, config=None):
     """``core.quadrivariate(grid, x, y, z, u, config)`` (quadrivariate_geometric.cpp:50-60)."""
     return _dispatch(grid, 4, "quadrivariate", [x, y, z, u], config or _config.geometric.Quadrivariate())
+
+
+def univariate(grid: Grid, x, config=None):
+    """``core.univariate(grid, x, config)`` (pybind/windowed/univariate.hpp:122-152)."""
+    return _dispatch(grid, 1, "univariate", [x], config or _config.windowed.Univariate())
+
+
+def univariate_derivative(grid: Grid, x, config=None):
+    """``core.univariate_derivative(grid, x, config)`` (pybind/windowed/univariate.hpp:160-190)."""
+    cfg = (config or _config.windowed.Univariate())._clone()
+    cfg._derivative = 1
+    return _dispatch(grid, 1, "univariate_derivative", [x], cfg)

@@ -538,7 +538,7 @@ pyi_grid* pyi_grid_create(int ndim, const pyi_axis* const* axes, int dtype, cons
     return static_cast<pyi_grid*>(nullptr);
   };
   if (require_device() != PYI_OK) return set(PYI_NO_DEVICE);
-  if (ndim < 2 || ndim > 4 || !axes || !data || !shape || dtype < PYI_I8 || dtype > PYI_F64) {
+  if (ndim < 1 || ndim > 4 || !axes || !data || !shape || dtype < PYI_I8 || dtype > PYI_F64) {
     g_error = "pyi_grid_create: invalid argument";
     return set(PYI_BAD_ARG);
   }
@@ -622,6 +622,7 @@ int pyi_grid_update(pyi_grid* grid, const void* data, int mem) {
 
 int pyi_grid_pack(pyi_grid* grid) {
   if (!grid) return fail(PYI_BAD_ARG, "null grid");
+  if (grid->ndim < 2) return PYI_OK;  // 1-D grids have no cell-packed copy
   size_t cells = 1;
   int shape[4] = {1, 1, 1, 1};
   for (int k = 0; k < grid->ndim; ++k) {
@@ -817,6 +818,110 @@ int pyi_windowed2d(const pyi_grid* grid, const pyi_windowed_config* cfg, int64_t
     q.oob_key = ws.oob_key;
     q.index_base = begin;
     return pyi::launch_windowed2d(q, s);
+  });
+  if (st != PYI_OK) return st;
+  if (cfg->bounds_error) {
+    unsigned long long key = pyi::kNoOob;
+    PYI_CUDA(cudaMemcpy(&key, ws.oob_key, sizeof(key), cudaMemcpyDeviceToHost));
+    return report_oob(key, oob_index, oob_axis);
+  }
+  return PYI_OK;
+}
+
+int pyi_windowed(const pyi_grid* grid, const pyi_windowed_nd_config* cfg, int64_t n,
+                 const double* x, const double* y, const void* z, const double* u, void* out,
+                 int mem, int64_t* oob_index, int* oob_axis, void* stream) {
+  int st = require_device();
+  if (st != PYI_OK) return st;
+  if (!grid || !cfg || n < 0) return fail(PYI_BAD_ARG, "pyi_windowed: null argument");
+  const int nd = grid->ndim;
+  if (cfg->half_x < 1 || (nd >= 2 && cfg->half_y < 1)) {
+    return fail(PYI_BAD_ARG, "Half window sizes must be at least 1");  // cache.hpp:258-260
+  }
+  if (cfg->half_x > 16 || (nd >= 2 && cfg->half_y > 16)) {
+    return fail(PYI_BAD_ARG, "pyi_windowed: half window sizes above 16 are not supported");
+  }
+  if (cfg->method < PYI_S_BICUBIC || cfg->method > PYI_S_POLYNOMIAL) {
+    return fail(PYI_BAD_ARG, "Unknown fitting model");  // config/windowed.hpp:54-55
+  }
+  if (nd == 1 && cfg->method < PYI_S_AKIMA) {
+    return fail(PYI_BAD_ARG, "pyi_windowed: a 1-D grid takes a univariate fitting model");
+  }
+  if (cfg->derivative && nd != 1) {
+    return fail(PYI_BAD_ARG, "pyi_windowed: derivatives are defined for 1-D grids only");
+  }
+  if (n > 0 && (!x || !out || (nd >= 2 && !y) || (nd >= 3 && !z) || (nd >= 4 && !u))) {
+    return fail(PYI_BAD_SHAPE, "pyi_windowed: missing array");
+  }
+  if (n == 0) return PYI_OK;
+  pyi::WinNdParams p{};
+  for (int k = 0; k < nd; ++k) p.ax[k] = grid->dax[k];
+  p.data = grid->d_data;
+  p.dtype = grid->dtype;
+  p.ndim = nd;
+  p.method = cfg->method;
+  p.half_x = cfg->half_x;
+  p.half_y = nd >= 2 ? cfg->half_y : 1;
+  p.boundary = cfg->boundary;
+  p.bounds_error = cfg->bounds_error;
+  p.z_method = cfg->z_method;
+  p.u_method = cfg->u_method;
+  p.derivative = cfg->derivative;
+  const size_t out_elem = result_is_f64(grid->dtype) ? 8 : 4;
+  if (mem == PYI_MEM_DEVICE) {
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    p.n = n;
+    p.x = x;
+    p.y = y;
+    p.z = z;
+    p.u = u;
+    p.out = out;
+    p.oob_key = grid->d_oob;
+    if (cfg->bounds_error) {
+      PYI_CUDA(cudaMemsetAsync(grid->d_oob, 0xff, sizeof(unsigned long long), s));
+    }
+    cudaError_t e = pyi::launch_windowed_nd(p, s);
+    if (e != cudaSuccess) return cuda_fail(e, "windowed kernel");
+    if (cfg->bounds_error) {
+      unsigned long long key = pyi::kNoOob;
+      PYI_CUDA(cudaMemcpyAsync(&key, grid->d_oob, sizeof(key), cudaMemcpyDeviceToHost, s));
+      PYI_CUDA(cudaStreamSynchronize(s));
+      return report_oob(key, oob_index, oob_axis);
+    }
+    return PYI_OK;
+  }
+  std::vector<Column> cols;
+  auto add_in = [&](const void* ptr) {
+    Column c;
+    c.host_in = ptr;
+    cols.push_back(c);
+    return cols.size() - 1;
+  };
+  const size_t cx = add_in(x);
+  const size_t cy = nd >= 2 ? add_in(y) : 0;
+  const size_t cz = nd >= 3 ? add_in(z) : 0;
+  const size_t cu = nd >= 4 ? add_in(u) : 0;
+  Column co;
+  co.host_out = out;
+  co.elem = out_elem;
+  cols.push_back(co);
+  const size_t cout_ = cols.size() - 1;
+  Workspace& ws = workspace();
+  std::lock_guard<std::recursive_mutex> ws_lock(ws.mu);
+  st = ws.ensure(0, 0);
+  if (st != PYI_OK) return st;
+  PYI_CUDA(cudaMemset(ws.oob_key, 0xff, sizeof(unsigned long long)));
+  st = run_pipeline(n, cols, [&](cudaStream_t s, long long begin, long long count, char* dev) {
+    pyi::WinNdParams q = p;
+    q.n = count;
+    q.x = reinterpret_cast<const double*>(dev + cols[cx].dev_off);
+    if (nd >= 2) q.y = reinterpret_cast<const double*>(dev + cols[cy].dev_off);
+    if (nd >= 3) q.z = dev + cols[cz].dev_off;
+    if (nd >= 4) q.u = reinterpret_cast<const double*>(dev + cols[cu].dev_off);
+    q.out = dev + cols[cout_].dev_off;
+    q.oob_key = ws.oob_key;
+    q.index_base = begin;
+    return pyi::launch_windowed_nd(q, s);
   });
   if (st != PYI_OK) return st;
   if (cfg->bounds_error) {

@@ -46,6 +46,28 @@ struct WinParams {
   unsigned long long* oob_key;
 };
 
+// windowed path on 1-D .. 4-D grids, every fitting model (pyi_windowed_nd.cuh)
+struct WinNdParams {
+  DAxis ax[4];
+  const void* data;
+  int32_t dtype;
+  int32_t ndim;
+  int32_t method;  // pyi_spatial_method
+  int32_t half_x, half_y;
+  int32_t boundary;
+  int32_t bounds_error;
+  int32_t z_method, u_method;
+  int32_t derivative;
+  long long n;
+  long long index_base;
+  const double* x;
+  const double* y;
+  const void* z;  // double or int64 according to ax[2].coord_i64
+  const double* u;
+  void* out;
+  unsigned long long* oob_key;
+};
+
 struct FindParams {
   DAxis ax;
   long long n;
@@ -56,6 +78,7 @@ struct FindParams {
 
 cudaError_t launch_geometric(const GeoParams& p, cudaStream_t stream);
 cudaError_t launch_windowed2d(const WinParams& p, cudaStream_t stream);
+cudaError_t launch_windowed_nd(const WinNdParams& p, cudaStream_t stream);
 cudaError_t launch_find_indexes(const FindParams& p, cudaStream_t stream);
 cudaError_t launch_find_index(const FindParams& p, cudaStream_t stream);
 // cell packing (2-D .. 4-D): the 2^ndim corners of every cell contiguous, in the

@@ -1,5 +1,7 @@
-// pyi_windowed.cu -- K4 translation unit: windowed 2-D interpolation (generic
-// kernel pyi_windowed.cuh, 6 x 6 bicubic fast path pyi_fastwin.cuh).
+// pyi_windowed.cu -- translation unit of the windowed path: K4 windowed 2-D
+// bicubic / bilinear (generic kernel pyi_windowed.cuh, 6 x 6 bicubic fast path
+// pyi_fastwin.cuh) and K6 windowed 1-D .. 4-D with every fitting model
+// (pyi_univariate.cuh, pyi_windowed_nd.cuh).
 #include "pyi_common.cuh"
 
 namespace pyi {
@@ -12,3 +14,44 @@ static bool force_generic() {
 }  // namespace pyi
 #include "pyi_windowed.cuh"
 #include "pyi_fastwin.cuh"
+
+namespace pyi {
+// K6 (pyi_windowed_nd.cuh) is instantiated per window capacity in
+// pyi_windowed_nd.cu, one object file each (PYI_ND_MAXW = 6, 12, 32)
+template <int MAXW>
+cudaError_t launch_windowed_nd_w(const WinNdParams& p, cudaStream_t stream);
+extern template cudaError_t launch_windowed_nd_w<6>(const WinNdParams&, cudaStream_t);
+extern template cudaError_t launch_windowed_nd_w<12>(const WinNdParams&, cudaStream_t);
+extern template cudaError_t launch_windowed_nd_w<32>(const WinNdParams&, cudaStream_t);
+
+cudaError_t launch_windowed_nd(const WinNdParams& p, cudaStream_t stream) {
+  if (p.n <= 0) return cudaSuccess;
+  // 2-D bicubic / bilinear keep K4 and its fast path
+  if (p.ndim == 2 && p.method <= PYI_S_BILINEAR) {
+    WinParams q{};
+    q.ax[0] = p.ax[0];
+    q.ax[1] = p.ax[1];
+    q.data = p.data;
+    q.dtype = p.dtype;
+    q.method = p.method;
+    q.half_x = p.half_x;
+    q.half_y = p.half_y;
+    q.boundary = p.boundary;
+    q.bounds_error = p.bounds_error;
+    q.n = p.n;
+    q.index_base = p.index_base;
+    q.x = p.x;
+    q.y = p.y;
+    q.out = p.out;
+    q.oob_key = p.oob_key;
+    return launch_windowed2d(q, stream);
+  }
+  const int hy = p.ndim >= 2 ? p.half_y : 1;
+  const int w = 2 * (p.half_x > hy ? p.half_x : hy);
+  if (w <= 6) return launch_windowed_nd_w<6>(p, stream);
+  if (w <= 12) return launch_windowed_nd_w<12>(p, stream);
+  if (w <= 32) return launch_windowed_nd_w<32>(p, stream);
+  return cudaErrorInvalidValue;
+}
+
+}  // namespace pyi

@@ -334,6 +334,7 @@ __device__ __forceinline__ int windowed_point(const WinParams& p, double x, doub
   return -1;
 }
 
+#ifndef PYI_WINDOWED_DEVICE_ONLY  // kernel and launchers: pyi_windowed.cu only
 template <int MAXW, typename R>
 __global__ void __launch_bounds__(128)
 windowed2d_kernel(const __grid_constant__ WinParams p) {
@@ -382,5 +383,7 @@ cudaError_t launch_windowed2d(const WinParams& p, cudaStream_t stream) {
   if (w <= 32) return launch_windowed_w<32>(p, stream);
   return cudaErrorInvalidValue;
 }
+
+#endif  // PYI_WINDOWED_DEVICE_ONLY
 
 }  // namespace pyi

@@ -41,7 +41,9 @@ def axis_values_i64(e):
 def _field(shape, dtype, seed, nan_fraction=0.0):
     rng = np.random.Generator(np.random.PCG64(seed))
     idx = np.indices(shape).astype(np.float64)
-    g = np.sin(idx[0] * 0.37) * np.cos(idx[1] * 0.23)
+    g = np.sin(idx[0] * 0.37)
+    if len(shape) >= 2:
+        g = g * np.cos(idx[1] * 0.23)
     for k in range(2, len(shape)):
         g = g * (1.0 + 0.1 * idx[k])
     g = g + 0.05 * rng.standard_normal(shape)
@@ -127,7 +129,41 @@ CASES = {
     "lookup_time_irregular": dict(kind="idx", axes=[(T0 + np.cumsum(np.arange(1, 41, dtype=np.int64)) * 3_600_000_000_000,
                                                      None, False)], n=3000, seed=20),
 }
+
+# windowed 1-D .. 4-D with every fitting model.  These are
+# produced and checked by the reference build only (ref_only): the plain-C
+# restatement does not cover them.
+WND_MODELS = ("akima", "akima_periodic", "c_spline", "c_spline_not_a_knot", "c_spline_periodic", "linear",
+              "steffen", "polynomial")
+for _k, _m in enumerate(WND_MODELS):
+    CASES[f"wnd1d_{_m}"] = dict(kind="wnd", ref_only=True, axes=[(LON72, 360.0, False)], dtype="float64",
+                                method=_m, half=(3, 1), boundary="undef", n=1500, seed=30 + _k,
+                                derivative=bool(_k % 2))
+    CASES[f"wnd2d_{_m}"] = dict(kind="wnd", ref_only=True, axes=[(LON72, 360.0, False), (LAT_IRR, None, False)],
+                                dtype="float64" if _k % 2 == 0 else "float32", method=_m,
+                                half=(3, 3) if _k % 3 else (4, 3), boundary="shrink" if _k % 2 else "undef",
+                                n=1500, seed=40 + _k)
+CASES["wnd3d_bicubic_time"] = dict(kind="wnd", ref_only=True,
+                                   axes=[(LON72, 360.0, False), (LAT36, None, False), (TIME10, None, False)],
+                                   dtype="float32", method="bicubic", half=(3, 3), boundary="undef", n=1500,
+                                   seed=50)
+CASES["wnd3d_c_spline_nearest_z"] = dict(kind="wnd", ref_only=True,
+                                         axes=[(LON72, 360.0, False), (LAT36, None, False),
+                                               (np.arange(6) * 2.5, None, False)],
+                                         dtype="float64", method="c_spline", half=(3, 3), boundary="shrink",
+                                         n=1500, seed=51, z_method=1)
+CASES["wnd4d_bilinear_depth"] = dict(kind="wnd", ref_only=True,
+                                     axes=[(LON72[::2], 360.0, False), (LAT36[::2], None, False),
+                                           (TIME10[:6], None, False), (DEPTH8, None, False)],
+                                     dtype="float32", method="bilinear", half=(2, 2), boundary="undef", n=1500,
+                                     seed=52)
+CASES["wnd4d_akima_f64"] = dict(kind="wnd", ref_only=True,
+                                axes=[(LON72[::2], 360.0, False), (LAT36[::2], None, False),
+                                      (np.arange(5) * 1.0, None, False), (DEPTH8, None, True)],
+                                dtype="float64", method="akima", half=(3, 3), boundary="undef", n=1200, seed=53,
+                                u_method=1)
 VECTOR_CASES = sorted(CASES)
+PORT_CASES = [k for k in VECTOR_CASES if not CASES[k].get("ref_only")]
 
 
 def build_case(name):
@@ -142,7 +178,7 @@ def build_case(name):
         v = np.asarray(values)
         integer = v.dtype.kind in "iu"
         lo, hi = v.min(), v.max()
-        if period is not None and c["kind"] != "win":
+        if period is not None and c["kind"] not in ("win", "wnd"):
             lo, hi = lo - float(period), hi + float(period)
         coords.append(_coords(rng, float(lo), float(hi), c["n"], nodes=v, integer=integer))
     for k, name_ in enumerate("xyzu"[: len(coords)]):
@@ -196,6 +232,12 @@ def run_case_on_oracle(o, name, d):
         out, _ = o.geometric(axes, d["grid"], d["x"], d["y"], d.get("z"), d.get("u"), method=m, z_method=am,
                              u_method=am)
         return {"out": out}
+    if c["kind"] == "wnd":
+        out, _ = o.windowed_nd(axes, d["grid"], d["x"], d.get("y"), d.get("z"), d.get("u"), method=c["method"],
+                               half_x=c["half"][0], half_y=c["half"][1], boundary=c["boundary"], stateless=True,
+                               z_method=c.get("z_method", 0), u_method=c.get("u_method", 0),
+                               derivative=c.get("derivative", False))
+        return {"out": out}
     out, _ = o.windowed2d(axes, d["grid"], d["x"], d["y"], method=WMETHOD[c["method"]], half_x=c["half"][0],
                           half_y=c["half"][1], boundary=c["boundary"], stateless=True)
     return {"out": out}
@@ -228,7 +270,30 @@ def run_case_on_gpu(pyi, name, d):
     if c["kind"] == "geo":
         fn = {2: pyi.bivariate, 3: pyi.trivariate, 4: pyi.quadrivariate}[len(axes)]
         return {"out": fn(grid, *coords, c["method"])}
+    if c["kind"] == "wnd":
+        return {"out": _run_wnd(pyi, c, grid, coords)}
     return {"out": pyi.core.bivariate(grid, *coords, _windowed_cfg(pyi, c))}
+
+
+def _run_wnd(pyi, c, grid, coords):
+    nd = len(coords)
+    cls = {1: pyi.windowed.Univariate, 2: pyi.windowed.Bivariate, 3: pyi.windowed.Trivariate,
+           4: pyi.windowed.Quadrivariate}[nd]
+    cfg = getattr(cls, c["method"])()
+    bc = pyi.config.BoundaryConfig.shrink() if c["boundary"] == "shrink" else pyi.config.BoundaryConfig.undef()
+    cfg = cfg.with_boundary_mode(bc)
+    if nd == 1:
+        cfg = cfg.with_half_window_size(c["half"][0])
+        fn = pyi.core.univariate_derivative if c.get("derivative") else pyi.core.univariate
+        return fn(grid, coords[0], cfg)
+    cfg = cfg.with_half_window_size_x(c["half"][0]).with_half_window_size_y(c["half"][1])
+    am = {0: pyi.windowed.AxisConfig.linear, 1: pyi.windowed.AxisConfig.nearest}
+    if nd >= 3:
+        cfg = cfg.with_third_axis(am[c.get("z_method", 0)]())
+    if nd >= 4:
+        cfg = cfg.with_fourth_axis(am[c.get("u_method", 0)]())
+    fn = {2: pyi.core.bivariate, 3: pyi.core.trivariate, 4: pyi.core.quadrivariate}[nd]
+    return fn(grid, *coords, cfg)
 
 
 def _windowed_cfg(pyi, c):

@@ -108,6 +108,8 @@ def test_known_answer_windowed_evaluators(orc_any):
 @pytest.mark.parametrize("name", gu.VECTOR_CASES)
 def test_reference_vectors(orc_any, name):
     """Seeded input/output vectors produced by the reference's own headers."""
+    if gu.CASES[name].get("ref_only") and orc_any.kind != "reference":
+        pytest.skip("windowed N-D models are pinned by the reference build only")
     d = gu.load_vectors(name)
     got = gu.run_case_on_oracle(orc_any, name, d)
     gu.compare(name, got, d, exact=True)

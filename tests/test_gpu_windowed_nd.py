@@ -1,0 +1,207 @@
+"""GPU parity of the widened windowed path: every fitting
+model on 1-D .. 4-D grids through the public API / C-ABI (pyi_windowed)
+against the reference build (oracle/_ref: the reference's own
+InterpolationCache, factory(), Univariate / BivariateBase classes) on identical
+seeded inputs.  The plain-C restatement does not cover these models; without
+the reference build the committed golden vectors (test_gpu_golden.py, cases
+wnd*) are the check.
+
+Bar: NaN positions identical, values within 1e-12 (float64) / 1e-5 (float32)
+relative with the field-scale guard; the fraction of bit-identical values is
+asserted too where the operation sequence is the reference's own.
+"""
+import numpy as np
+import pytest
+
+import axes_zoo
+from test_gpu_parity import close, _mk_axis, _queries
+
+pytestmark = pytest.mark.gpu
+
+MODELS = ["akima", "akima_periodic", "c_spline", "c_spline_not_a_knot", "c_spline_periodic", "linear",
+          "steffen", "polynomial"]
+SPATIAL = ["bicubic", "bilinear"] + MODELS
+
+
+def _axes(pyi, o, specs):
+    pairs = [_mk_axis(pyi, o, s) for s in specs]
+    return [p[0] for p in pairs], [p[1] for p in pairs]
+
+
+def _field(shape, dtype, seed=5, nan=0.0):
+    rng = np.random.default_rng(seed)
+    g = rng.normal(size=shape) * 40.0
+    if np.dtype(dtype).kind == "f":
+        g = g.astype(dtype)
+        if nan:
+            g[rng.random(shape) < nan] = np.nan
+    else:
+        info = np.iinfo(dtype)
+        g = np.clip(np.round(g), info.min, info.max).astype(dtype)
+    return g
+
+
+def _cfg(pyi, nd, model, half, boundary, z_method="linear", u_method="linear"):
+    cls = {1: pyi.windowed.Univariate, 2: pyi.windowed.Bivariate, 3: pyi.windowed.Trivariate,
+           4: pyi.windowed.Quadrivariate}[nd]
+    cfg = getattr(cls, model)().with_boundary_mode(getattr(pyi.windowed.BoundaryConfig, boundary)())
+    if nd == 1:
+        return cfg.with_half_window_size(half[0])
+    cfg = cfg.with_half_window_size_x(half[0]).with_half_window_size_y(half[1])
+    if nd >= 3:
+        cfg = cfg.with_third_axis(getattr(pyi.windowed.AxisConfig, z_method)())
+    if nd >= 4:
+        cfg = cfg.with_fourth_axis(getattr(pyi.windowed.AxisConfig, u_method)())
+    return cfg
+
+
+@pytest.mark.parametrize("model", MODELS)
+def test_univariate_models(pyi, ref, model):
+    """core.univariate / univariate_derivative on regular periodic, irregular
+    and descending 1-D grids, window sizes 2 .. 10, both boundary modes."""
+    fz = axes_zoo.f64_axes()
+    specs = {"lon": (np.arange(72) * 5.0, dict(period=360.0), False), "irr": fz["lat_irregular"],
+             "desc": fz["lat_desc"]}
+    for aname, spec in specs.items():
+        (ga,), (ca,) = _axes(pyi, ref, [spec])
+        d = ca.describe()
+        g = _field((d["size"],), "float64", nan=0.001 if aname == "irr" else 0.0)
+        grid = pyi.Grid1D(ga, g)
+        rng = np.random.default_rng(11)
+        x = rng.uniform(d["min_value"] - 30, d["max_value"] + 30, 20_000)
+        x[::37] = np.nan
+        for half in (1, 2, 3, 5):
+            for boundary in ("undef", "shrink"):
+                cfg = _cfg(pyi, 1, model, (half,), boundary)
+                for deriv in (False, True):
+                    fn = pyi.core.univariate_derivative if deriv else pyi.core.univariate
+                    got = fn(grid, x, cfg)
+                    want, _ = ref.windowed_nd([ca], g, x, method=model, half_x=half, boundary=boundary,
+                                              num_threads=0, derivative=deriv)
+                    exact = close(got, want, 50.0, f"{model} {aname} half={half} {boundary} d={deriv}")
+                    assert exact == 1.0, (model, aname, half, boundary, deriv, exact)
+
+
+@pytest.mark.parametrize("model", SPATIAL)
+@pytest.mark.parametrize("boundary", ["undef", "shrink"])
+def test_bivariate_models(pyi, ref, model, boundary):
+    fz = axes_zoo.f64_axes()
+    for dtype, nan, xs, ys in (("float64", 0.0, (np.arange(72) * 5.0, dict(period=360.0), False),
+                                (-87.5 + np.arange(36) * 5.0, {}, False)),
+                               ("float32", 0.002, fz["lon_180"], fz["lat_irregular"]),
+                               ("int16", 0.0, (np.arange(72) * 5.0, {}, False), fz["small_irregular"])):
+        (gx, gy), caxes = _axes(pyi, ref, [xs, ys])
+        ds = [c.describe() for c in caxes]
+        g = _field((ds[0]["size"], ds[1]["size"]), dtype, nan=nan)
+        grid = pyi.Grid(gx, gy, g)
+        q = _queries(2, 20_000, 21, xr=(ds[0]["min_value"] - 200, ds[0]["max_value"] + 200),
+                     yr=(ds[1]["min_value"] - 3, ds[1]["max_value"] + 3))
+        for half in ((3, 3), (2, 4), (1, 1), (5, 2)):
+            if model == "c_spline_periodic" and (half[0] != half[1] or boundary == "shrink"):
+                # The reference's CSplinePeriodic only re-sizes its system when it
+                # grows (cspline_periodic.hpp:134-146): after a larger solve (rows
+                # vs columns of unequal windows) it solves a stale larger system,
+                # history dependent.  The product solves every system afresh
+                # (deviations); only equal windows are comparable.
+                continue
+            cfg = _cfg(pyi, 2, model, half, boundary)
+            got = pyi.core.bivariate(grid, q[0], q[1], cfg)
+            want, _ = ref.windowed_nd(caxes, g, q[0], q[1], method=model, half_x=half[0], half_y=half[1],
+                                      boundary=boundary, num_threads=0)
+            exact = close(got, want, 50.0, f"{model} {boundary} {half} {dtype}")
+            assert exact == 1.0, (model, boundary, half, dtype, exact)
+
+
+@pytest.mark.parametrize("model", ["bicubic", "bilinear", "c_spline", "akima", "steffen", "polynomial"])
+@pytest.mark.parametrize("z_kind,z_method", [("monthly30", "linear"), ("monthly30", "nearest"),
+                                             ("depth", "linear")])
+def test_trivariate_models(pyi, ref, model, z_kind, z_method):
+    fz, iz = axes_zoo.f64_axes(), axes_zoo.i64_axes()
+    zs = iz[z_kind] if z_kind in iz else fz[z_kind]
+    specs = [(np.arange(72) * 5.0, dict(period=360.0), False), (-87.5 + np.arange(36) * 5.0, {}, False), zs]
+    gaxes, caxes = _axes(pyi, ref, specs)
+    ds = [c.describe() for c in caxes]
+    for dtype, nan in (("float32", 0.001), ("float64", 0.0)):
+        g = _field(tuple(d["size"] for d in ds), dtype, nan=nan)
+        grid = pyi.Grid(*gaxes, g)
+        q = _queries(3, 15_000, 5, z_f64=z_kind not in iz)
+        for boundary in ("undef", "shrink"):
+            cfg = _cfg(pyi, 3, model, (3, 3), boundary, z_method=z_method)
+            z = q[2].view("datetime64[ns]") if grid.has_temporal_axis else q[2]
+            got = pyi.core.trivariate(grid, q[0], q[1], z, cfg)
+            want, _ = ref.windowed_nd(caxes, g, q[0], q[1], q[2], method=model, boundary=boundary,
+                                      num_threads=0, z_method=0 if z_method == "linear" else 1)
+            exact = close(got, want, 50.0, f"{model} {z_kind} {z_method} {boundary} {dtype}")
+            assert exact == 1.0, (model, z_kind, z_method, boundary, dtype, exact)
+
+
+@pytest.mark.parametrize("model", ["bicubic", "bilinear", "c_spline_not_a_knot", "linear", "akima_periodic"])
+@pytest.mark.parametrize("methods", [("linear", "linear"), ("nearest", "linear"), ("linear", "nearest")])
+def test_quadrivariate_models(pyi, ref, model, methods):
+    iz = axes_zoo.i64_axes()
+    specs = [(np.arange(36) * 10.0, dict(period=360.0), False), (-85.0 + np.arange(18) * 10.0, {}, False),
+             iz["monthly30"], (np.round(5500.0 * (np.arange(9) / 8) ** 2.2, 1), {}, False)]
+    gaxes, caxes = _axes(pyi, ref, specs)
+    ds = [c.describe() for c in caxes]
+    for dtype in ("float32", "float64"):
+        g = _field(tuple(d["size"] for d in ds), dtype, nan=0.0005)
+        grid = pyi.Grid(*gaxes, g)
+        q = _queries(4, 10_000, 6)
+        cfg = _cfg(pyi, 4, model, (3, 2), "shrink", z_method=methods[0], u_method=methods[1])
+        got = pyi.core.quadrivariate(grid, q[0], q[1], q[2].view("datetime64[ns]"), q[3], cfg)
+        want, _ = ref.windowed_nd(caxes, g, q[0], q[1], q[2], q[3], method=model, half_x=3, half_y=2,
+                                  boundary="shrink", num_threads=0, z_method=0 if methods[0] == "linear" else 1,
+                                  u_method=0 if methods[1] == "linear" else 1)
+        exact = close(got, want, 50.0, f"{model} {methods} {dtype}")
+        assert exact == 1.0, (model, methods, dtype, exact)
+
+
+def test_windowed_nd_bounds_error_and_device_tensors(pyi, ref):
+    import torch
+    iz = axes_zoo.i64_axes()
+    specs = [(np.arange(72) * 5.0, {}, False), (-87.5 + np.arange(36) * 5.0, {}, False), iz["monthly30"]]
+    gaxes, caxes = _axes(pyi, ref, specs)
+    ds = [c.describe() for c in caxes]
+    g = _field(tuple(d["size"] for d in ds), "float64")
+    grid = pyi.Grid(*gaxes, g)
+    q = _queries(3, 4000, 8)
+    want = ref.windowed_nd(caxes, g, q[0], q[1], q[2], method="steffen", bounds_error=True, num_threads=3)[1]
+    assert want is not None
+    cfg = pyi.windowed.Trivariate.steffen().with_bounds_error(True)
+    with pytest.raises(IndexError) as ei:
+        pyi.core.trivariate(grid, q[0], q[1], q[2].view("datetime64[ns]"), cfg)
+    assert str(ei.value) == want[2]
+    # z out of bounds only
+    x, y = np.full(10, 100.0), np.full(10, 0.0)
+    z = np.full(10, ds[2]["min_value"] + 5, dtype=np.int64)
+    z[6] = ds[2]["max_value"] + 10
+    want = ref.windowed_nd(caxes, g, x, y, z, method="bicubic", bounds_error=True)[1]
+    assert want[0] == 6 and want[1] == 2
+    with pytest.raises(IndexError) as ei:
+        pyi.trivariate(grid, x, y, z.view("datetime64[ns]"), "bicubic", bounds_error=True)
+    # the oracle drives math::Axis<int64> (integer repr); the product formats the
+    # coordinate like the reference's TemporalAxis (math/temporal_axis.hpp:80-83)
+    assert str(ei.value) == ("2021-11-27T00:00:00.000000010 is out of bounds for axis z "
+                             "[2021-01-01T00:00:00.000000000, ..., 2021-11-27T00:00:00.000000000]")
+    # device tensors == host arrays
+    host = pyi.trivariate(grid, q[0], q[1], q[2].view("datetime64[ns]"), "akima", third_axis="nearest")
+    dev = pyi.trivariate(grid, torch.from_numpy(q[0]).cuda(), torch.from_numpy(q[1]).cuda(),
+                         torch.from_numpy(q[2]).cuda(), "akima", third_axis="nearest")
+    assert dev.is_cuda and np.array_equal(host, dev.cpu().numpy(), equal_nan=True)
+
+
+def test_windowed_nd_api_errors(pyi):
+    lon, lat = np.arange(72) * 5.0, -87.5 + np.arange(36) * 5.0
+    grid2 = pyi.Grid(pyi.Axis(lon, period=360.0), pyi.Axis(lat), np.zeros((72, 36)))
+    grid1 = pyi.Grid1D(pyi.Axis(lon), np.zeros(72, dtype=np.float32))
+    assert pyi.univariate(grid1, np.array([12.0])).dtype == np.float32
+    with pytest.raises(ValueError, match="univariate requires 1D grid, got 2D"):
+        pyi.univariate(grid2, np.zeros(3))
+    with pytest.raises(ValueError, match="Unknown windowed method"):
+        pyi.univariate(grid1, np.zeros(3), "bicubic2")
+    with pytest.raises(TypeError, match="not valid for geometric method"):
+        pyi.bivariate(grid2, np.zeros(3), np.zeros(3), "bilinear", half_window_size_x=2)
+    with pytest.raises(AttributeError):
+        pyi.windowed.Univariate.bicubic()
+    out = pyi.bivariate(grid2, np.zeros(0), np.zeros(0), "steffen")
+    assert out.shape == (0,) and out.dtype == np.float64
