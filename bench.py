@@ -33,7 +33,11 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-BYTES_PER_POINT = {"bilinear": 24, "bicubic": 24, "trivariate": 60, "quadrivariate": 100}
+BYTES_PER_POINT = {"bilinear": 24, "bicubic": 24, "trivariate": 60, "quadrivariate": 100,
+                   # K6: streams only; the windows are compute / L2 work
+                   "c_spline2d": 24, "bicubic3d": 28}
+# windowed workloads: fitting model of the public API
+WINDOWED = {"bicubic": "bicubic", "c_spline2d": "c_spline", "bicubic3d": "bicubic"}
 METRIC = "Mpoints/s"
 
 
@@ -53,7 +57,7 @@ def parse():
 
 def default_points(workload: str) -> int:
     return {"bilinear": 1_000_000_000, "bicubic": 100_000_000, "trivariate": 100_000_000,
-            "quadrivariate": 100_000_000}[workload]
+            "quadrivariate": 100_000_000, "c_spline2d": 20_000_000, "bicubic3d": 20_000_000}[workload]
 
 
 def ncu_traffic(workload, n):
@@ -65,7 +69,7 @@ def ncu_traffic(workload, n):
         with open(path) as f:
             e = json.load(f)[workload]
         return {"bytes_per_launch": e["dram_bytes_per_point"] * n, "dram_bytes_per_point": e["dram_bytes_per_point"],
-                "source": e["source"]}
+                "source": e["source"], "secondary": e.get("secondary")}
     except Exception:
         return None
 
@@ -85,9 +89,9 @@ def build_host_case(workload: str):
     """Axis values + grid array (numpy) of the workload."""
     syn = __import__("importlib").import_module("pangeo-pyinterp_b200.synthetic")
     lon, lat = syn.lon_axis_values(), syn.lat_axis_values()
-    if workload in ("bilinear", "bicubic"):
+    if workload in ("bilinear", "bicubic", "c_spline2d"):
         return dict(nd=2, lon=lon, lat=lat, grid=syn.field(lon, lat), dtype="f64")
-    if workload == "trivariate":
+    if workload in ("trivariate", "bicubic3d"):
         t = syn.time_axis_values(365)
         return dict(nd=3, lon=lon, lat=lat, time=t, grid=syn.field(lon, lat, nz=365, dtype="float32", noise=0.0),
                     dtype="f32")
@@ -106,6 +110,8 @@ def workload_name(workload, n):
     shape = {"bilinear": "bivariate bilinear f64 Grid2D 1440x720 circular lon",
              "bicubic": "bivariate bicubic (6x6 window) f64 Grid2D 1440x720 circular lon",
              "trivariate": "trivariate bilinear f32 Grid3D 1440x720x365 int64 TemporalAxis",
+             "c_spline2d": "bivariate windowed c_spline (6x6 window) f64 Grid2D 1440x720 circular lon",
+             "bicubic3d": "trivariate windowed bicubic (6x6 window, linear in time) f32 Grid3D 1440x720x365",
              "quadrivariate": "quadrivariate bilinear f32 Grid4D 1440x720x12x50 time on z, irregular depth on u"}
     return f"{shape[workload]}, {n:.3g} uniform random points per GPU"
 
@@ -128,6 +134,9 @@ def cpu_run(case, workload, q, threads=0):
         t0 = time.perf_counter()
         if workload == "bicubic":
             out, _ = o.windowed2d(axes, case["grid"], qq[0], qq[1], num_threads=threads, stateless=False)
+        elif workload in WINDOWED:
+            out, _ = o.windowed_nd(axes, case["grid"], *qq, method=WINDOWED[workload], num_threads=threads,
+                                   stateless=False)
         else:
             out, _ = o.geometric(axes, case["grid"], *qq, num_threads=threads)
         return out, time.perf_counter() - t0
@@ -304,13 +313,21 @@ def main():
     if rank == 0 and not args.no_cpu:
         q = host_queries(case, 1_000_000, 1001)
         _, run = cpu_run(case, args.workload, None)
-        if args.workload == "bicubic":
+        if args.workload in WINDOWED:
             sys.path.insert(0, os.path.join(ROOT, "oracle"))
             import orc
             o = orc.Oracle("reference" if orc.available("reference") else "port")
-            want, _ = o.windowed2d([o.axis(case["lon"], period=360.0), o.axis(case["lat"])], case["grid"], q[0], q[1],
-                                   num_threads=0, stateless=True)
-            got = pyi.bivariate(grid, q[0], q[1], "bicubic")
+            oaxes = [o.axis(case["lon"], period=360.0), o.axis(case["lat"])]
+            qq = list(q)
+            if nd >= 3:
+                oaxes.append(o.axis(case["time"].astype("datetime64[ns]").astype(np.int64)))
+                qq[2] = qq[2].view("datetime64[ns]")
+            if args.workload == "bicubic":
+                want, _ = o.windowed2d(oaxes, case["grid"], q[0], q[1], num_threads=0, stateless=True)
+            else:
+                want, _ = o.windowed_nd(oaxes, case["grid"], *q, method=WINDOWED[args.workload], num_threads=0,
+                                        stateless=True)
+            got = {2: pyi.bivariate, 3: pyi.trivariate}[nd](grid, *qq, WINDOWED[args.workload])
         else:
             want, _ = run(q)
             fn = {2: pyi.bivariate, 3: pyi.trivariate, 4: pyi.quadrivariate}[nd]
@@ -340,8 +357,8 @@ def main():
     if nd >= 4:
         coords.append(torch.rand(n, dtype=torch.float64, device=dev, generator=gen).mul_(5610.0).sub_(10.0))
     fn = {2: pyi.core.bivariate, 3: pyi.core.trivariate, 4: pyi.core.quadrivariate}[nd]
-    if args.workload == "bicubic":
-        cfg = pyi.windowed.Bivariate.bicubic()
+    if args.workload in WINDOWED:
+        cfg = getattr({2: pyi.windowed.Bivariate, 3: pyi.windowed.Trivariate}[nd], WINDOWED[args.workload])()
     else:
         cfg = {2: pyi.geometric.Bivariate, 3: pyi.geometric.Trivariate, 4: pyi.geometric.Quadrivariate}[nd].bilinear()
 
@@ -391,7 +408,7 @@ def main():
     if nd >= 3:
         hq[2] = hq[2].view("datetime64[ns]")
     api = {2: pyi.bivariate, 3: pyi.trivariate, 4: pyi.quadrivariate}[nd]
-    method = "bicubic" if args.workload == "bicubic" else "bilinear"
+    method = WINDOWED.get(args.workload, "bilinear")
     grid._resident = True
     for _ in range(2):
         r = api(grid, *hq, method)
@@ -428,7 +445,8 @@ def main():
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": (tr or {}).get("bytes_per_launch"), "traffic_detail": tr,
                          "peak_source": peak_src,
-                         "bytes_per_point": bpp, "kernel_ms": k_ms},
+                         "bytes_per_point": bpp, "kernel_ms": k_ms,
+                         "secondary": (tr or {}).get("secondary")},
             "clocks": clk.summary(),
         }
         if world == 1 and not args.no_cpu:
