@@ -44,7 +44,8 @@ typedef enum pyi_status {
   PYI_BAD_ARG = 3,    /* invalid argument / unsupported combination */
   PYI_NO_DEVICE = 4,  /* no CUDA device: the product path refuses to run */
   PYI_CUDA_ERROR = 5, /* a CUDA call failed, see pyi_last_error() */
-  PYI_NOMEM = 6
+  PYI_NOMEM = 6,
+  PYI_OVERFLOW = 7    /* checked int64 arithmetic overflowed (reference: std::overflow_error) */
 } pyi_status;
 
 /* ---- enumerations ---------------------------------------------------------- */
@@ -81,6 +82,23 @@ typedef enum pyi_spatial_method {
 } pyi_spatial_method;
 /* the two boundary modes the reference exposes, config/windowed.hpp:88-98 */
 typedef enum pyi_boundary { PYI_BOUNDARY_UNDEF = 0, PYI_BOUNDARY_SHRINK = 1 } pyi_boundary;
+/* numpy datetime64 / timedelta64 units, values of dateutils::DType::Resolution
+ * (dateutils.hpp:186-200) */
+typedef enum pyi_resolution {
+  PYI_RES_YEAR = 0,
+  PYI_RES_MONTH = 1,
+  PYI_RES_WEEK = 2,
+  PYI_RES_DAY = 3,
+  PYI_RES_HOUR = 4,
+  PYI_RES_MINUTE = 5,
+  PYI_RES_SECOND = 6,
+  PYI_RES_MILLISECOND = 7,
+  PYI_RES_MICROSECOND = 8,
+  PYI_RES_NANOSECOND = 9,
+  PYI_RES_PICOSECOND = 10,
+  PYI_RES_FEMTOSECOND = 11,
+  PYI_RES_ATTOSECOND = 12
+} pyi_resolution;
 /* where caller buffers live */
 typedef enum pyi_mem { PYI_MEM_HOST = 0, PYI_MEM_DEVICE = 1 } pyi_mem;
 
@@ -245,6 +263,16 @@ int pyi_windowed(const pyi_grid *grid, const pyi_windowed_nd_config *cfg,
                  int64_t n, const double *x, const double *y, const void *z,
                  const double *u, void *out, int mem, int64_t *oob_index,
                  int *oob_axis, void *stream);
+
+/* dateutils::convert (dateutils.hpp:821-935): n int64 datetime64 / timedelta64
+ * values from resolution `src` to resolution `dst` (pyi_resolution), the
+ * pre-step of TemporalAxis::cast_to_int64 (src/pybind/temporal_axis.cpp:78-98,
+ * 216-220).  in == out is allowed.  Returns PYI_OVERFLOW when the reference's
+ * checked arithmetic would throw: overflow_index = lowest offending value,
+ * overflow_op = 1 multiplication / 2 addition (the reference's two messages). */
+int pyi_datetime_convert(int src, int dst, int64_t n, const int64_t *in,
+                         int64_t *out, int mem, int64_t *overflow_index,
+                         int *overflow_op, void *stream);
 
 /* Reference text "{coord} is out of bounds for axis {x|y|z|u} [{min}, ...,
  * {max}]" (pybind/grid.hpp:367-370). `coord` points to a double or an int64

@@ -51,6 +51,7 @@ _SIG = {
                                   C.c_int64, _P, _P, _P, _P, _P, C.POINTER(C.c_int64), C.POINTER(C.c_int),
                                   C.c_char_p, C.c_size_t]),
     "orc_univariate": (C.c_double, [C.c_int, _P, _P, C.c_int, C.c_double, C.c_int]),
+    "orc_datetime_convert": (C.c_int, [C.c_int, C.c_int, C.c_int64, _P, _P, C.c_char_p, C.c_size_t]),
     "orc_eval2d_f64": (C.c_double, [C.c_int, C.c_int, C.c_int] + [C.c_double] * 10),
     "orc_eval2d_f32": (C.c_float, [C.c_int, C.c_int, C.c_int] + [C.c_float] * 10),
     "orc_axis_interp_f64": (C.c_double, [C.c_int] + [C.c_double] * 5),
@@ -235,6 +236,18 @@ class Oracle:
         ya = np.ascontiguousarray(ya, dtype=np.float64)
         m = _abi.SPATIAL_METHODS[method] if isinstance(method, str) else int(method)
         return self.lib.orc_univariate(m, _ptr(xa), _ptr(ya), xa.size, x, int(derivative))
+
+    def datetime_convert(self, values, src: str, dst: str):
+        """dateutils::convert between numpy units; raises OverflowError like the reference."""
+        v = np.ascontiguousarray(values, dtype=np.int64)
+        out = np.empty_like(v)
+        msg = C.create_string_buffer(256)
+        st = self.lib.orc_datetime_convert(_abi.RESOLUTIONS[src], _abi.RESOLUTIONS[dst], v.size, _ptr(v),
+                                           _ptr(out), msg, 256)
+        if st == _abi.PYI_OVERFLOW:
+            raise OverflowError(msg.value.decode())
+        assert st == 0, (st, msg.value)
+        return out
 
     def window_eval(self, method, xa, ya, za, x, y):
         xa = np.ascontiguousarray(xa, dtype=np.float64)

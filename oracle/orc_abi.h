@@ -105,6 +105,12 @@ int orc_windowed_nd(int ndim, const orc_axis *const *axes, int dtype,
 double orc_univariate(int method, const double *xa, const double *ya, int n,
                       double x, int derivative);
 
+/* dateutils::convert (dateutils.hpp:821-935) between pyi_resolution units.
+ * PYI_OVERFLOW with the reference's message when its checked arithmetic
+ * throws.  Reference build only. */
+int orc_datetime_convert(int src, int dst, int64_t n, const int64_t *in,
+                         int64_t *out, char *msg, size_t msglen);
+
 /* ---- scalar probes used by the golden-vector tests ------------------------ */
 /* geometric evaluators (math/interpolate/geometric/bivariate.hpp).
  * cartesian != 0: the Cartesian point type the reference unit tests use;

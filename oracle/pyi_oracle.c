@@ -1485,3 +1485,9 @@ double orc_univariate(int method, const double *xa, const double *ya, int n,
   (void)method; (void)xa; (void)ya; (void)n; (void)x; (void)derivative;
   return NAN;
 }
+
+int orc_datetime_convert(int src, int dst, int64_t n, const int64_t *in,
+                         int64_t *out, char *msg, size_t msglen) {
+  (void)src; (void)dst; (void)n; (void)in; (void)out; (void)msg; (void)msglen;
+  return PYI_BAD_ARG;
+}

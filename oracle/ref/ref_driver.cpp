@@ -1184,3 +1184,30 @@ extern "C" double orc_univariate(int method, const double* xa, const double* ya,
   ref::Vector<double> vy = Eigen::Map<const ref::Vector<double>>(ya, n);
   return derivative ? f->derivative(vx, vy, x) : (*f)(vx, vy, x);
 }
+
+// ---------------------------------------------------------------------------
+// dateutils::convert (dateutils.hpp:821-935), the reference's own function
+// ---------------------------------------------------------------------------
+#include "pyinterp/dateutils.hpp"
+
+extern "C" int orc_datetime_convert(int src, int dst, int64_t n,
+                                    const int64_t* in, int64_t* out, char* msg,
+                                    size_t msglen) {
+  static const char* units[] = {"Y",  "M",  "W",  "D",  "h",  "m", "s",
+                                "ms", "us", "ns", "ps", "fs", "as"};
+  if (src < 0 || src > 12 || dst < 0 || dst > 12) return PYI_BAD_ARG;
+  try {
+    const ref::dateutils::DType s(std::string("datetime64[") + units[src] + "]");
+    const ref::dateutils::DType d(std::string("datetime64[") + units[dst] + "]");
+    ref::Vector<int64_t> v = Eigen::Map<const ref::Vector<int64_t>>(in, n);
+    ref::dateutils::convert(v, s, d);
+    std::copy(v.data(), v.data() + n, out);
+  } catch (const std::overflow_error& e) {
+    set_err(msg, msglen, e.what());
+    return PYI_OVERFLOW;
+  } catch (const std::exception& e) {
+    set_err(msg, msglen, e.what());
+    return PYI_BAD_ARG;
+  }
+  return PYI_OK;
+}

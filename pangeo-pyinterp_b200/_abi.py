@@ -11,7 +11,7 @@ import ctypes as C
 import os
 
 # ---- status codes / enums (include/pyinterp_b200.h) -------------------------
-PYI_OK, PYI_OOB, PYI_BAD_SHAPE, PYI_BAD_ARG, PYI_NO_DEVICE, PYI_CUDA_ERROR, PYI_NOMEM = range(7)
+PYI_OK, PYI_OOB, PYI_BAD_SHAPE, PYI_BAD_ARG, PYI_NO_DEVICE, PYI_CUDA_ERROR, PYI_NOMEM, PYI_OVERFLOW = range(8)
 PYI_AXIS_REGULAR, PYI_AXIS_IRREGULAR = 0, 1
 PYI_COORD_F64, PYI_COORD_I64 = 0, 1
 PYI_BILINEAR, PYI_IDW, PYI_NEAREST = 0, 1, 2
@@ -22,6 +22,9 @@ SPATIAL_METHODS = {
     "bicubic": 0, "bilinear": 1, "akima": 2, "akima_periodic": 3, "c_spline": 4,
     "c_spline_not_a_knot": 5, "c_spline_periodic": 6, "linear": 7, "steffen": 8, "polynomial": 9,
 }
+#: numpy datetime unit -> pyi_resolution (dateutils::DType::Resolution)
+RESOLUTIONS = {"Y": 0, "M": 1, "W": 2, "D": 3, "h": 4, "m": 5, "s": 6, "ms": 7, "us": 8, "ns": 9,
+               "ps": 10, "fs": 11, "as": 12}
 PYI_BOUNDARY_UNDEF, PYI_BOUNDARY_SHRINK = 0, 1
 PYI_MEM_HOST, PYI_MEM_DEVICE = 0, 1
 PYI_GRID_DEFAULT, PYI_GRID_PACK_CELLS, PYI_GRID_BORROW_DEVICE = 0, 1, 2
@@ -123,6 +126,7 @@ SIGNATURES = {
                                  _I64P, _IP, _P]),
     "pyi_windowed": (C.c_int, [_P, C.POINTER(WindowedNdConfig), C.c_int64, _P, _P, _P, _P, _P, C.c_int,
                                _I64P, _IP, _P]),
+    "pyi_datetime_convert": (C.c_int, [C.c_int, C.c_int, C.c_int64, _P, _P, C.c_int, _I64P, _IP, _P]),
     "pyi_format_bounds_error": (C.c_int, [_P, C.c_int, _P, C.c_char_p, C.c_size_t]),
     "pyi_launch_count": (C.c_int64, []),
 }
@@ -166,6 +170,8 @@ def check(status: int, what: str = "") -> None:
     text = msg.decode() if msg else ""
     names = {PYI_BAD_SHAPE: "BAD_SHAPE", PYI_BAD_ARG: "BAD_ARG", PYI_NO_DEVICE: "NO_DEVICE",
              PYI_CUDA_ERROR: "CUDA_ERROR", PYI_NOMEM: "NOMEM"}
+    if status == PYI_OVERFLOW:
+        raise OverflowError(text)  # std::overflow_error (dateutils.hpp:55,99)
     if status in (PYI_BAD_SHAPE, PYI_BAD_ARG):
         raise ValueError(f"{what}: {text or names[status]}")
     raise PyiError(f"{what}: {names.get(status, status)}: {text}")

@@ -285,19 +285,26 @@ class TemporalAxis(Axis):
         return np.timedelta64(int(v), np.datetime_data(self._dtype)[0])
 
     def cast_to_int64(self, array) -> np.ndarray:
-        """TemporalAxis::cast_to_int64 (src/pybind/temporal_axis.cpp:216-220):
-        values converted to the axis resolution, viewed as int64 (NaT =
-        INT64_MIN)."""
+        """TemporalAxis::cast_to_int64 (src/pybind/temporal_axis.cpp:78-98,216-220):
+        values converted to the axis resolution, as int64.  A resolution change
+        runs dateutils::convert on the device (pyi_datetime_convert); like the
+        reference it raises OverflowError when the checked arithmetic overflows
+        (NaT included: the reference converts it as the integer it is)."""
         if _is_torch_cuda(array):
             return array
         a = np.asarray(array)
         if a.dtype.kind in "iu" and a.dtype.itemsize == 8:
             return np.ascontiguousarray(a.astype(np.int64, copy=False))
         if a.dtype.kind != self._dtype.kind:
-            raise ValueError(f"array must be a numpy {self._dtype.name} array, got {a.dtype}")
-        if a.dtype != self._dtype:
-            a = a.astype(self._dtype)
-        return np.ascontiguousarray(a.view(np.int64))
+            # temporal_axis.cpp:84-89
+            raise ValueError(f"array must be of type {'datetime64' if self._dtype.kind == 'M' else 'timedelta64'}, "
+                             f"got {a.dtype}")
+        src = np.datetime_data(a.dtype)[0]
+        dst = np.datetime_data(self._dtype)[0]
+        v = np.ascontiguousarray(a.view(np.int64))
+        if src == dst:
+            return v
+        return convert_resolution(v, src, dst)
 
     def cast_to_temporal_axis(self, array):
         return self.cast_to_int64(array).view(self._dtype)
@@ -312,6 +319,34 @@ class TemporalAxis(Axis):
         names = {"Y": "years", "M": "months", "W": "weeks", "D": "days", "h": "hours", "m": "minutes",
                  "s": "seconds", "ms": "milliseconds", "us": "microseconds", "ns": "nanoseconds"}
         return f"{int(value)} {names.get(np.datetime_data(self._dtype)[0], '')}".strip()
+
+
+def convert_resolution(values, src: str, dst: str):
+    """``dateutils::convert`` (dateutils.hpp:821-935) on the device: int64
+    datetime64 / timedelta64 values from numpy unit ``src`` to unit ``dst``.
+    numpy int64 arrays or CUDA int64 tensors; returns the same kind."""
+    lib = _lib()
+    for u in (src, dst):
+        if u not in _abi.RESOLUTIONS:
+            raise ValueError(f"unknown datetime unit {u!r}")
+    oi, op = C.c_int64(-1), C.c_int(0)
+    if _is_torch_cuda(values):
+        import torch
+        if values.dtype != torch.int64:
+            raise ValueError("values must be an int64 tensor")
+        v = values.contiguous()
+        out = torch.empty_like(v)
+        with torch.cuda.device(v.device):
+            st = lib.pyi_datetime_convert(_abi.RESOLUTIONS[src], _abi.RESOLUTIONS[dst], v.numel(), v.data_ptr(),
+                                          out.data_ptr(), _abi.PYI_MEM_DEVICE, C.byref(oi), C.byref(op),
+                                          torch.cuda.current_stream(v.device).cuda_stream)
+    else:
+        v = np.ascontiguousarray(values, dtype=np.int64)
+        out = np.empty_like(v)
+        st = lib.pyi_datetime_convert(_abi.RESOLUTIONS[src], _abi.RESOLUTIONS[dst], v.size, _np_ptr(v),
+                                      _np_ptr(out), _abi.PYI_MEM_HOST, C.byref(oi), C.byref(op), None)
+    _abi.check(st, "convert_resolution")
+    return out
 
 
 # ---------------------------------------------------------------------------

@@ -932,6 +932,65 @@ int pyi_windowed(const pyi_grid* grid, const pyi_windowed_nd_config* cfg, int64_
   return PYI_OK;
 }
 
+int pyi_datetime_convert(int src, int dst, int64_t n, const int64_t* in, int64_t* out, int mem,
+                         int64_t* overflow_index, int* overflow_op, void* stream) {
+  int st = require_device();
+  if (st != PYI_OK) return st;
+  if (src < PYI_RES_YEAR || src > PYI_RES_ATTOSECOND || dst < PYI_RES_YEAR ||
+      dst > PYI_RES_ATTOSECOND || n < 0) {
+    return fail(PYI_BAD_ARG, "pyi_datetime_convert: unknown resolution");
+  }
+  if (n > 0 && (!in || !out)) return fail(PYI_BAD_SHAPE, "pyi_datetime_convert: missing array");
+  if (n == 0) return PYI_OK;
+  auto report = [&](unsigned long long key) {
+    if (key == pyi::kNoOob) return static_cast<int>(PYI_OK);
+    if (overflow_index) *overflow_index = static_cast<int64_t>(key >> 2);
+    if (overflow_op) *overflow_op = static_cast<int>(key & 3);
+    // dateutils.hpp:55,99
+    return fail(PYI_OVERFLOW, (key & 3) == 1 ? "integer overflow in multiplication"
+                                              : "integer overflow in addition");
+  };
+  Workspace& ws = workspace();
+  std::lock_guard<std::recursive_mutex> ws_lock(ws.mu);
+  st = ws.ensure(0, 0);
+  if (st != PYI_OK) return st;
+  if (mem == PYI_MEM_DEVICE) {
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if (src == dst) {  // dateutils.hpp:824-826
+      if (in != out) {
+        PYI_CUDA(cudaMemcpyAsync(out, in, static_cast<size_t>(n) * 8, cudaMemcpyDeviceToDevice, s));
+      }
+      return PYI_OK;
+    }
+    PYI_CUDA(cudaMemsetAsync(ws.oob_key, 0xff, sizeof(unsigned long long), s));
+    cudaError_t e = pyi::launch_datetime_convert(reinterpret_cast<const long long*>(in),
+                                                 reinterpret_cast<long long*>(out), n, 0, src, dst,
+                                                 ws.oob_key, s);
+    if (e != cudaSuccess) return cuda_fail(e, "datetime kernel");
+    unsigned long long key = pyi::kNoOob;
+    PYI_CUDA(cudaMemcpyAsync(&key, ws.oob_key, sizeof(key), cudaMemcpyDeviceToHost, s));
+    PYI_CUDA(cudaStreamSynchronize(s));
+    return report(key);
+  }
+  if (src == dst) {
+    if (in != out) std::memcpy(out, in, static_cast<size_t>(n) * 8);
+    return PYI_OK;
+  }
+  std::vector<Column> cols(2);
+  cols[0].host_in = in;
+  cols[1].host_out = out;
+  PYI_CUDA(cudaMemset(ws.oob_key, 0xff, sizeof(unsigned long long)));
+  st = run_pipeline(n, cols, [&](cudaStream_t s, long long begin, long long count, char* dev) {
+    return pyi::launch_datetime_convert(reinterpret_cast<const long long*>(dev + cols[0].dev_off),
+                                        reinterpret_cast<long long*>(dev + cols[1].dev_off), count,
+                                        begin, src, dst, ws.oob_key, s);
+  });
+  if (st != PYI_OK) return st;
+  unsigned long long key = pyi::kNoOob;
+  PYI_CUDA(cudaMemcpy(&key, ws.oob_key, sizeof(key), cudaMemcpyDeviceToHost));
+  return report(key);
+}
+
 // "{coord} is out of bounds for axis {label} [{min}, ..., {max}]"
 // (pybind/grid.hpp:362-371).  Doubles are printed like std::format("{}"):
 // shortest round-trip digits via std::to_chars.  int64 coordinates are printed

@@ -81,6 +81,10 @@ cudaError_t launch_windowed2d(const WinParams& p, cudaStream_t stream);
 cudaError_t launch_windowed_nd(const WinNdParams& p, cudaStream_t stream);
 cudaError_t launch_find_indexes(const FindParams& p, cudaStream_t stream);
 cudaError_t launch_find_index(const FindParams& p, cudaStream_t stream);
+// dateutils::convert on the device (pyi_datetime.cu); bad_key = (index << 2) | op
+cudaError_t launch_datetime_convert(const long long* in, long long* out, long long n,
+                                    long long index_base, int src, int dst,
+                                    unsigned long long* bad_key, cudaStream_t stream);
 // cell packing (2-D .. 4-D): the 2^ndim corners of every cell contiguous, in the
 // result type; x + 1 wraps (periodic seam cell), the other axes clamp.
 cudaError_t launch_pack_cells(const void* data, int dtype, int ndim, const int* shape, void* packed,

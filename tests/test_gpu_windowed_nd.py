@@ -205,3 +205,70 @@ def test_windowed_nd_api_errors(pyi):
         pyi.windowed.Univariate.bicubic()
     out = pyi.bivariate(grid2, np.zeros(0), np.zeros(0), "steffen")
     assert out.shape == (0,) and out.dtype == np.float64
+
+
+UNITS = ["Y", "M", "W", "D", "h", "m", "s", "ms", "us", "ns"]
+
+
+def test_datetime_resolution_conversion(pyi, ref):
+    """dateutils::convert on the device (pyi_datetime_convert) against the
+    reference's own function, every pair of numpy units, negative and large
+    values, host arrays and device tensors."""
+    import torch
+    rng = np.random.default_rng(3)
+    overflowed = 0
+    for src in UNITS:
+        span = {"Y": 3000, "M": 40_000, "W": 200_000, "D": 1_500_000, "h": 30_000_000, "m": 2_000_000_000}.get(
+            src, 2 ** 45)
+        v = rng.integers(-span, span, 20_000, dtype=np.int64)
+        v[:8] = [0, -1, 1, -span, span, 59, -61, 86_399]
+        for dst in UNITS:
+            try:
+                want = ref.datetime_convert(v, src, dst)
+            except OverflowError as e:  # e.g. +-3000 years in nanoseconds
+                with pytest.raises(OverflowError, match=str(e)):
+                    pyi.core.convert_resolution(v, src, dst)
+                overflowed += 1
+                continue
+            got = pyi.core.convert_resolution(v, src, dst)
+            assert got.dtype == np.int64 and np.array_equal(got, want), (src, dst)
+            dev = pyi.core.convert_resolution(torch.from_numpy(v).cuda(), src, dst)
+            assert dev.is_cuda and np.array_equal(dev.cpu().numpy(), want), (src, dst)
+    assert 0 < overflowed < 30
+    # numpy agrees wherever it defines the conversion without ambiguity (finer units)
+    d = rng.integers(-100_000, 100_000, 1000).astype("datetime64[D]")
+    assert np.array_equal(pyi.core.convert_resolution(d.view(np.int64), "D", "ns"),
+                          d.astype("datetime64[ns]").view(np.int64))
+
+
+def test_datetime_conversion_overflow(pyi, ref):
+    v = np.array([5, 2 ** 40, -3, 2 ** 62], dtype=np.int64)
+    with pytest.raises(OverflowError) as want:
+        ref.datetime_convert(v, "s", "ns")
+    with pytest.raises(OverflowError) as got:
+        pyi.core.convert_resolution(v, "s", "ns")
+    assert str(want.value) in str(got.value)
+    # NaT is converted as the integer it is (no special case, dateutils.hpp:845-933)
+    nat = np.array([np.iinfo(np.int64).min], dtype=np.int64)
+    assert np.array_equal(pyi.core.convert_resolution(nat, "ns", "s"), ref.datetime_convert(nat, "ns", "s"))
+    with pytest.raises(OverflowError):
+        pyi.core.convert_resolution(nat, "s", "ns")
+
+
+def test_temporal_axis_casts_on_device(pyi, ref):
+    """trivariate with datetime64[s] / [D] coordinates on a datetime64[ns]
+    axis: the pre-step of grid_dispatch.hpp:190-195 runs on the GPU."""
+    t = np.datetime64("2021-01-01", "ns") + np.arange(20) * np.timedelta64(1, "D")
+    lon, lat = np.arange(72) * 5.0, -87.5 + np.arange(36) * 5.0
+    g = _field((72, 36, 20), "float64")
+    grid = pyi.Grid(pyi.Axis(lon, period=360.0), pyi.Axis(lat), pyi.TemporalAxis(t), g)
+    rng = np.random.default_rng(1)
+    x, y = rng.uniform(0, 360, 5000), rng.uniform(-80, 80, 5000)
+    zs = (np.datetime64("2021-01-01", "s") + rng.integers(0, 19 * 86400, 5000).astype("timedelta64[s]"))
+    got = pyi.trivariate(grid, x, y, zs)
+    caxes = [ref.axis(lon, period=360.0), ref.axis(lat), ref.axis(t.astype(np.int64))]
+    want, _ = ref.geometric(caxes, g, x, y, ref.datetime_convert(zs.view(np.int64), "s", "ns"), num_threads=0)
+    assert np.array_equal(got, want, equal_nan=True) and np.isfinite(got).all()
+    assert np.array_equal(grid.z.cast_to_int64(zs), zs.astype("datetime64[ns]").view(np.int64))
+    with pytest.raises(ValueError, match="must be of type datetime64"):
+        grid.z.cast_to_int64(np.arange(3).astype("timedelta64[s]"))
