@@ -30,6 +30,26 @@ def _is_torch_cuda(a: Any) -> bool:
     return type(a).__module__.startswith("torch") and getattr(a, "is_cuda", False)
 
 
+def _device_view(a: Any):
+    """Zero-copy view of a device array as a CUDA tensor: torch
+    CUDA tensors pass through; objects exposing ``__cuda_array_interface__``
+    (CuPy, Numba, RAPIDS) or a CUDA ``__dlpack__`` are wrapped without a copy.
+    Host objects are returned unchanged."""
+    if _is_torch_cuda(a) or isinstance(a, np.ndarray):
+        return a
+    if hasattr(a, "__cuda_array_interface__"):
+        import torch
+        return torch.as_tensor(a, device="cuda")
+    if hasattr(a, "__dlpack__") and hasattr(a, "__dlpack_device__"):
+        try:
+            if int(a.__dlpack_device__()[0]) == 2:  # kDLCUDA
+                import torch
+                return torch.from_dlpack(a)
+        except Exception:
+            pass
+    return a
+
+
 def _np_ptr(a: np.ndarray):
     return a.ctypes.data_as(_P)
 
@@ -184,6 +204,7 @@ class Axis:
 
     # -- lookups (GPU) -------------------------------------------------------
     def _coords(self, coordinates):
+        coordinates = _device_view(coordinates)
         if _is_torch_cuda(coordinates):
             return coordinates
         return np.ascontiguousarray(coordinates, dtype=np.float64)
@@ -290,6 +311,7 @@ class TemporalAxis(Axis):
         runs dateutils::convert on the device (pyi_datetime_convert); like the
         reference it raises OverflowError when the checked arithmetic overflows
         (NaT included: the reference converts it as the integer it is)."""
+        array = _device_view(array)
         if _is_torch_cuda(array):
             return array
         a = np.asarray(array)
@@ -367,6 +389,7 @@ class Grid:
         if len(args) < 2 or len(args) > 5:
             raise ValueError("Grid(x[, y[, z[, u]]], array): 1 to 4 axes and an array are required")
         *axes, array = args
+        array = _device_view(array)
         for a in axes:
             if not isinstance(a, Axis):
                 raise TypeError("axes must be Axis or TemporalAxis instances")
@@ -508,6 +531,7 @@ def _run(grid: Grid, cfg, coords: list, windowed: bool):
     lib = _lib()
     nd = grid.ndim
     names = ["x", "y", "z", "u"][:nd]
+    coords = [_device_view(c) for c in coords]
     on_device = any(_is_torch_cuda(c) for c in coords)
     oi, oa = C.c_int64(-1), C.c_int(-1)
     # 2-D bicubic / bilinear keep the dedicated entry point (and its fast kernel)

@@ -523,3 +523,33 @@ def test_windowed2d_bounds_error_in_late_chunk(pyi, orc_best):
     import torch
     with pytest.raises(IndexError):
         pyi.bivariate(grid, torch.from_numpy(x).cuda(), torch.from_numpy(y).cuda(), "bicubic", bounds_error=True)
+
+
+class _CudaArray:
+    """A foreign device array: only ``__cuda_array_interface__`` (what CuPy /
+    Numba / RAPIDS objects expose), backed by a torch allocation."""
+
+    def __init__(self, t):
+        self._t = t
+        self.__cuda_array_interface__ = t.__cuda_array_interface__
+
+
+def test_cuda_array_interface_inputs(pyi):
+    """Zero-copy front end: coordinates and the grid given as
+    foreign device arrays; the result stays on the device."""
+    import torch
+    s = pyi.synthetic
+    lon, lat = s.lon_axis_values(144), s.lat_axis_values(72)
+    g = s.field(lon, lat)
+    x, y = s.queries(100_000, 7)
+    host_grid = pyi.Grid(pyi.Axis(lon, period=360.0), pyi.Axis(lat), g)
+    want = pyi.bivariate(host_grid, x, y)
+    dg = _CudaArray(torch.from_numpy(g).cuda())
+    grid = pyi.Grid(pyi.Axis(lon, period=360.0), pyi.Axis(lat), dg)
+    dx, dy = _CudaArray(torch.from_numpy(x).cuda()), _CudaArray(torch.from_numpy(y).cuda())
+    got = pyi.bivariate(grid, dx, dy)
+    assert got.is_cuda and np.array_equal(got.cpu().numpy(), want, equal_nan=True)
+    got = pyi.bivariate(grid, dx, dy, "c_spline")
+    assert np.array_equal(got.cpu().numpy(), pyi.bivariate(host_grid, x, y, "c_spline"), equal_nan=True)
+    idx = grid.x.find_indexes(dx)
+    assert idx.is_cuda and np.array_equal(idx.cpu().numpy(), host_grid.x.find_indexes(x))
