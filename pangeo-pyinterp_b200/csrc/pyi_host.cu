@@ -7,6 +7,7 @@
 
 #include <algorithm>
 #include <charconv>
+#include <cmath>
 #include <cstdio>
 #include <cstring>
 #include <memory>
@@ -403,6 +404,10 @@ struct pyi_grid {
   bool borrowed{false};
   void* d_packed{nullptr};
   unsigned long long* d_oob{nullptr};  // for device-memory calls
+  // natural-spline constants of a uniformly spaced six-node window on x / y
+  // (regular axes with moderate steps), computed on the device at creation
+  double u6[2][24]{};
+  int u6_ok[2]{0, 0};
 };
 
 extern "C" {
@@ -596,6 +601,24 @@ pyi_grid* pyi_grid_create(int ndim, const pyi_axis* const* axes, int dtype, cons
   }
   cudaError_t e = cudaMalloc(reinterpret_cast<void**>(&g->d_oob), sizeof(unsigned long long));
   if (e != cudaSuccess) return set(cuda_fail(e, "cudaMalloc(oob)"));
+  if (ndim >= 2) {
+    double* d_tmp = nullptr;
+    if (cudaMalloc(reinterpret_cast<void**>(&d_tmp), 24 * sizeof(double)) == cudaSuccess) {
+      for (int k = 0; k < 2; ++k) {
+        const pyi::DAxis& a = g->dax[k];
+        const double mag = std::fabs(a.step);
+        if (a.kind != 0 || a.coord_i64 || !(mag >= 9.313225746154785e-10 && mag <= 1073741824.0)) {
+          continue;  // irregular, or outside the spacing range of the fast path (2^-30 .. 2^30)
+        }
+        if (pyi::launch_spline6_uniform(a.step, d_tmp, nullptr) == cudaSuccess &&
+            cudaMemcpy(g->u6[k], d_tmp, 24 * sizeof(double), cudaMemcpyDeviceToHost) == cudaSuccess) {
+          g->u6_ok[k] = 1;
+        }
+      }
+      cudaFree(d_tmp);
+    }
+    cudaGetLastError();
+  }
   pyi_grid* raw = g.release();
   if (flags & PYI_GRID_PACK_CELLS) {
     int st = pyi_grid_pack(raw);
@@ -778,6 +801,10 @@ int pyi_windowed2d(const pyi_grid* grid, const pyi_windowed_config* cfg, int64_t
   p.half_y = cfg->half_y;
   p.boundary = cfg->boundary;
   p.bounds_error = cfg->bounds_error;
+  for (int a = 0; a < 2; ++a) {
+    p.u6_ok[a] = grid->u6_ok[a];
+    std::memcpy(p.u6[a], grid->u6[a], sizeof(p.u6[a]));
+  }
   const size_t out_elem = result_is_f64(grid->dtype) ? 8 : 4;
   if (mem == PYI_MEM_DEVICE) {
     cudaStream_t s = static_cast<cudaStream_t>(stream);
@@ -867,6 +894,10 @@ int pyi_windowed(const pyi_grid* grid, const pyi_windowed_nd_config* cfg, int64_
   p.z_method = cfg->z_method;
   p.u_method = cfg->u_method;
   p.derivative = cfg->derivative;
+  for (int a = 0; a < 2; ++a) {
+    p.u6_ok[a] = grid->u6_ok[a];
+    std::memcpy(p.u6[a], grid->u6[a], sizeof(p.u6[a]));
+  }
   const size_t out_elem = result_is_f64(grid->dtype) ? 8 : 4;
   if (mem == PYI_MEM_DEVICE) {
     cudaStream_t s = static_cast<cudaStream_t>(stream);

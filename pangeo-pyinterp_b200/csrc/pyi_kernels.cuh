@@ -44,6 +44,10 @@ struct WinParams {
   const double* y;
   void* out;
   unsigned long long* oob_key;
+  // 24 natural-spline constants of a uniformly spaced six-node window on x / y
+  // (pyi_fastwin.cuh: spline6_uniform_kernel), valid when u6_ok
+  double u6[2][24];
+  int32_t u6_ok[2];
 };
 
 // windowed path on 1-D .. 4-D grids, every fitting model (pyi_windowed_nd.cuh)
@@ -66,6 +70,8 @@ struct WinNdParams {
   const double* u;
   void* out;
   unsigned long long* oob_key;
+  double u6[2][24];  // forwarded to K4 (2-D bicubic)
+  int32_t u6_ok[2];
 };
 
 struct FindParams {
@@ -79,6 +85,8 @@ struct FindParams {
 cudaError_t launch_geometric(const GeoParams& p, cudaStream_t stream);
 cudaError_t launch_windowed2d(const WinParams& p, cudaStream_t stream);
 cudaError_t launch_windowed_nd(const WinNdParams& p, cudaStream_t stream);
+// the 24 constants of a uniformly spaced six-node spline (device buffer of 24 doubles)
+cudaError_t launch_spline6_uniform(double step, double* out24, cudaStream_t stream);
 cudaError_t launch_find_indexes(const FindParams& p, cudaStream_t stream);
 cudaError_t launch_find_index(const FindParams& p, cudaStream_t stream);
 // dateutils::convert on the device (pyi_datetime.cu); bad_key = (index << 2) | op

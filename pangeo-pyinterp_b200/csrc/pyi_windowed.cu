@@ -44,6 +44,10 @@ cudaError_t launch_windowed_nd(const WinNdParams& p, cudaStream_t stream) {
     q.y = p.y;
     q.out = p.out;
     q.oob_key = p.oob_key;
+    for (int a = 0; a < 2; ++a) {
+      q.u6_ok[a] = p.u6_ok[a];
+      for (int k = 0; k < 24; ++k) q.u6[a][k] = p.u6[a][k];
+    }
     return launch_windowed2d(q, stream);
   }
   const int hy = p.ndim >= 2 ? p.half_y : 1;
