@@ -136,7 +136,7 @@ def cpu_run(case, workload, q, threads=0):
             out, _ = o.windowed2d(axes, case["grid"], qq[0], qq[1], num_threads=threads, stateless=False)
         elif workload in WINDOWED:
             out, _ = o.windowed_nd(axes, case["grid"], *qq, method=WINDOWED[workload], num_threads=threads,
-                                   stateless=False)
+                                   stateless=kind != "reference")  # the C port has the stateless form only
         else:
             out, _ = o.geometric(axes, case["grid"], *qq, num_threads=threads)
         return out, time.perf_counter() - t0

@@ -91,9 +91,9 @@ int orc_windowed2d(const orc_axis *const *axes, int dtype, const void *data,
 
 /* windowed::pybind::univariate / univariate_derivative / bivariate /
  * trivariate / quadrivariate with every fitting model
- * (pybind/windowed/*.hpp, math/interpolate/factory.hpp).  Reference build only
- * (liboracle_ref.so); the plain-C library returns PYI_BAD_ARG for the models
- * it does not restate. */
+ * (pybind/windowed/{uni,bi,tri,quadri}variate.hpp, math/interpolate/factory.hpp).
+ * stateless == 0 (the reference's per-thread cache) is served by the reference
+ * build only; the plain-C library returns PYI_BAD_ARG for it. */
 int orc_windowed_nd(int ndim, const orc_axis *const *axes, int dtype,
                     const void *data, const pyi_windowed_nd_config *cfg,
                     int stateless, int64_t n, const double *x, const double *y,
@@ -101,13 +101,13 @@ int orc_windowed_nd(int ndim, const orc_axis *const *axes, int dtype,
                     int64_t *oob_index, int *oob_axis, char *msg,
                     size_t msglen);
 /* One univariate model on explicit nodes: value or derivative at x
- * (math/interpolate/univariate/*.hpp). method: pyi_spatial_method >= 2. */
+ * (math/interpolate/univariate/ headers). method: pyi_spatial_method >= 2. */
 double orc_univariate(int method, const double *xa, const double *ya, int n,
                       double x, int derivative);
 
 /* dateutils::convert (dateutils.hpp:821-935) between pyi_resolution units.
  * PYI_OVERFLOW with the reference's message when its checked arithmetic
- * throws.  Reference build only. */
+ * throws. */
 int orc_datetime_convert(int src, int dst, int64_t n, const int64_t *in,
                          int64_t *out, char *msg, size_t msglen);
 

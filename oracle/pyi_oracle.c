@@ -1463,31 +1463,5 @@ int orc_windowed2d(const orc_axis *const *axes, int dtype, const void *data,
 }
 
 
-/* ---- models this plain-C restatement does not cover ------------------------
- * The univariate fitting models of the windowed path beyond the natural cubic
- * spline, and the windowed 1-D / 3-D / 4-D drivers, are checked against the
- * reference build (oracle/_ref/liboracle_ref.so, ref/ref_driver.cpp) and the
- * golden vectors generated from it (tests/golden/ref_vectors_wnd_*.npz). */
-int orc_windowed_nd(int ndim, const orc_axis *const *axes, int dtype,
-                    const void *data, const pyi_windowed_nd_config *cfg,
-                    int stateless, int64_t n, const double *x, const double *y,
-                    const void *z, const double *u, void *out,
-                    int64_t *oob_index, int *oob_axis, char *msg,
-                    size_t msglen) {
-  (void)ndim; (void)axes; (void)dtype; (void)data; (void)cfg; (void)stateless;
-  (void)n; (void)x; (void)y; (void)z; (void)u; (void)out; (void)oob_index;
-  (void)oob_axis; (void)msg; (void)msglen;
-  return PYI_BAD_ARG;
-}
-
-double orc_univariate(int method, const double *xa, const double *ya, int n,
-                      double x, int derivative) {
-  (void)method; (void)xa; (void)ya; (void)n; (void)x; (void)derivative;
-  return NAN;
-}
-
-int orc_datetime_convert(int src, int dst, int64_t n, const int64_t *in,
-                         int64_t *out, char *msg, size_t msglen) {
-  (void)src; (void)dst; (void)n; (void)in; (void)out; (void)msg; (void)msglen;
-  return PYI_BAD_ARG;
-}
+/* the rest of the windowed path and dateutils::convert */
+#include "pyi_oracle_wnd.inc"

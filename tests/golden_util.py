@@ -130,34 +130,32 @@ CASES = {
                                                      None, False)], n=3000, seed=20),
 }
 
-# windowed 1-D .. 4-D with every fitting model.  These are
-# produced and checked by the reference build only (ref_only): the plain-C
-# restatement does not cover them.
+# windowed 1-D .. 4-D with every fitting model
 WND_MODELS = ("akima", "akima_periodic", "c_spline", "c_spline_not_a_knot", "c_spline_periodic", "linear",
               "steffen", "polynomial")
 for _k, _m in enumerate(WND_MODELS):
-    CASES[f"wnd1d_{_m}"] = dict(kind="wnd", ref_only=True, axes=[(LON72, 360.0, False)], dtype="float64",
+    CASES[f"wnd1d_{_m}"] = dict(kind="wnd", axes=[(LON72, 360.0, False)], dtype="float64",
                                 method=_m, half=(3, 1), boundary="undef", n=1500, seed=30 + _k,
                                 derivative=bool(_k % 2))
-    CASES[f"wnd2d_{_m}"] = dict(kind="wnd", ref_only=True, axes=[(LON72, 360.0, False), (LAT_IRR, None, False)],
+    CASES[f"wnd2d_{_m}"] = dict(kind="wnd", axes=[(LON72, 360.0, False), (LAT_IRR, None, False)],
                                 dtype="float64" if _k % 2 == 0 else "float32", method=_m,
                                 half=(3, 3) if _k % 3 else (4, 3), boundary="shrink" if _k % 2 else "undef",
                                 n=1500, seed=40 + _k)
-CASES["wnd3d_bicubic_time"] = dict(kind="wnd", ref_only=True,
+CASES["wnd3d_bicubic_time"] = dict(kind="wnd",
                                    axes=[(LON72, 360.0, False), (LAT36, None, False), (TIME10, None, False)],
                                    dtype="float32", method="bicubic", half=(3, 3), boundary="undef", n=1500,
                                    seed=50)
-CASES["wnd3d_c_spline_nearest_z"] = dict(kind="wnd", ref_only=True,
+CASES["wnd3d_c_spline_nearest_z"] = dict(kind="wnd",
                                          axes=[(LON72, 360.0, False), (LAT36, None, False),
                                                (np.arange(6) * 2.5, None, False)],
                                          dtype="float64", method="c_spline", half=(3, 3), boundary="shrink",
                                          n=1500, seed=51, z_method=1)
-CASES["wnd4d_bilinear_depth"] = dict(kind="wnd", ref_only=True,
+CASES["wnd4d_bilinear_depth"] = dict(kind="wnd",
                                      axes=[(LON72[::2], 360.0, False), (LAT36[::2], None, False),
                                            (TIME10[:6], None, False), (DEPTH8, None, False)],
                                      dtype="float32", method="bilinear", half=(2, 2), boundary="undef", n=1500,
                                      seed=52)
-CASES["wnd4d_akima_f64"] = dict(kind="wnd", ref_only=True,
+CASES["wnd4d_akima_f64"] = dict(kind="wnd",
                                 axes=[(LON72[::2], 360.0, False), (LAT36[::2], None, False),
                                       (np.arange(5) * 1.0, None, False), (DEPTH8, None, True)],
                                 dtype="float64", method="akima", half=(3, 3), boundary="undef", n=1200, seed=53,

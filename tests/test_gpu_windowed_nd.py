@@ -1,10 +1,10 @@
 """GPU parity of the widened windowed path: every fitting
 model on 1-D .. 4-D grids through the public API / C-ABI (pyi_windowed)
-against the reference build (oracle/_ref: the reference's own
-InterpolationCache, factory(), Univariate / BivariateBase classes) on identical
-seeded inputs.  The plain-C restatement does not cover these models; without
-the reference build the committed golden vectors (test_gpu_golden.py, cases
-wnd*) are the check.
+against the CPU oracle on identical seeded inputs: the reference build
+(oracle/_ref: the reference's own InterpolationCache, factory(), Univariate /
+BivariateBase classes) when present, else the plain-C restatement pinned
+bit-for-bit against it (tests/test_oracle_vs_ref.py); the committed golden
+vectors (test_gpu_golden.py, cases wnd*) are checked as well.
 
 Bar: NaN positions identical, values within 1e-12 (float64) / 1e-5 (float32)
 relative with the field-scale guard; the fraction of bit-identical values is
@@ -14,7 +14,7 @@ import numpy as np
 import pytest
 
 import axes_zoo
-from test_gpu_parity import close, _mk_axis, _queries
+from test_gpu_parity import close, _mk_axis, _queries, orc_best  # noqa: F401
 
 pytestmark = pytest.mark.gpu
 
@@ -56,7 +56,8 @@ def _cfg(pyi, nd, model, half, boundary, z_method="linear", u_method="linear"):
 
 
 @pytest.mark.parametrize("model", MODELS)
-def test_univariate_models(pyi, ref, model):
+def test_univariate_models(pyi, orc_best, model):
+    ref = orc_best
     """core.univariate / univariate_derivative on regular periodic, irregular
     and descending 1-D grids, window sizes 2 .. 10, both boundary modes."""
     fz = axes_zoo.f64_axes()
@@ -84,7 +85,8 @@ def test_univariate_models(pyi, ref, model):
 
 @pytest.mark.parametrize("model", SPATIAL)
 @pytest.mark.parametrize("boundary", ["undef", "shrink"])
-def test_bivariate_models(pyi, ref, model, boundary):
+def test_bivariate_models(pyi, orc_best, model, boundary):
+    ref = orc_best
     fz = axes_zoo.f64_axes()
     for dtype, nan, xs, ys in (("float64", 0.0, (np.arange(72) * 5.0, dict(period=360.0), False),
                                 (-87.5 + np.arange(36) * 5.0, {}, False)),
@@ -115,7 +117,8 @@ def test_bivariate_models(pyi, ref, model, boundary):
 @pytest.mark.parametrize("model", ["bicubic", "bilinear", "c_spline", "akima", "steffen", "polynomial"])
 @pytest.mark.parametrize("z_kind,z_method", [("monthly30", "linear"), ("monthly30", "nearest"),
                                              ("depth", "linear")])
-def test_trivariate_models(pyi, ref, model, z_kind, z_method):
+def test_trivariate_models(pyi, orc_best, model, z_kind, z_method):
+    ref = orc_best
     fz, iz = axes_zoo.f64_axes(), axes_zoo.i64_axes()
     zs = iz[z_kind] if z_kind in iz else fz[z_kind]
     specs = [(np.arange(72) * 5.0, dict(period=360.0), False), (-87.5 + np.arange(36) * 5.0, {}, False), zs]
@@ -137,7 +140,8 @@ def test_trivariate_models(pyi, ref, model, z_kind, z_method):
 
 @pytest.mark.parametrize("model", ["bicubic", "bilinear", "c_spline_not_a_knot", "linear", "akima_periodic"])
 @pytest.mark.parametrize("methods", [("linear", "linear"), ("nearest", "linear"), ("linear", "nearest")])
-def test_quadrivariate_models(pyi, ref, model, methods):
+def test_quadrivariate_models(pyi, orc_best, model, methods):
+    ref = orc_best
     iz = axes_zoo.i64_axes()
     specs = [(np.arange(36) * 10.0, dict(period=360.0), False), (-85.0 + np.arange(18) * 10.0, {}, False),
              iz["monthly30"], (np.round(5500.0 * (np.arange(9) / 8) ** 2.2, 1), {}, False)]
@@ -156,7 +160,8 @@ def test_quadrivariate_models(pyi, ref, model, methods):
         assert exact == 1.0, (model, methods, dtype, exact)
 
 
-def test_windowed_nd_bounds_error_and_device_tensors(pyi, ref):
+def test_windowed_nd_bounds_error_and_device_tensors(pyi, orc_best):
+    ref = orc_best
     import torch
     iz = axes_zoo.i64_axes()
     specs = [(np.arange(72) * 5.0, {}, False), (-87.5 + np.arange(36) * 5.0, {}, False), iz["monthly30"]]
@@ -210,7 +215,8 @@ def test_windowed_nd_api_errors(pyi):
 UNITS = ["Y", "M", "W", "D", "h", "m", "s", "ms", "us", "ns"]
 
 
-def test_datetime_resolution_conversion(pyi, ref):
+def test_datetime_resolution_conversion(pyi, orc_best):
+    ref = orc_best
     """dateutils::convert on the device (pyi_datetime_convert) against the
     reference's own function, every pair of numpy units, negative and large
     values, host arrays and device tensors."""
@@ -241,7 +247,8 @@ def test_datetime_resolution_conversion(pyi, ref):
                           d.astype("datetime64[ns]").view(np.int64))
 
 
-def test_datetime_conversion_overflow(pyi, ref):
+def test_datetime_conversion_overflow(pyi, orc_best):
+    ref = orc_best
     v = np.array([5, 2 ** 40, -3, 2 ** 62], dtype=np.int64)
     with pytest.raises(OverflowError) as want:
         ref.datetime_convert(v, "s", "ns")
@@ -255,7 +262,8 @@ def test_datetime_conversion_overflow(pyi, ref):
         pyi.core.convert_resolution(nat, "s", "ns")
 
 
-def test_temporal_axis_casts_on_device(pyi, ref):
+def test_temporal_axis_casts_on_device(pyi, orc_best):
+    ref = orc_best
     """trivariate with datetime64[s] / [D] coordinates on a datetime64[ns]
     axis: the pre-step of grid_dispatch.hpp:190-195 runs on the GPU."""
     t = np.datetime64("2021-01-01", "ns") + np.arange(20) * np.timedelta64(1, "D")

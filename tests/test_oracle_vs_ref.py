@@ -251,3 +251,82 @@ def test_scalar_probes(port, ref):
         for d in (False, True):
             p, r = port.cspline(xa, ya, x, d), ref.cspline(xa, ya, x, d)
             assert p == r or (np.isnan(p) and np.isnan(r))
+
+
+# ---- the widened windowed path and dateutils::convert ----
+WND_MODELS = ["akima", "akima_periodic", "c_spline", "c_spline_not_a_knot", "c_spline_periodic", "linear",
+              "steffen", "polynomial"]
+
+
+@pytest.mark.parametrize("model", WND_MODELS)
+def test_univariate_models_port_vs_ref(port, ref, model):
+    """Every model on explicit nodes, 2 .. 16 of them, value and derivative
+    (covers the Eigen packet traversals restated for polynomial / periodic)."""
+    rng = np.random.default_rng(21)
+    for n in range(2, 17):
+        for trial in range(30):
+            xa = np.sort(rng.uniform(-5, 5, n))
+            if trial % 7 == 3 and n > 3:
+                xa[2] = xa[1]  # duplicate abscissa
+            ya = rng.normal(size=n) * 10
+            for x in (rng.uniform(xa[0], xa[-1]), xa[n // 2], xa[0], xa[-1], xa[-1] + 1.0):
+                for der in (False, True):
+                    a, b = port.univariate(model, xa, ya, x, der), ref.univariate(model, xa, ya, x, der)
+                    assert (a == b) or (a != a and b != b), (model, n, trial, x, der, a, b)
+
+
+@pytest.mark.parametrize("nd", [1, 2, 3, 4])
+@pytest.mark.parametrize("boundary", ["undef", "shrink"])
+def test_windowed_nd_port_vs_ref(port, ref, nd, boundary):
+    rng = np.random.default_rng(nd)
+    T0, DAY = axes_zoo.T0, axes_zoo.DAY
+    specs = [(np.arange(36) * 10.0, dict(period=360.0)), (np.degrees(np.arcsin(np.linspace(-0.99, 0.99, 20))), {}),
+             (T0 + np.arange(6, dtype=np.int64) * DAY, {}), (np.array([0.0, 5.0, 20.0, 100.0]), {})][:nd]
+    shape = tuple(len(s[0]) for s in specs)
+    n = 1500
+    q = [rng.uniform(-200, 500, n), rng.uniform(-95, 95, n),
+         rng.integers(T0 - DAY, T0 + 6 * DAY, n, dtype=np.int64), rng.uniform(-5, 105, n)][:nd]
+    q[0][::50] = np.nan
+    models = WND_MODELS if nd == 1 else ["bicubic", "bilinear"] + WND_MODELS
+    for dtype in ("float64", "float32", "int16"):
+        g = (rng.normal(size=shape) * 30).astype(dtype)
+        if dtype == "float32":
+            g[rng.random(shape) < 0.003] = np.nan
+        for model in models:
+            for half in ((3, 3), (2, 4)):
+                if model == "c_spline_periodic" and nd >= 2 and (half[0] != half[1] or boundary == "shrink"):
+                    continue  # reference solves a stale larger system (DESIGN.md section 4, deviation)
+                kw = dict(method=model, half_x=half[0], half_y=half[1], boundary=boundary, z_method=nd % 2,
+                          u_method=(nd + 1) % 2, derivative=(nd == 1 and half[0] == 2))
+                outs = []
+                for o in (port, ref):
+                    axes = [o.axis(v, **k) for v, k in specs]
+                    outs.append(o.windowed_nd(axes, g, *q, num_threads=2, **kw)[0])
+                _same(outs[0], outs[1])
+    # bounds error: same point, axis and message
+    errs = []
+    for o in (port, ref):
+        axes = [o.axis(v, **k) for v, k in specs]
+        errs.append(o.windowed_nd(axes, g, *q, method=models[-1], bounds_error=True, num_threads=3)[1])
+    if nd >= 2:
+        assert errs[0] is not None and errs[0] == errs[1]
+
+
+def test_datetime_convert_port_vs_ref(port, ref):
+    units = ["Y", "M", "W", "D", "h", "m", "s", "ms", "us", "ns", "ps"]
+    rng = np.random.default_rng(2)
+    for src in units:
+        span = {"Y": 2000, "M": 20_000, "W": 100_000, "D": 700_000}.get(src, 2 ** 40)
+        v = rng.integers(-span, span, 5000, dtype=np.int64)
+        v[:4] = [0, -1, 1, np.iinfo(np.int64).min if src in ("ns", "ps") else 7]
+        for dst in units:
+            res = []
+            for o in (port, ref):
+                try:
+                    res.append(o.datetime_convert(v, src, dst))
+                except OverflowError as e:
+                    res.append(str(e))
+            if isinstance(res[1], str):
+                assert res[0] == res[1], (src, dst)
+            else:
+                assert np.array_equal(res[0], res[1]), (src, dst)
