@@ -99,6 +99,11 @@ typedef enum pyi_resolution {
   PYI_RES_FEMTOSECOND = 11,
   PYI_RES_ATTOSECOND = 12
 } pyi_resolution;
+/* config::fill::FirstGuess (config/fill.hpp:18-23) */
+typedef enum pyi_first_guess {
+  PYI_FIRST_GUESS_ZONAL_AVERAGE = 0,
+  PYI_FIRST_GUESS_ZERO = 1
+} pyi_first_guess;
 /* where caller buffers live */
 typedef enum pyi_mem { PYI_MEM_HOST = 0, PYI_MEM_DEVICE = 1 } pyi_mem;
 
@@ -273,6 +278,27 @@ int pyi_windowed(const pyi_grid *grid, const pyi_windowed_nd_config *cfg,
 int pyi_datetime_convert(int src, int dst, int64_t n, const int64_t *in,
                          int64_t *out, int mem, int64_t *overflow_index,
                          int *overflow_op, void *stream);
+
+/* config::fill::GaussSeidel (config/fill.hpp:67-160,255-279), without
+ * num_threads (the device result does not depend on it, as the reference's) */
+typedef struct pyi_fill_config {
+  int32_t first_guess;      /* pyi_first_guess */
+  int32_t is_periodic;      /* x axis periodic (longitude) */
+  uint64_t max_iterations;
+  double epsilon;
+  double relaxation;
+} pyi_fill_config;
+
+/* fill::gauss_seidel (fill/gauss_seidel.hpp:166-211): the NaN cells of the
+ * row-major (nx, ny) grid (dtype PYI_F32 or PYI_F64) are replaced IN PLACE by
+ * the red-black relaxed solution of the Laplace equation.  iterations /
+ * max_residual are the reference's returned tuple (max_residual is exact for
+ * both dtypes).  Results are bit-identical to the reference whatever its
+ * thread count. */
+int pyi_fill_gauss_seidel(void *grid, int dtype, int64_t nx, int64_t ny,
+                          const pyi_fill_config *cfg, int mem,
+                          uint64_t *iterations, double *max_residual,
+                          void *stream);
 
 /* Reference text "{coord} is out of bounds for axis {x|y|z|u} [{min}, ...,
  * {max}]" (pybind/grid.hpp:367-370). `coord` points to a double or an int64

@@ -52,6 +52,12 @@ _SIG = {
                                   C.c_char_p, C.c_size_t]),
     "orc_univariate": (C.c_double, [C.c_int, _P, _P, C.c_int, C.c_double, C.c_int]),
     "orc_datetime_convert": (C.c_int, [C.c_int, C.c_int, C.c_int64, _P, _P, C.c_char_p, C.c_size_t]),
+    "orc_fill_gauss_seidel": (C.c_int, [_P, C.c_int, C.c_int64, C.c_int64, C.c_int, C.c_int, C.c_uint64,
+                                        C.c_double, C.c_double, C.c_int, C.POINTER(C.c_uint64),
+                                        C.POINTER(C.c_double), C.c_char_p, C.c_size_t]),
+    "orc_fill_multigrid": (C.c_int, [_P, C.c_int, C.c_int64, C.c_int64, C.c_int, C.c_int, C.c_uint64,
+                                     C.c_double, C.c_uint32, C.c_uint32, C.c_int, C.POINTER(C.c_uint64),
+                                     C.POINTER(C.c_double), C.c_char_p, C.c_size_t]),
     "orc_eval2d_f64": (C.c_double, [C.c_int, C.c_int, C.c_int] + [C.c_double] * 10),
     "orc_eval2d_f32": (C.c_float, [C.c_int, C.c_int, C.c_int] + [C.c_float] * 10),
     "orc_axis_interp_f64": (C.c_double, [C.c_int] + [C.c_double] * 5),
@@ -248,6 +254,33 @@ class Oracle:
             raise OverflowError(msg.value.decode())
         assert st == 0, (st, msg.value)
         return out
+
+    def _fill_args(self, grid):
+        assert isinstance(grid, np.ndarray) and grid.ndim == 2 and grid.flags.c_contiguous
+        assert grid.dtype in (np.float32, np.float64)
+        return _abi.DTYPES[grid.dtype.name], grid.shape[0], grid.shape[1]
+
+    def fill_gauss_seidel(self, grid, first_guess="zonal_average", is_periodic=True, max_iterations=2000,
+                          epsilon=1e-4, relaxation=1.0, num_threads=1):
+        """fill::gauss_seidel in place; returns (iterations, max_residual)."""
+        dt, nx, ny = self._fill_args(grid)
+        it, res, msg = C.c_uint64(0), C.c_double(0), C.create_string_buffer(256)
+        st = self.lib.orc_fill_gauss_seidel(_ptr(grid), dt, nx, ny, _abi.FIRST_GUESS[first_guess],
+                                            int(is_periodic), max_iterations, epsilon, relaxation,
+                                            num_threads, C.byref(it), C.byref(res), msg, 256)
+        assert st == 0, (st, msg.value)
+        return it.value, res.value
+
+    def fill_multigrid(self, grid, first_guess="zonal_average", is_periodic=True, max_iterations=100,
+                       epsilon=1e-4, pre_smooth=2, post_smooth=2, num_threads=1):
+        """fill::multigrid in place; returns (iterations, max_residual)."""
+        dt, nx, ny = self._fill_args(grid)
+        it, res, msg = C.c_uint64(0), C.c_double(0), C.create_string_buffer(256)
+        st = self.lib.orc_fill_multigrid(_ptr(grid), dt, nx, ny, _abi.FIRST_GUESS[first_guess],
+                                         int(is_periodic), max_iterations, epsilon, pre_smooth,
+                                         post_smooth, num_threads, C.byref(it), C.byref(res), msg, 256)
+        assert st == 0, (st, msg.value)
+        return it.value, res.value
 
     def window_eval(self, method, xa, ya, za, x, y):
         xa = np.ascontiguousarray(xa, dtype=np.float64)

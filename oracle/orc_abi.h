@@ -111,6 +111,23 @@ double orc_univariate(int method, const double *xa, const double *ya, int n,
 int orc_datetime_convert(int src, int dst, int64_t n, const int64_t *in,
                          int64_t *out, char *msg, size_t msglen);
 
+/* fill::gauss_seidel (fill/gauss_seidel.hpp:166-211) and fill::multigrid
+ * (fill/multi_grid.hpp:276-334) in place on a row-major (nx, ny) grid of dtype
+ * PYI_F32 / PYI_F64.  first_guess: pyi_first_guess.  num_threads <= 0: all
+ * cores (the result does not depend on it). */
+int orc_fill_gauss_seidel(void *grid, int dtype, int64_t nx, int64_t ny,
+                          int first_guess, int is_periodic,
+                          uint64_t max_iterations, double epsilon,
+                          double relaxation, int num_threads,
+                          uint64_t *iterations, double *max_residual, char *msg,
+                          size_t msglen);
+int orc_fill_multigrid(void *grid, int dtype, int64_t nx, int64_t ny,
+                       int first_guess, int is_periodic,
+                       uint64_t max_iterations, double epsilon,
+                       uint32_t pre_smooth, uint32_t post_smooth,
+                       int num_threads, uint64_t *iterations,
+                       double *max_residual, char *msg, size_t msglen);
+
 /* ---- scalar probes used by the golden-vector tests ------------------------ */
 /* geometric evaluators (math/interpolate/geometric/bivariate.hpp).
  * cartesian != 0: the Cartesian point type the reference unit tests use;

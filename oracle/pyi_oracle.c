@@ -1465,3 +1465,6 @@ int orc_windowed2d(const orc_axis *const *axes, int dtype, const void *data,
 
 /* the rest of the windowed path and dateutils::convert */
 #include "pyi_oracle_wnd.inc"
+
+/* grid filling */
+#include "pyi_oracle_fill.inc"

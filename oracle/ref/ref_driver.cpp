@@ -1211,3 +1211,102 @@ extern "C" int orc_datetime_convert(int src, int dst, int64_t n,
   }
   return PYI_OK;
 }
+
+// ---------------------------------------------------------------------------
+// fill::gauss_seidel / fill::multigrid (fill/gauss_seidel.hpp:166-211,
+// fill/multi_grid.hpp:276-334), the reference's own functions, in place on a
+// row-major (nx, ny) grid.  config/fill.hpp and Boost.Accumulators come from
+// ref/shim (see the headers there for why).
+// ---------------------------------------------------------------------------
+#include "pyinterp/fill/gauss_seidel.hpp"
+#include "pyinterp/fill/multi_grid.hpp"
+
+namespace {
+
+template <typename T, typename Config, typename Fn>
+int fill_run(void* grid, int64_t nx, int64_t ny, const Config& cfg, Fn&& fn,
+             uint64_t* iterations, double* max_residual) {
+  Eigen::Map<ref::RowMajorMatrix<T>> m(static_cast<T*>(grid), nx, ny);
+  auto [it, res] = fn(ref::EigenDRef<ref::RowMajorMatrix<T>>(m), cfg);
+  *iterations = it;
+  *max_residual = static_cast<double>(res);
+  return PYI_OK;
+}
+
+template <typename Config>
+void fill_base(Config& c, int first_guess, int is_periodic,
+               uint64_t max_iterations, double epsilon, int num_threads) {
+  c.first_guess_ = static_cast<ref::config::fill::FirstGuess>(first_guess);
+  c.is_periodic_ = is_periodic != 0;
+  c.max_iterations_ = static_cast<uint32_t>(max_iterations);
+  c.epsilon_ = epsilon;
+  c.num_threads_ = num_threads <= 0 ? std::thread::hardware_concurrency()
+                                    : static_cast<size_t>(num_threads);
+}
+
+}  // namespace
+
+extern "C" int orc_fill_gauss_seidel(void* grid, int dtype, int64_t nx,
+                                     int64_t ny, int first_guess,
+                                     int is_periodic, uint64_t max_iterations,
+                                     double epsilon, double relaxation,
+                                     int num_threads, uint64_t* iterations,
+                                     double* max_residual, char* msg,
+                                     size_t msglen) {
+  try {
+    ref::config::fill::GaussSeidel cfg;
+    fill_base(cfg, first_guess, is_periodic, max_iterations, epsilon,
+              num_threads);
+    cfg.relaxation_ = relaxation;
+    if (dtype == PYI_F32) {
+      return fill_run<float>(
+          grid, nx, ny, cfg,
+          [](auto g, const auto& c) { return ref::fill::gauss_seidel<float>(g, c); },
+          iterations, max_residual);
+    }
+    if (dtype == PYI_F64) {
+      return fill_run<double>(
+          grid, nx, ny, cfg,
+          [](auto g, const auto& c) { return ref::fill::gauss_seidel<double>(g, c); },
+          iterations, max_residual);
+    }
+    set_err(msg, msglen, "grid must be float32 or float64");
+    return PYI_BAD_ARG;
+  } catch (const std::exception& e) {
+    set_err(msg, msglen, e.what());
+    return PYI_BAD_ARG;
+  }
+}
+
+extern "C" int orc_fill_multigrid(void* grid, int dtype, int64_t nx, int64_t ny,
+                                  int first_guess, int is_periodic,
+                                  uint64_t max_iterations, double epsilon,
+                                  uint32_t pre_smooth, uint32_t post_smooth,
+                                  int num_threads, uint64_t* iterations,
+                                  double* max_residual, char* msg,
+                                  size_t msglen) {
+  try {
+    ref::config::fill::Multigrid cfg;
+    fill_base(cfg, first_guess, is_periodic, max_iterations, epsilon,
+              num_threads);
+    cfg.pre_smooth_ = pre_smooth;
+    cfg.post_smooth_ = post_smooth;
+    if (dtype == PYI_F32) {
+      return fill_run<float>(
+          grid, nx, ny, cfg,
+          [](auto g, const auto& c) { return ref::fill::multigrid<float>(g, c); },
+          iterations, max_residual);
+    }
+    if (dtype == PYI_F64) {
+      return fill_run<double>(
+          grid, nx, ny, cfg,
+          [](auto g, const auto& c) { return ref::fill::multigrid<double>(g, c); },
+          iterations, max_residual);
+    }
+    set_err(msg, msglen, "grid must be float32 or float64");
+    return PYI_BAD_ARG;
+  } catch (const std::exception& e) {
+    set_err(msg, msglen, e.what());
+    return PYI_BAD_ARG;
+  }
+}

@@ -1,0 +1,3 @@
+// TEST INFRASTRUCTURE ONLY: see ../accumulators.hpp
+#pragma once
+#include "../accumulators.hpp"

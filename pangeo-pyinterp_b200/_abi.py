@@ -25,6 +25,8 @@ SPATIAL_METHODS = {
 #: numpy datetime unit -> pyi_resolution (dateutils::DType::Resolution)
 RESOLUTIONS = {"Y": 0, "M": 1, "W": 2, "D": 3, "h": 4, "m": 5, "s": 6, "ms": 7, "us": 8, "ns": 9,
                "ps": 10, "fs": 11, "as": 12}
+#: pyi_first_guess (config::fill::FirstGuess, config/fill.hpp:18-23)
+FIRST_GUESS = {"zonal_average": 0, "zero": 1}
 PYI_BOUNDARY_UNDEF, PYI_BOUNDARY_SHRINK = 0, 1
 PYI_MEM_HOST, PYI_MEM_DEVICE = 0, 1
 PYI_GRID_DEFAULT, PYI_GRID_PACK_CELLS, PYI_GRID_BORROW_DEVICE = 0, 1, 2
@@ -99,6 +101,16 @@ class WindowedNdConfig(C.Structure):
     ]
 
 
+class FillConfig(C.Structure):
+    _fields_ = [
+        ("first_guess", C.c_int32),
+        ("is_periodic", C.c_int32),
+        ("max_iterations", C.c_uint64),
+        ("epsilon", C.c_double),
+        ("relaxation", C.c_double),
+    ]
+
+
 #: every symbol include/pyinterp_b200.h declares: name -> (restype, argtypes)
 _P = C.c_void_p
 _I64P = C.POINTER(C.c_int64)
@@ -127,6 +139,8 @@ SIGNATURES = {
     "pyi_windowed": (C.c_int, [_P, C.POINTER(WindowedNdConfig), C.c_int64, _P, _P, _P, _P, _P, C.c_int,
                                _I64P, _IP, _P]),
     "pyi_datetime_convert": (C.c_int, [C.c_int, C.c_int, C.c_int64, _P, _P, C.c_int, _I64P, _IP, _P]),
+    "pyi_fill_gauss_seidel": (C.c_int, [_P, C.c_int, C.c_int64, C.c_int64, C.POINTER(FillConfig), C.c_int,
+                                        C.POINTER(C.c_uint64), C.POINTER(C.c_double), _P]),
     "pyi_format_bounds_error": (C.c_int, [_P, C.c_int, _P, C.c_char_p, C.c_size_t]),
     "pyi_launch_count": (C.c_int64, []),
 }

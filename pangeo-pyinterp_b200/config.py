@@ -244,3 +244,85 @@ geometric = types.SimpleNamespace(Bivariate=_GBivariate, Trivariate=_GTrivariate
 windowed = types.SimpleNamespace(Univariate=_WUnivariate, Bivariate=_WBivariate,
                                  Trivariate=_WTrivariate, Quadrivariate=_WQuadrivariate,
                                  BoundaryConfig=BoundaryConfig, AxisConfig=AxisConfig)
+
+
+# ---------------------------------------------------------------------------
+# pyinterp.core.config.fill (config/fill.hpp, src/pybind/config.cpp:404-515)
+# ---------------------------------------------------------------------------
+import enum  # noqa: E402
+
+
+class FirstGuess(enum.IntEnum):
+    """config::fill::FirstGuess (config/fill.hpp:18-23)."""
+    ZONAL_AVERAGE = _abi.FIRST_GUESS["zonal_average"]
+    ZERO = _abi.FIRST_GUESS["zero"]
+
+
+class _FillBase:
+    """FillBase<Derived> (config/fill.hpp:67-160): immutable, ``with_*`` return
+    a copy; ``num_threads`` is accepted and ignored (the result of the
+    reference does not depend on it either)."""
+
+    _first_guess = FirstGuess.ZONAL_AVERAGE
+    _is_periodic = True
+    _max_iterations = 500
+    _epsilon = 1e-4
+    _num_threads = 0
+
+    def _with(self, name, value):
+        c = copy.copy(self)
+        setattr(c, name, value)
+        return c
+
+    def with_first_guess(self, value):
+        if not isinstance(value, FirstGuess):
+            raise TypeError("with_first_guess(): value must be a FirstGuess")
+        return self._with("_first_guess", value)
+
+    def with_is_periodic(self, value: bool):
+        return self._with("_is_periodic", bool(value))
+
+    def with_max_iterations(self, value: int):
+        value = int(value)
+        if not 0 <= value < 2 ** 32:  # uint32_t argument of the reference binding
+            raise TypeError("with_max_iterations(): value must fit an uint32")
+        return self._with("_max_iterations", value)
+
+    def with_epsilon(self, value: float):
+        return self._with("_epsilon", float(value))
+
+    def with_num_threads(self, value: int):
+        if int(value) < 0:
+            raise TypeError("with_num_threads(): value must be non-negative")
+        return self._with("_num_threads", int(value))
+
+    def first_guess(self):
+        return self._first_guess
+
+    def is_periodic(self) -> bool:
+        return self._is_periodic
+
+    def max_iterations(self) -> int:
+        return self._max_iterations
+
+    def epsilon(self) -> float:
+        return self._epsilon
+
+    def num_threads(self) -> int:
+        return self._num_threads
+
+
+class GaussSeidel(_FillBase):
+    """config::fill::GaussSeidel (config/fill.hpp:255-279)."""
+
+    _max_iterations = 2000
+    _relaxation = 1.0
+
+    def with_relaxation(self, value: float):
+        return self._with("_relaxation", float(value))
+
+    def relaxation(self) -> float:
+        return self._relaxation
+
+
+fill = types.SimpleNamespace(FirstGuess=FirstGuess, GaussSeidel=GaussSeidel)

@@ -1022,6 +1022,64 @@ int pyi_datetime_convert(int src, int dst, int64_t n, const int64_t* in, int64_t
   return report(key);
 }
 
+// fill::gauss_seidel (fill/gauss_seidel.hpp:166-211) in place.  Host grids are
+// staged through one device copy; everything else happens in pyi_fill.cu.
+int pyi_fill_gauss_seidel(void* grid, int dtype, int64_t nx, int64_t ny,
+                          const pyi_fill_config* cfg, int mem, uint64_t* iterations,
+                          double* max_residual, void* stream) {
+  int st = require_device();
+  if (st != PYI_OK) return st;
+  if (!cfg || !iterations || !max_residual) {
+    return fail(PYI_BAD_ARG, "pyi_fill_gauss_seidel: missing argument");
+  }
+  if (dtype != PYI_F32 && dtype != PYI_F64) {
+    return fail(PYI_BAD_ARG, "pyi_fill_gauss_seidel: grid must be float32 or float64");
+  }
+  if (nx < 0 || ny < 0 || (nx > 0 && ny > (int64_t{1} << 40) / nx)) {
+    return fail(PYI_BAD_SHAPE, "pyi_fill_gauss_seidel: invalid grid shape");
+  }
+  if (cfg->first_guess != PYI_FIRST_GUESS_ZERO &&
+      cfg->first_guess != PYI_FIRST_GUESS_ZONAL_AVERAGE) {
+    // gauss_seidel.hpp:190-193
+    return fail(PYI_BAD_ARG,
+                "Unsupported first guess method: " + std::to_string(cfg->first_guess));
+  }
+  *iterations = 0;
+  *max_residual = 0.0;
+  if (nx == 0 || ny == 0) return PYI_OK;
+  if (!grid) return fail(PYI_BAD_SHAPE, "pyi_fill_gauss_seidel: missing grid");
+  unsigned long long its = 0;
+  double res = 0.0;
+  if (mem == PYI_MEM_DEVICE) {
+    cudaError_t e = pyi::fill_gauss_seidel(grid, dtype, nx, ny, cfg->first_guess,
+                                           cfg->is_periodic != 0, cfg->max_iterations,
+                                           cfg->epsilon, cfg->relaxation, &its, &res,
+                                           static_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) return cuda_fail(e, "fill kernels");
+    *iterations = its;
+    *max_residual = res;
+    return PYI_OK;
+  }
+  const size_t bytes = static_cast<size_t>(nx) * static_cast<size_t>(ny) * dtype_size(dtype);
+  Workspace& ws = workspace();
+  std::lock_guard<std::recursive_mutex> ws_lock(ws.mu);
+  st = ws.ensure(bytes, 0);
+  if (st != PYI_OK) return st;
+  Slot& slot = ws.slot[0];
+  PYI_CUDA(cudaMemcpyAsync(slot.dev, grid, bytes, cudaMemcpyHostToDevice, slot.stream));
+  cudaError_t e = pyi::fill_gauss_seidel(slot.dev, dtype, nx, ny, cfg->first_guess,
+                                         cfg->is_periodic != 0, cfg->max_iterations, cfg->epsilon,
+                                         cfg->relaxation, &its, &res, slot.stream);
+  if (e != cudaSuccess) return cuda_fail(e, "fill kernels");
+  if (its > 0) {
+    PYI_CUDA(cudaMemcpyAsync(grid, slot.dev, bytes, cudaMemcpyDeviceToHost, slot.stream));
+  }
+  PYI_CUDA(cudaStreamSynchronize(slot.stream));
+  *iterations = its;
+  *max_residual = res;
+  return PYI_OK;
+}
+
 // "{coord} is out of bounds for axis {label} [{min}, ..., {max}]"
 // (pybind/grid.hpp:362-371).  Doubles are printed like std::format("{}"):
 // shortest round-trip digits via std::to_chars.  int64 coordinates are printed

@@ -93,6 +93,11 @@ cudaError_t launch_find_index(const FindParams& p, cudaStream_t stream);
 cudaError_t launch_datetime_convert(const long long* in, long long* out, long long n,
                                     long long index_base, int src, int dst,
                                     unsigned long long* bad_key, cudaStream_t stream);
+// fill::gauss_seidel on a device-resident row-major (nx, ny) grid (pyi_fill.cu)
+cudaError_t fill_gauss_seidel(void* grid, int dtype, long long nx, long long ny, int first_guess,
+                              int periodic, unsigned long long max_iterations, double epsilon,
+                              double relaxation, unsigned long long* iterations, double* residual,
+                              cudaStream_t stream);
 // cell packing (2-D .. 4-D): the 2^ndim corners of every cell contiguous, in the
 // result type; x + 1 wraps (periodic seam cell), the other axes clamp.
 cudaError_t launch_pack_cells(const void* data, int dtype, int ndim, const int* shape, void* packed,

@@ -160,13 +160,46 @@ CASES["wnd4d_akima_f64"] = dict(kind="wnd",
                                       (np.arange(5) * 1.0, None, False), (DEPTH8, None, True)],
                                 dtype="float64", method="akima", half=(3, 3), boundary="undef", n=1200, seed=53,
                                 u_method=1)
+# grid filling: the whole filled grid, the iteration count and
+# the final residual of the reference build are the fixture
+CASES["fill_gs_f64_periodic"] = dict(kind="fill", algo="gauss_seidel", shape=(72, 36), dtype="float64", seed=61,
+                                     first_guess="zonal_average", is_periodic=True, max_iterations=500,
+                                     epsilon=1e-4, relaxation=1.0)
+CASES["fill_gs_f32_zero_reflect"] = dict(kind="fill", algo="gauss_seidel", shape=(45, 31), dtype="float32", seed=62,
+                                         first_guess="zero", is_periodic=False, max_iterations=300,
+                                         epsilon=1e-4, relaxation=1.4)
+CASES["fill_gs_f64_odd_seam"] = dict(kind="fill", algo="gauss_seidel", shape=(37, 23), dtype="float64", seed=63,
+                                     first_guess="zonal_average", is_periodic=True, max_iterations=40,
+                                     epsilon=1e-12, relaxation=1.2)
 VECTOR_CASES = sorted(CASES)
 PORT_CASES = [k for k in VECTOR_CASES if not CASES[k].get("ref_only")]
+
+
+def fill_field(shape, dtype, seed, fraction=0.15, blobs=4):
+    """Smooth field + noise with scattered and clustered NaN cells (an empty
+    latitude band included when the grid is large enough)."""
+    rng = np.random.Generator(np.random.PCG64(5000 + seed))
+    nx, ny = shape
+    x = np.linspace(0.0, 2.0 * np.pi, nx, endpoint=False)[:, None]
+    y = np.linspace(-1.0, 1.0, ny)[None, :]
+    g = 10.0 * np.sin(x) * np.cos(2.0 * y) + 3.0 * y + 0.3 * rng.standard_normal((nx, ny))
+    m = rng.random((nx, ny)) < fraction
+    for _ in range(blobs):
+        i, j = int(rng.integers(0, nx)), int(rng.integers(0, ny))
+        w, h = max(nx // 8, 1), max(ny // 8, 1)
+        m[max(i - w, 0): i + w, max(j - h, 0): j + h] = True
+    if ny > 8:
+        m[:, ny // 3] = True  # a band without any defined value
+    g = g.astype(dtype)
+    g[m] = np.nan
+    return g
 
 
 def build_case(name):
     """Inputs of a case (no outputs), deterministic."""
     c = CASES[name]
+    if c["kind"] == "fill":
+        return {"grid": fill_field(c["shape"], c["dtype"], c["seed"])}
     rng = np.random.Generator(np.random.PCG64(1000 + c["seed"]))
     d = {}
     for k, (values, _, _) in enumerate(c["axes"]):
@@ -218,8 +251,22 @@ def _orc_axes(o, c):
     return out
 
 
+def _fill_result(grid, its, res):
+    return {"out": grid, "iterations": np.array([its], dtype=np.int64),
+            "residual": np.array([res], dtype=np.float64)}
+
+
 def run_case_on_oracle(o, name, d):
     c = CASES[name]
+    if c["kind"] == "fill":
+        g = d["grid"].copy()
+        if c["algo"] == "gauss_seidel":
+            its, res = o.fill_gauss_seidel(g, c["first_guess"], c["is_periodic"], c["max_iterations"],
+                                           c["epsilon"], c["relaxation"])
+        else:
+            its, res = o.fill_multigrid(g, c["first_guess"], c["is_periodic"], c["max_iterations"],
+                                        c["epsilon"], c["pre_smooth"], c["post_smooth"])
+        return _fill_result(g, its, res)
     axes = _orc_axes(o, c)
     if c["kind"] == "idx":
         return {"pairs": axes[0].find_indexes(d["x"]), "index": axes[0].find_index(d["x"], False),
@@ -256,6 +303,15 @@ def _pyi_axes(pyi, c):
 def run_case_on_gpu(pyi, name, d):
     """Same case through the product's public API (CUDA kernels behind the C-ABI)."""
     c = CASES[name]
+    if c["kind"] == "fill":
+        g = d["grid"].copy()
+        kw = dict(first_guess=c["first_guess"], is_periodic=c["is_periodic"],
+                  max_iterations=c["max_iterations"], epsilon=c["epsilon"])
+        if c["algo"] == "gauss_seidel":
+            its, res = pyi.fill.gauss_seidel(g, relaxation=c["relaxation"], **kw)
+        else:
+            its, res = pyi.fill.multigrid(g, pre_smooth=c["pre_smooth"], post_smooth=c["post_smooth"], **kw)
+        return _fill_result(g, its, res)
     axes = _pyi_axes(pyi, c)
     if c["kind"] == "idx":
         x = d["x"].astype("datetime64[ns]") if d["x"].dtype.kind == "i" else d["x"]
@@ -305,6 +361,7 @@ def compare(name, got, d, exact):
     """exact: bit-for-bit (CPU restatement vs reference build).  Otherwise the
     north-star tolerances: indexes bit-exact, float64 values 1e-12, float32
     1e-5 relative (scale guard: max(|want|, 1))."""
+    exact = exact or CASES[name]["kind"] == "fill"  # the fill kernels are bit-identical by construction
     for k, g in got.items():
         want = d["want_" + k]
         g = np.asarray(g)

@@ -1,0 +1,88 @@
+"""GPU parity of the grid filling: the product's CUDA kernels
+behind pyi_fill_gauss_seidel against the reference build (oracle/_ref) or the
+pinned C restatement.  Everything is compared BIT FOR BIT: filled grid,
+iteration count and final residual."""
+import numpy as np
+import pytest
+
+import golden_util as gu
+from test_gpu_parity import orc_best  # noqa: F401  (fixture)
+
+pytestmark = pytest.mark.gpu
+
+SHAPES = [(40, 30), (37, 23), (1, 9), (9, 1), (2, 2), (3, 3), (5, 64), (64, 5), (1, 1), (129, 67), (300, 2)]
+
+
+def _same(a, b, what):
+    assert a.dtype == b.dtype and a.shape == b.shape, what
+    assert np.array_equal(a, b, equal_nan=True), (what, int((a != b).sum()))
+
+
+@pytest.mark.parametrize("dtype", ["float64", "float32"])
+@pytest.mark.parametrize("first_guess", ["zonal_average", "zero"])
+@pytest.mark.parametrize("is_periodic", [True, False])
+def test_gauss_seidel_bit_exact(pyi, orc_best, dtype, first_guess, is_periodic):
+    for k, shape in enumerate(SHAPES):
+        g0 = gu.fill_field(shape, dtype, 200 + k, blobs=2)
+        for relax, its, eps in ((1.0, 80, 1e-4), (1.6, 9, 0.0)):
+            want = g0.copy()
+            r_want = orc_best.fill_gauss_seidel(want, first_guess, is_periodic, its, eps, relax, num_threads=2)
+            got = g0.copy()
+            r_got = pyi.fill.gauss_seidel(got, first_guess=first_guess, is_periodic=is_periodic,
+                                          max_iterations=its, epsilon=eps, relaxation=relax)
+            assert r_got == r_want, (shape, relax)
+            _same(got, want, (shape, relax))
+
+
+def test_gauss_seidel_full_size_converges(pyi, orc_best):
+    """BASELINE grid size (1440 x 720, circular longitude): same iteration count,
+    residual and grid as the reference; the filled field is finite everywhere
+    and the defined cells are untouched."""
+    g0 = gu.fill_field((1440, 720), "float64", 7, fraction=0.05, blobs=12)
+    want = g0.copy()
+    r_want = orc_best.fill_gauss_seidel(want, "zonal_average", True, 300, 1e-3, 1.0, num_threads=0)
+    got = g0.copy()
+    r_got = pyi.fill.gauss_seidel(got, max_iterations=300, epsilon=1e-3)
+    assert r_got == r_want and r_got[0] > 5
+    _same(got, want, "full size")
+    assert np.isfinite(got).all()
+    m = ~np.isnan(g0)
+    assert np.array_equal(got[m], g0[m])
+
+
+def test_gauss_seidel_config_object_and_device_tensor(pyi, orc_best):
+    import torch
+    g0 = gu.fill_field((90, 45), "float32", 11)
+    cfg = (pyi.config.fill.GaussSeidel().with_max_iterations(50).with_epsilon(1e-5).with_relaxation(1.3)
+           .with_first_guess(pyi.config.fill.FirstGuess.ZERO).with_is_periodic(False).with_num_threads(4))
+    want = g0.copy()
+    r_want = orc_best.fill_gauss_seidel(want, "zero", False, 50, 1e-5, 1.3)
+    t = torch.from_numpy(g0.copy()).cuda()
+    r_got = pyi.fill.gauss_seidel(t, cfg)
+    assert r_got == r_want
+    _same(t.cpu().numpy(), want, "device tensor")
+    # non-contiguous host view: filled through a dense copy, written back
+    big = np.full((90, 90), -1.0, dtype=np.float32)
+    view = big[:, ::2]
+    view[...] = g0
+    assert pyi.fill.gauss_seidel(view, cfg) == r_want
+    _same(np.ascontiguousarray(view), want, "strided view")
+    assert (big[:, 1::2] == -1.0).all()
+
+
+def test_gauss_seidel_trivial_and_errors(pyi):
+    g = np.arange(12, dtype=np.float64).reshape(3, 4)
+    assert pyi.fill.gauss_seidel(g) == (0, 0.0)
+    g = np.full((6, 5), np.nan)
+    assert pyi.fill.gauss_seidel(g, max_iterations=10) == (1, 0.0) and not g.any()
+    g = np.full((6, 5), np.nan)
+    assert pyi.fill.gauss_seidel(g, max_iterations=0) == (0, 0.0)
+    assert pyi.fill.gauss_seidel(np.empty((0, 4))) == (0, 0.0)
+    with pytest.raises(TypeError):
+        pyi.fill.gauss_seidel(np.zeros((3, 3), dtype=np.int32))
+    with pytest.raises(TypeError):
+        pyi.fill.gauss_seidel(np.zeros(5))
+    with pytest.raises(KeyError):
+        pyi.fill.gauss_seidel(np.zeros((3, 3)), first_guess="mean")
+    with pytest.raises(TypeError):
+        pyi.fill.gauss_seidel(np.zeros((3, 3)), pyi.windowed.Bivariate.bicubic())

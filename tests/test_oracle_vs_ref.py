@@ -1,6 +1,8 @@
 """Pins oracle/liboracle.so (plain-C restatement) against the reference's own
 headers compiled in place (oracle/_ref/liboracle_ref.so): bit for bit."""
 import numpy as np
+
+import golden_util as gu
 import pytest
 
 import axes_zoo
@@ -330,3 +332,28 @@ def test_datetime_convert_port_vs_ref(port, ref):
                 assert res[0] == res[1], (src, dst)
             else:
                 assert np.array_equal(res[0], res[1]), (src, dst)
+
+
+@pytest.mark.parametrize("dtype", ["float64", "float32"])
+def test_fill_gauss_seidel_port_vs_ref(port, ref, dtype):
+    """fill::gauss_seidel: filled grid, iteration count and residual of the C
+    restatement equal the reference build's, serial and threaded (the red /
+    black sweeps are order independent; the port sweeps black first like the
+    g++ build of the reference)."""
+    for k, shape in enumerate([(40, 30), (37, 23), (1, 9), (9, 1), (2, 2), (3, 3), (5, 64), (64, 5), (1, 1)]):
+        g0 = gu.fill_field(shape, dtype, 100 + k, blobs=2)
+        for fg in ("zonal_average", "zero"):
+            for per in (True, False):
+                for relax, its, eps in ((1.0, 60, 1e-4), (1.5, 7, 0.0)):
+                    a, b = g0.copy(), g0.copy()
+                    ra = ref.fill_gauss_seidel(a, fg, per, its, eps, relax, num_threads=3)
+                    rb = port.fill_gauss_seidel(b, fg, per, its, eps, relax)
+                    assert ra == rb, (shape, fg, per, relax)
+                    assert np.array_equal(a, b, equal_nan=True), (shape, fg, per, relax)
+    # no NaN: nothing happens (gauss_seidel.hpp:175-177); all NaN: zeros
+    for o in (port, ref):
+        g = np.arange(12, dtype=dtype).reshape(3, 4)
+        assert o.fill_gauss_seidel(g.copy()) == (0, 0.0)
+        g = np.full((6, 5), np.nan, dtype=dtype)
+        its, res = o.fill_gauss_seidel(g, max_iterations=10)
+        assert (its, res) == (1, 0.0) and not g.any()
