@@ -279,14 +279,17 @@ int pyi_datetime_convert(int src, int dst, int64_t n, const int64_t *in,
                          int64_t *out, int mem, int64_t *overflow_index,
                          int *overflow_op, void *stream);
 
-/* config::fill::GaussSeidel (config/fill.hpp:67-160,255-279), without
- * num_threads (the device result does not depend on it, as the reference's) */
+/* config::fill::GaussSeidel / Multigrid (config/fill.hpp:67-160,255-324),
+ * without num_threads (the device result does not depend on it, as the
+ * reference's) */
 typedef struct pyi_fill_config {
   int32_t first_guess;      /* pyi_first_guess */
   int32_t is_periodic;      /* x axis periodic (longitude) */
   uint64_t max_iterations;
   double epsilon;
-  double relaxation;
+  double relaxation;        /* Gauss-Seidel only */
+  uint32_t pre_smooth;      /* multigrid only */
+  uint32_t post_smooth;     /* multigrid only */
 } pyi_fill_config;
 
 /* fill::gauss_seidel (fill/gauss_seidel.hpp:166-211): the NaN cells of the
@@ -299,6 +302,16 @@ int pyi_fill_gauss_seidel(void *grid, int dtype, int64_t nx, int64_t ny,
                           const pyi_fill_config *cfg, int mem,
                           uint64_t *iterations, double *max_residual,
                           void *stream);
+
+/* fill::multigrid (fill/multi_grid.hpp:276-334): V-cycles (red-black
+ * Gauss-Seidel smoothing, 2 x 2 restriction, bilinear prolongation, 50
+ * iterations on the coarsest grid) until max |residual| < epsilon.  Same
+ * conventions and the same bit-identical guarantee as pyi_fill_gauss_seidel.
+ * Grids hold at most 2^31 - 1 cells. */
+int pyi_fill_multigrid(void *grid, int dtype, int64_t nx, int64_t ny,
+                       const pyi_fill_config *cfg, int mem,
+                       uint64_t *iterations, double *max_residual,
+                       void *stream);
 
 /* Reference text "{coord} is out of bounds for axis {x|y|z|u} [{min}, ...,
  * {max}]" (pybind/grid.hpp:367-370). `coord` points to a double or an int64

@@ -108,6 +108,8 @@ class FillConfig(C.Structure):
         ("max_iterations", C.c_uint64),
         ("epsilon", C.c_double),
         ("relaxation", C.c_double),
+        ("pre_smooth", C.c_uint32),
+        ("post_smooth", C.c_uint32),
     ]
 
 
@@ -141,6 +143,8 @@ SIGNATURES = {
     "pyi_datetime_convert": (C.c_int, [C.c_int, C.c_int, C.c_int64, _P, _P, C.c_int, _I64P, _IP, _P]),
     "pyi_fill_gauss_seidel": (C.c_int, [_P, C.c_int, C.c_int64, C.c_int64, C.POINTER(FillConfig), C.c_int,
                                         C.POINTER(C.c_uint64), C.POINTER(C.c_double), _P]),
+    "pyi_fill_multigrid": (C.c_int, [_P, C.c_int, C.c_int64, C.c_int64, C.POINTER(FillConfig), C.c_int,
+                                     C.POINTER(C.c_uint64), C.POINTER(C.c_double), _P]),
     "pyi_format_bounds_error": (C.c_int, [_P, C.c_int, _P, C.c_char_p, C.c_size_t]),
     "pyi_launch_count": (C.c_int64, []),
 }

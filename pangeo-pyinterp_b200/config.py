@@ -325,4 +325,30 @@ class GaussSeidel(_FillBase):
         return self._relaxation
 
 
-fill = types.SimpleNamespace(FirstGuess=FirstGuess, GaussSeidel=GaussSeidel)
+class Multigrid(_FillBase):
+    """config::fill::Multigrid (config/fill.hpp:282-324)."""
+
+    _max_iterations = 100
+    _pre_smooth = 2
+    _post_smooth = 2
+
+    def _smooth(self, name, value):
+        value = int(value)
+        if not 0 <= value < 2 ** 32:  # uint32_t argument of the reference binding
+            raise TypeError(f"with{name}(): value must fit an uint32")
+        return self._with(name, value)
+
+    def with_pre_smooth(self, value: int):
+        return self._smooth("_pre_smooth", value)
+
+    def with_post_smooth(self, value: int):
+        return self._smooth("_post_smooth", value)
+
+    def pre_smooth(self) -> int:
+        return self._pre_smooth
+
+    def post_smooth(self) -> int:
+        return self._post_smooth
+
+
+fill = types.SimpleNamespace(FirstGuess=FirstGuess, GaussSeidel=GaussSeidel, Multigrid=Multigrid)

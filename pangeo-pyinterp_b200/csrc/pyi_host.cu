@@ -1022,39 +1022,49 @@ int pyi_datetime_convert(int src, int dst, int64_t n, const int64_t* in, int64_t
   return report(key);
 }
 
-// fill::gauss_seidel (fill/gauss_seidel.hpp:166-211) in place.  Host grids are
-// staged through one device copy; everything else happens in pyi_fill.cu.
-int pyi_fill_gauss_seidel(void* grid, int dtype, int64_t nx, int64_t ny,
-                          const pyi_fill_config* cfg, int mem, uint64_t* iterations,
-                          double* max_residual, void* stream) {
+// fill::gauss_seidel (fill/gauss_seidel.hpp:166-211) and fill::multigrid
+// (fill/multi_grid.hpp:276-334) in place.  Host grids are staged through one
+// device copy; everything else happens in pyi_fill.cu.
+namespace {
+
+int fill_entry(bool multigrid, void* grid, int dtype, int64_t nx, int64_t ny,
+               const pyi_fill_config* cfg, int mem, uint64_t* iterations, double* max_residual,
+               void* stream) {
+  const char* name = multigrid ? "pyi_fill_multigrid" : "pyi_fill_gauss_seidel";
   int st = require_device();
   if (st != PYI_OK) return st;
   if (!cfg || !iterations || !max_residual) {
-    return fail(PYI_BAD_ARG, "pyi_fill_gauss_seidel: missing argument");
+    return fail(PYI_BAD_ARG, std::string(name) + ": missing argument");
   }
   if (dtype != PYI_F32 && dtype != PYI_F64) {
-    return fail(PYI_BAD_ARG, "pyi_fill_gauss_seidel: grid must be float32 or float64");
+    return fail(PYI_BAD_ARG, std::string(name) + ": grid must be float32 or float64");
   }
-  if (nx < 0 || ny < 0 || (nx > 0 && ny > (int64_t{1} << 40) / nx)) {
-    return fail(PYI_BAD_SHAPE, "pyi_fill_gauss_seidel: invalid grid shape");
+  if (nx < 0 || ny < 0 || (nx > 0 && ny > int64_t{0x7fffffff} / nx)) {
+    return fail(PYI_BAD_SHAPE, std::string(name) + ": invalid grid shape (at most 2^31 - 1 cells)");
   }
   if (cfg->first_guess != PYI_FIRST_GUESS_ZERO &&
       cfg->first_guess != PYI_FIRST_GUESS_ZONAL_AVERAGE) {
-    // gauss_seidel.hpp:190-193
+    // gauss_seidel.hpp:190-193, multi_grid.hpp:296-299
     return fail(PYI_BAD_ARG,
                 "Unsupported first guess method: " + std::to_string(cfg->first_guess));
   }
   *iterations = 0;
   *max_residual = 0.0;
   if (nx == 0 || ny == 0) return PYI_OK;
-  if (!grid) return fail(PYI_BAD_SHAPE, "pyi_fill_gauss_seidel: missing grid");
+  if (!grid) return fail(PYI_BAD_SHAPE, std::string(name) + ": missing grid");
   unsigned long long its = 0;
   double res = 0.0;
+  auto run = [&](void* dev, cudaStream_t s) {
+    return multigrid
+               ? pyi::fill_multigrid(dev, dtype, nx, ny, cfg->first_guess, cfg->is_periodic != 0,
+                                     cfg->max_iterations, cfg->epsilon, cfg->pre_smooth,
+                                     cfg->post_smooth, &its, &res, s)
+               : pyi::fill_gauss_seidel(dev, dtype, nx, ny, cfg->first_guess,
+                                        cfg->is_periodic != 0, cfg->max_iterations, cfg->epsilon,
+                                        cfg->relaxation, &its, &res, s);
+  };
   if (mem == PYI_MEM_DEVICE) {
-    cudaError_t e = pyi::fill_gauss_seidel(grid, dtype, nx, ny, cfg->first_guess,
-                                           cfg->is_periodic != 0, cfg->max_iterations,
-                                           cfg->epsilon, cfg->relaxation, &its, &res,
-                                           static_cast<cudaStream_t>(stream));
+    cudaError_t e = run(grid, static_cast<cudaStream_t>(stream));
     if (e != cudaSuccess) return cuda_fail(e, "fill kernels");
     *iterations = its;
     *max_residual = res;
@@ -1067,9 +1077,7 @@ int pyi_fill_gauss_seidel(void* grid, int dtype, int64_t nx, int64_t ny,
   if (st != PYI_OK) return st;
   Slot& slot = ws.slot[0];
   PYI_CUDA(cudaMemcpyAsync(slot.dev, grid, bytes, cudaMemcpyHostToDevice, slot.stream));
-  cudaError_t e = pyi::fill_gauss_seidel(slot.dev, dtype, nx, ny, cfg->first_guess,
-                                         cfg->is_periodic != 0, cfg->max_iterations, cfg->epsilon,
-                                         cfg->relaxation, &its, &res, slot.stream);
+  cudaError_t e = run(slot.dev, slot.stream);
   if (e != cudaSuccess) return cuda_fail(e, "fill kernels");
   if (its > 0) {
     PYI_CUDA(cudaMemcpyAsync(grid, slot.dev, bytes, cudaMemcpyDeviceToHost, slot.stream));
@@ -1078,6 +1086,19 @@ int pyi_fill_gauss_seidel(void* grid, int dtype, int64_t nx, int64_t ny,
   *iterations = its;
   *max_residual = res;
   return PYI_OK;
+}
+
+}  // namespace
+
+int pyi_fill_gauss_seidel(void* grid, int dtype, int64_t nx, int64_t ny,
+                          const pyi_fill_config* cfg, int mem, uint64_t* iterations,
+                          double* max_residual, void* stream) {
+  return fill_entry(false, grid, dtype, nx, ny, cfg, mem, iterations, max_residual, stream);
+}
+
+int pyi_fill_multigrid(void* grid, int dtype, int64_t nx, int64_t ny, const pyi_fill_config* cfg,
+                       int mem, uint64_t* iterations, double* max_residual, void* stream) {
+  return fill_entry(true, grid, dtype, nx, ny, cfg, mem, iterations, max_residual, stream);
 }
 
 // "{coord} is out of bounds for axis {label} [{min}, ..., {max}]"

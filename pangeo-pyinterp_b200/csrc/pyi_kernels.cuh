@@ -98,6 +98,10 @@ cudaError_t fill_gauss_seidel(void* grid, int dtype, long long nx, long long ny,
                               int periodic, unsigned long long max_iterations, double epsilon,
                               double relaxation, unsigned long long* iterations, double* residual,
                               cudaStream_t stream);
+cudaError_t fill_multigrid(void* grid, int dtype, long long nx, long long ny, int first_guess,
+                           int periodic, unsigned long long max_iterations, double epsilon,
+                           unsigned pre_smooth, unsigned post_smooth,
+                           unsigned long long* iterations, double* residual, cudaStream_t stream);
 // cell packing (2-D .. 4-D): the 2^ndim corners of every cell contiguous, in the
 // result type; x + 1 wraps (periodic seam cell), the other axes clamp.
 cudaError_t launch_pack_cells(const void* data, int dtype, int ndim, const int* shape, void* packed,

@@ -2,7 +2,9 @@
 (pyinterp/fill.py) for the methods that run on the device:
 
 * :func:`gauss_seidel` -- ``core.fill.gauss_seidel``
-  (cxx/include/pyinterp/fill/gauss_seidel.hpp:166-211).
+  (cxx/include/pyinterp/fill/gauss_seidel.hpp:166-211);
+* :func:`multigrid` -- ``core.fill.multigrid``
+  (cxx/include/pyinterp/fill/multi_grid.hpp:276-334).
 
 Grids are filled IN PLACE like the reference: numpy arrays are staged through
 the device, CUDA tensors (torch, or anything exposing
@@ -21,7 +23,7 @@ from . import _abi
 from .config import fill as _cfg
 from .core import _device_view, _is_torch_cuda, _lib, _np_ptr
 
-__all__ = ["gauss_seidel"]
+__all__ = ["gauss_seidel", "multigrid"]
 
 #: pyinterp/fill.py:47-50
 _FIRST_GUESS_MAP = {
@@ -77,23 +79,47 @@ def gauss_seidel(grid, config=None, *, max_iterations: int | None = None, epsilo
             is_periodic=is_periodic, num_threads=num_threads)
     elif not isinstance(config, _cfg.GaussSeidel):
         raise TypeError("config must be a config.fill.GaussSeidel")
-    arr, ptr, dt, nx, ny, mem, stream = _grid_args(grid)
     pod = _abi.FillConfig(int(config.first_guess()), int(config.is_periodic()), config.max_iterations(),
-                          config.epsilon(), config.relaxation())
+                          config.epsilon(), config.relaxation(), 0, 0)
+    return _run("pyi_fill_gauss_seidel", "gauss_seidel", grid, pod)
+
+
+def _run(entry: str, what: str, grid, pod) -> tuple[int, float]:
+    arr, ptr, dt, nx, ny, mem, stream = _grid_args(grid)
     its, res = C.c_uint64(0), C.c_double(0.0)
-    lib = _lib()
+    fn = getattr(_lib(), entry)
     if mem == _abi.PYI_MEM_DEVICE:
         import torch
         with torch.cuda.device(arr.device):
-            st = lib.pyi_fill_gauss_seidel(ptr, dt, nx, ny, C.byref(pod), mem, C.byref(its), C.byref(res),
-                                           stream)
+            st = fn(ptr, dt, nx, ny, C.byref(pod), mem, C.byref(its), C.byref(res), stream)
     else:
         # the reference accepts any strided view (EigenDRef): fill a dense copy
         # and write it back when the caller's array is not C-contiguous
         dense = arr if arr.flags.c_contiguous else np.ascontiguousarray(arr)
-        st = lib.pyi_fill_gauss_seidel(_np_ptr(dense), dt, nx, ny, C.byref(pod), mem, C.byref(its),
-                                       C.byref(res), None)
+        st = fn(_np_ptr(dense), dt, nx, ny, C.byref(pod), mem, C.byref(its), C.byref(res), None)
         if dense is not arr and st == _abi.PYI_OK:
             arr[...] = dense
-    _abi.check(st, "gauss_seidel")
+    _abi.check(st, what)
     return int(its.value), float(res.value)
+
+
+def multigrid(grid, config=None, *, max_iterations: int | None = None, epsilon: float | None = None,
+              pre_smooth: int | None = None, post_smooth: int | None = None, first_guess: str | None = None,
+              is_periodic: bool | None = None, num_threads: int | None = None) -> tuple[int, float]:
+    """``pyinterp.fill.multigrid`` (pyinterp/fill.py:308-372): replaces the NaN
+    cells of ``grid`` in place by V-cycle multigrid relaxation of the Laplace
+    equation; returns ``(iterations, max_residual)``."""
+    if config is None:
+        config = _build_config(
+            _cfg.Multigrid,
+            {"max_iterations": ("with_max_iterations", None), "epsilon": ("with_epsilon", None),
+             "pre_smooth": ("with_pre_smooth", None), "post_smooth": ("with_post_smooth", None),
+             "first_guess": ("with_first_guess", _FIRST_GUESS_MAP), "is_periodic": ("with_is_periodic", None),
+             "num_threads": ("with_num_threads", None)},
+            max_iterations=max_iterations, epsilon=epsilon, pre_smooth=pre_smooth, post_smooth=post_smooth,
+            first_guess=first_guess, is_periodic=is_periodic, num_threads=num_threads)
+    elif not isinstance(config, _cfg.Multigrid):
+        raise TypeError("config must be a config.fill.Multigrid")
+    pod = _abi.FillConfig(int(config.first_guess()), int(config.is_periodic()), config.max_iterations(),
+                          config.epsilon(), 1.0, config.pre_smooth(), config.post_smooth())
+    return _run("pyi_fill_multigrid", "multigrid", grid, pod)

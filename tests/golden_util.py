@@ -171,6 +171,15 @@ CASES["fill_gs_f32_zero_reflect"] = dict(kind="fill", algo="gauss_seidel", shape
 CASES["fill_gs_f64_odd_seam"] = dict(kind="fill", algo="gauss_seidel", shape=(37, 23), dtype="float64", seed=63,
                                      first_guess="zonal_average", is_periodic=True, max_iterations=40,
                                      epsilon=1e-12, relaxation=1.2)
+CASES["fill_mg_f64_periodic"] = dict(kind="fill", algo="multigrid", shape=(72, 36), dtype="float64", seed=64,
+                                     first_guess="zonal_average", is_periodic=True, max_iterations=30,
+                                     epsilon=1e-6, pre_smooth=2, post_smooth=2)
+CASES["fill_mg_f32_zero_reflect"] = dict(kind="fill", algo="multigrid", shape=(45, 31), dtype="float32", seed=65,
+                                         first_guess="zero", is_periodic=False, max_iterations=12,
+                                         epsilon=1e-4, pre_smooth=1, post_smooth=3)
+CASES["fill_mg_f64_odd_sizes"] = dict(kind="fill", algo="multigrid", shape=(77, 41), dtype="float64", seed=66,
+                                      first_guess="zonal_average", is_periodic=True, max_iterations=6,
+                                      epsilon=0.0, pre_smooth=2, post_smooth=1)
 VECTOR_CASES = sorted(CASES)
 PORT_CASES = [k for k in VECTOR_CASES if not CASES[k].get("ref_only")]
 

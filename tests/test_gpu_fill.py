@@ -86,3 +86,54 @@ def test_gauss_seidel_trivial_and_errors(pyi):
         pyi.fill.gauss_seidel(np.zeros((3, 3)), first_guess="mean")
     with pytest.raises(TypeError):
         pyi.fill.gauss_seidel(np.zeros((3, 3)), pyi.windowed.Bivariate.bicubic())
+
+
+MG_SHAPES = [(40, 30), (37, 23), (77, 41), (9, 9), (5, 5), (4, 50), (64, 5), (6, 7), (1, 1), (129, 67), (300, 2),
+             (200, 160)]
+
+
+@pytest.mark.parametrize("dtype", ["float64", "float32"])
+@pytest.mark.parametrize("is_periodic", [True, False])
+def test_multigrid_bit_exact(pyi, orc_best, dtype, is_periodic):
+    for k, shape in enumerate(MG_SHAPES):
+        g0 = gu.fill_field(shape, dtype, 400 + k, blobs=2)
+        for fg, pre, post, its, eps in (("zonal_average", 2, 2, 8, 1e-6), ("zero", 1, 3, 3, 0.0), ("zero", 0, 1, 2, 0.0)):
+            want = g0.copy()
+            r_want = orc_best.fill_multigrid(want, fg, is_periodic, its, eps, pre, post, num_threads=2)
+            got = g0.copy()
+            r_got = pyi.fill.multigrid(got, first_guess=fg, is_periodic=is_periodic, max_iterations=its,
+                                       epsilon=eps, pre_smooth=pre, post_smooth=post)
+            assert r_got == r_want, (shape, fg, pre, post)
+            _same(got, want, (shape, fg, pre, post))
+
+
+def test_multigrid_full_size(pyi, orc_best):
+    """BASELINE grid size: multi-block sweeps on the fine levels, single-block
+    smoothing below, nine levels."""
+    g0 = gu.fill_field((1440, 720), "float64", 8, fraction=0.05, blobs=12)
+    want = g0.copy()
+    r_want = orc_best.fill_multigrid(want, "zonal_average", True, 5, 1e-9, 2, 2, num_threads=0)
+    got = g0.copy()
+    r_got = pyi.fill.multigrid(got, max_iterations=5, epsilon=1e-9)
+    assert r_got == r_want
+    _same(got, want, "full size")
+    m = ~np.isnan(g0)
+    assert np.isfinite(got).all() and np.array_equal(got[m], g0[m])
+
+
+def test_multigrid_config_device_tensor_and_errors(pyi, orc_best):
+    import torch
+    g0 = gu.fill_field((90, 45), "float32", 12)
+    cfg = (pyi.config.fill.Multigrid().with_max_iterations(4).with_epsilon(1e-7).with_pre_smooth(3)
+           .with_post_smooth(1).with_first_guess(pyi.config.fill.FirstGuess.ZERO).with_is_periodic(False))
+    want = g0.copy()
+    r_want = orc_best.fill_multigrid(want, "zero", False, 4, 1e-7, 3, 1)
+    t = torch.from_numpy(g0.copy()).cuda()
+    assert pyi.fill.multigrid(t, cfg) == r_want
+    _same(t.cpu().numpy(), want, "device tensor")
+    assert pyi.fill.multigrid(np.arange(12.0).reshape(3, 4)) == (0, 0.0)
+    g = np.full((9, 9), np.nan, dtype=np.float32)
+    its, res = pyi.fill.multigrid(g, max_iterations=0)
+    assert its == 0 and res == float(np.finfo(np.float32).max)  # multi_grid.hpp:311
+    with pytest.raises(TypeError):
+        pyi.fill.multigrid(np.zeros((3, 3)), pyi.config.fill.GaussSeidel())
