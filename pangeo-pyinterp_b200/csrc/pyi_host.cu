@@ -403,6 +403,11 @@ struct pyi_grid {
   void* d_data{nullptr};
   bool borrowed{false};
   void* d_packed{nullptr};
+  // plane-major copy [z][u][x][y] of a 3-D / 4-D grid, built on the first
+  // windowed bicubic call (pyi_fastwin_nd.cuh)
+  mutable void* d_planes{nullptr};
+  mutable bool planes_tried{false};
+  mutable std::mutex planes_mu;
   unsigned long long* d_oob{nullptr};  // for device-memory calls
   // natural-spline constants of a uniformly spaced six-node window on x / y
   // (regular axes with moderate steps), computed on the device at creation
@@ -631,6 +636,29 @@ pyi_grid* pyi_grid_create(int ndim, const pyi_axis* const* axes, int dtype, cons
   return raw;
 }
 
+// Builds (or refreshes) the plane-major copy of a 3-D / 4-D grid.  It is an
+// optimisation: when it does not fit, the windowed kernels keep the C-order
+// array.
+static int grid_planes(const pyi_grid* grid, bool refresh) {
+  if (grid->ndim < 3) return PYI_OK;
+  std::lock_guard<std::mutex> lock(grid->planes_mu);
+  if (grid->d_planes && !refresh) return PYI_OK;
+  if (!grid->d_planes) {
+    if (grid->planes_tried) return PYI_OK;
+    grid->planes_tried = true;
+    size_t free_b = 0, total_b = 0;
+    PYI_CUDA(cudaMemGetInfo(&free_b, &total_b));
+    if (grid->bytes > free_b / 2) return PYI_OK;
+    PYI_CUDA(cudaMalloc(&grid->d_planes, std::max<size_t>(grid->bytes, 64)));
+  }
+  const long long shape[4] = {grid->shape[0], grid->shape[1], grid->shape[2], grid->shape[3]};
+  cudaError_t e = pyi::launch_plane_major(grid->d_data, grid->d_planes,
+                                          static_cast<int>(dtype_size(grid->dtype)), shape, nullptr);
+  if (e != cudaSuccess) return cuda_fail(e, "plane_major");
+  PYI_CUDA(cudaStreamSynchronize(nullptr));
+  return PYI_OK;
+}
+
 int pyi_grid_update(pyi_grid* grid, const void* data, int mem) {
   if (!grid || !data) return fail(PYI_BAD_ARG, "null argument");
   if (grid->borrowed) {
@@ -638,6 +666,10 @@ int pyi_grid_update(pyi_grid* grid, const void* data, int mem) {
   } else {
     PYI_CUDA(cudaMemcpy(grid->d_data, data, grid->bytes,
                         mem == PYI_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice));
+  }
+  if (grid->d_planes) {
+    int st = grid_planes(grid, true);
+    if (st != PYI_OK) return st;
   }
   if (grid->d_packed) return pyi_grid_pack(grid);
   return PYI_OK;
@@ -674,6 +706,7 @@ void pyi_grid_destroy(pyi_grid* grid) {
   if (!grid) return;
   if (!grid->borrowed) cudaFree(grid->d_data);
   cudaFree(grid->d_packed);
+  cudaFree(grid->d_planes);
   cudaFree(grid->d_oob);
   for (auto& a : grid->axes) {
     if (a) free_axis_device(a.get());
@@ -897,6 +930,11 @@ int pyi_windowed(const pyi_grid* grid, const pyi_windowed_nd_config* cfg, int64_
   for (int a = 0; a < 2; ++a) {
     p.u6_ok[a] = grid->u6_ok[a];
     std::memcpy(p.u6[a], grid->u6[a], sizeof(p.u6[a]));
+  }
+  if (nd >= 3 && cfg->method == PYI_S_BICUBIC && cfg->half_x == 3 && cfg->half_y == 3) {
+    st = grid_planes(grid, false);
+    if (st != PYI_OK) return st;
+    p.planes = grid->d_planes;
   }
   const size_t out_elem = result_is_f64(grid->dtype) ? 8 : 4;
   if (mem == PYI_MEM_DEVICE) {

@@ -72,6 +72,8 @@ struct WinNdParams {
   unsigned long long* oob_key;
   double u6[2][24];  // forwarded to K4 (2-D bicubic)
   int32_t u6_ok[2];
+  const void* planes;  // plane-major copy [z][u][x][y] (3-D / 4-D bicubic fast path) or null
+  int32_t redo;        // generic kernel: recompute only the points tagged by the fast pass
 };
 
 struct FindParams {
@@ -102,6 +104,9 @@ cudaError_t fill_multigrid(void* grid, int dtype, long long nx, long long ny, in
                            int periodic, unsigned long long max_iterations, double epsilon,
                            unsigned pre_smooth, unsigned post_smooth,
                            unsigned long long* iterations, double* residual, cudaStream_t stream);
+// plane-major copy of a 3-D / 4-D grid: [x][y][z][u] -> [z][u][x][y]
+cudaError_t launch_plane_major(const void* in, void* out, int elem_size, const long long* shape,
+                               cudaStream_t stream);
 // cell packing (2-D .. 4-D): the 2^ndim corners of every cell contiguous, in the
 // result type; x + 1 wraps (periodic seam cell), the other axes clamp.
 cudaError_t launch_pack_cells(const void* data, int dtype, int ndim, const int* shape, void* packed,

@@ -14,6 +14,7 @@ static bool force_generic() {
 }  // namespace pyi
 #include "pyi_windowed.cuh"
 #include "pyi_fastwin.cuh"
+#include "pyi_fastwin_nd.cuh"
 
 namespace pyi {
 // K6 (pyi_windowed_nd.cuh) is instantiated per window capacity in
@@ -49,6 +50,16 @@ cudaError_t launch_windowed_nd(const WinNdParams& p, cudaStream_t stream) {
       for (int k = 0; k < 24; ++k) q.u6[a][k] = p.u6[a][k];
     }
     return launch_windowed2d(q, stream);
+  }
+  // 3-D / 4-D bicubic on a 6 x 6 window: fast pass over the plane-major copy,
+  // then the generic kernel recomputes the points that pass tagged
+  if (p.ndim >= 3 && p.method == PYI_S_BICUBIC && p.half_x == 3 && p.half_y == 3 && p.planes &&
+      !force_generic()) {
+    cudaError_t e = launch_bicubic6_nd_fast(p, stream);
+    if (e != cudaSuccess) return e;
+    WinNdParams q = p;
+    q.redo = 1;
+    return launch_windowed_nd_w<6>(q, stream);
   }
   const int hy = p.ndim >= 2 ? p.half_y : 1;
   const int w = 2 * (p.half_x > hy ? p.half_x : hy);

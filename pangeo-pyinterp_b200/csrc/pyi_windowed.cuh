@@ -239,6 +239,45 @@ __device__ __forceinline__ double bicubic_cell(double x, double y, double x0, do
 
 // One query point of windowed::pybind::bivariate
 // (pybind/windowed/bivariate.hpp:46-76 + cache_loader.hpp:46-172).
+// Axis::contains axis.hpp:405-416
+__device__ __forceinline__ bool axis_contains(const DAxis& a, double c) {
+  return !isnan(c) && (a.periodic || (c >= a.min && c <= a.max));
+}
+__device__ __forceinline__ bool axis_contains(const DAxis& a, long long c) {
+  return c != LLONG_MIN && (a.periodic || (c >= a.imin && c <= a.imax));
+}
+
+// Axis::find_indexes(c, 1, boundary) axis.hpp:814-881: the bracketing pair, or
+// (0, 0) on a singleton axis
+template <typename T>
+__device__ __forceinline__ bool window_pair(const DAxis& a, T c, int& i0, int& i1) {
+  if (find_indexes<T>(a, c, i0, i1)) return true;
+  if (a.n != 1) return false;
+  i0 = 0;
+  i1 = 0;
+  return true;
+}
+
+// The "recompute me" tags (quiet NaNs with a payload): results are either
+// finite, infinite, the canonical NaN the kernels write, or the default NaN
+// of an invalid operation -- never these.
+template <typename R>
+struct RedoTag;
+template <>
+struct RedoTag<double> {
+  static __device__ __forceinline__ double value() {
+    return __longlong_as_double(0x7ff8b200b200b200LL);
+  }
+  static __device__ __forceinline__ bool is(double v) {
+    return __double_as_longlong(v) == 0x7ff8b200b200b200LL;
+  }
+};
+template <>
+struct RedoTag<float> {
+  static __device__ __forceinline__ float value() { return __int_as_float(0x7fcb2000); }
+  static __device__ __forceinline__ bool is(float v) { return __float_as_int(v) == 0x7fcb2000; }
+};
+
 // Returns -1 (value in res, possibly NaN) or the axis that is truly out of
 // bounds (cache_loader.hpp:69-80).
 template <int MAXW>

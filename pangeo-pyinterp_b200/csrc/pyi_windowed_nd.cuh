@@ -20,25 +20,6 @@
 
 namespace pyi {
 
-// Axis::contains axis.hpp:405-416
-__device__ __forceinline__ bool axis_contains(const DAxis& a, double c) {
-  return !isnan(c) && (a.periodic || (c >= a.min && c <= a.max));
-}
-__device__ __forceinline__ bool axis_contains(const DAxis& a, long long c) {
-  return c != LLONG_MIN && (a.periodic || (c >= a.imin && c <= a.imax));
-}
-
-// Axis::find_indexes(c, 1, boundary) axis.hpp:814-881: the bracketing pair, or
-// (0, 0) on a singleton axis
-template <typename T>
-__device__ __forceinline__ bool window_pair(const DAxis& a, T c, int& i0, int& i1) {
-  if (find_indexes<T>(a, c, i0, i1)) return true;
-  if (a.n != 1) return false;
-  i0 = 0;
-  i1 = 0;
-  return true;
-}
-
 // Univariate<T>::min_size of the model (akima.hpp:28, cspline*.hpp, linear.hpp:25,
 // steffen.hpp:27, polynomial.hpp:26)
 __device__ __forceinline__ int spline_min_size(int method) {
@@ -246,6 +227,9 @@ windowed_nd_kernel(const __grid_constant__ WinNdParams p) {
   const ZT* __restrict__ zs = static_cast<const ZT*>(p.z);
   for (long long k = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; k < p.n;
        k += stride) {
+    // redo mode (after the bicubic fast pass, pyi_fastwin_nd.cuh): only the
+    // points tagged by that pass are computed
+    if (p.redo && !RedoTag<R>::is(out[k])) continue;
     R res;
     const double y = ND >= 2 ? __ldg(p.y + k) : 0.0;
     const ZT z = ND >= 3 ? __ldg(zs + k) : ZT{};

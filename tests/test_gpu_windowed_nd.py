@@ -280,3 +280,95 @@ def test_temporal_axis_casts_on_device(pyi, orc_best):
     assert np.array_equal(grid.z.cast_to_int64(zs), zs.astype("datetime64[ns]").view(np.int64))
     with pytest.raises(ValueError, match="must be of type datetime64"):
         grid.z.cast_to_int64(np.arange(3).astype("timedelta64[s]"))
+
+
+# ---- bicubic fast path on 3-D / 4-D grids (pyi_fastwin_nd.cuh) -----------------
+def _generic(fn):
+    """Runs fn with the windowed fast paths disabled (generic K6 kernel)."""
+    import os
+    os.environ["PYINTERP_B200_GENERIC"] = "1"
+    try:
+        return fn()
+    finally:
+        os.environ.pop("PYINTERP_B200_GENERIC", None)
+
+
+@pytest.mark.parametrize("dtype,nan", [("float64", 0.0), ("float64", 0.002), ("float32", 0.001), ("int16", 0.0),
+                                       ("uint64", 0.0)])
+@pytest.mark.parametrize("y_kind", ["regular", "irregular"])
+def test_bicubic_nd_fast_path_trivariate(pyi, orc_best, dtype, nan, y_kind):
+    """Fast pass + redo pass == generic kernel == reference, bit for bit: regular
+    axes (uniform spline constants) and an irregular latitude, NaN cells, integer
+    grids, edges, out-of-range and NaN coordinates, temporal z, both z methods."""
+    ref = orc_best
+    iz = axes_zoo.i64_axes()
+    lat = -87.5 + np.arange(36) * 5.0
+    if y_kind == "irregular":
+        lat = lat + 1.7 * np.sin(np.arange(36) * 0.9)
+    specs = [(np.arange(72) * 5.0, dict(period=360.0), False), (lat, {}, False), iz["monthly30"]]
+    gaxes, caxes = _axes(pyi, ref, specs)
+    ds = [c.describe() for c in caxes]
+    g = _field(tuple(d["size"] for d in ds), dtype, seed=31, nan=nan)
+    grid = pyi.Grid(*gaxes, g)
+    q = _queries(3, 60_000, 33)
+    z = q[2].view("datetime64[ns]")
+    for z_method in ("linear", "nearest"):
+        for boundary in ("undef", "shrink"):
+            cfg = _cfg(pyi, 3, "bicubic", (3, 3), boundary, z_method=z_method)
+            got = pyi.core.trivariate(grid, q[0], q[1], z, cfg)
+            gen = _generic(lambda: pyi.core.trivariate(grid, q[0], q[1], z, cfg))
+            assert np.array_equal(got, gen, equal_nan=True), (z_method, boundary, int((got != gen).sum()))
+            want, _ = ref.windowed_nd(caxes, g, q[0], q[1], q[2], method="bicubic", boundary=boundary,
+                                      num_threads=0, z_method=0 if z_method == "linear" else 1)
+            assert close(got, want, 50.0, f"{dtype} {y_kind} {z_method} {boundary}") == 1.0
+    assert np.isfinite(got).mean() > 0.3  # the fast pass did most of the work
+
+
+@pytest.mark.parametrize("dtype", ["float64", "float32", "int32"])
+def test_bicubic_nd_fast_path_quadrivariate(pyi, orc_best, dtype):
+    ref = orc_best
+    iz = axes_zoo.i64_axes()
+    specs = [(np.arange(36) * 10.0, dict(period=360.0), False), (-85.0 + np.arange(18) * 10.0, {}, False),
+             iz["monthly30"], (np.round(5500.0 * (np.arange(9) / 8) ** 2.2, 1), {}, False)]
+    gaxes, caxes = _axes(pyi, ref, specs)
+    ds = [c.describe() for c in caxes]
+    g = _field(tuple(d["size"] for d in ds), dtype, seed=41, nan=0.0005)
+    grid = pyi.Grid(*gaxes, g)
+    q = _queries(4, 40_000, 43)
+    z = q[2].view("datetime64[ns]")
+    for methods in (("linear", "linear"), ("nearest", "linear"), ("linear", "nearest")):
+        cfg = _cfg(pyi, 4, "bicubic", (3, 3), "undef", z_method=methods[0], u_method=methods[1])
+        got = pyi.core.quadrivariate(grid, q[0], q[1], z, q[3], cfg)
+        gen = _generic(lambda: pyi.core.quadrivariate(grid, q[0], q[1], z, q[3], cfg))
+        assert np.array_equal(got, gen, equal_nan=True), (methods, int((got != gen).sum()))
+        want, _ = ref.windowed_nd(caxes, g, q[0], q[1], q[2], q[3], method="bicubic", boundary="undef",
+                                  num_threads=0, z_method=0 if methods[0] == "linear" else 1,
+                                  u_method=0 if methods[1] == "linear" else 1)
+        assert close(got, want, 50.0, f"{dtype} {methods}") == 1.0
+
+
+def test_bicubic_nd_fast_path_refresh_bounds_and_device(pyi, orc_best):
+    """The plane-major copy follows the caller's array (non-resident grids are
+    refreshed before every call); bounds errors come from the redo pass; device
+    tensors give the same bits as host arrays; float64 depth axis."""
+    import torch
+    ref = orc_best
+    fz = axes_zoo.f64_axes()
+    specs = [(np.arange(72) * 5.0, dict(period=360.0), False), (-87.5 + np.arange(36) * 5.0, {}, False), fz["depth"]]
+    gaxes, caxes = _axes(pyi, ref, specs)
+    ds = [c.describe() for c in caxes]
+    g = _field(tuple(d["size"] for d in ds), "float64", seed=51)
+    grid = pyi.Grid(*gaxes, g)
+    q = _queries(3, 30_000, 53, z_f64=True)
+    first = pyi.trivariate(grid, q[0], q[1], q[2], "bicubic")
+    g *= -2.0  # the reference borrows the buffer: the next call sees the new values
+    second = pyi.trivariate(grid, q[0], q[1], q[2], "bicubic")
+    want, _ = ref.windowed_nd(caxes, g, q[0], q[1], q[2], method="bicubic", num_threads=0)
+    assert close(second, want, 50.0, "refreshed") == 1.0
+    assert not np.array_equal(first, second, equal_nan=True)
+    dev = pyi.trivariate(grid, *(torch.from_numpy(c).cuda() for c in q), "bicubic")
+    assert np.array_equal(dev.cpu().numpy(), second, equal_nan=True)
+    want_err = ref.windowed_nd(caxes, g, q[0], q[1], q[2], method="bicubic", bounds_error=True, num_threads=0)[1]
+    with pytest.raises(IndexError) as ei:
+        pyi.trivariate(grid, q[0], q[1], q[2], "bicubic", bounds_error=True)
+    assert str(ei.value) == want_err[2]
