@@ -413,6 +413,9 @@ struct pyi_grid {
   // (regular axes with moderate steps), computed on the device at creation
   double u6[2][24]{};
   int u6_ok[2]{0, 0};
+  // node-derivative weights of the six-node spline on x / y (pyi_bicubicw.cuh)
+  int w_ok{0};
+  double w6[2][12]{};
 };
 
 extern "C" {
@@ -623,6 +626,29 @@ pyi_grid* pyi_grid_create(int ndim, const pyi_axis* const* axes, int dtype, cons
       cudaFree(d_tmp);
     }
     cudaGetLastError();
+    // derivative weights of the weights kernel: both axes regular (and closing
+    // their period when circular), steps in the fast path's range
+    double* d_w = nullptr;
+    if (cudaMalloc(reinterpret_cast<void**>(&d_w), 12 * sizeof(double)) == cudaSuccess) {
+      int have = 0;
+      for (int k = 0; k < 2; ++k) {
+        const pyi::DAxis& a = g->dax[k];
+        const double mag = std::fabs(a.step);
+        const bool closes = !a.periodic || std::fabs(static_cast<double>(a.n) * a.step) == a.period;
+        if (a.coord_i64 || a.n < 6 || a.kind != 0 || !closes ||
+            !(mag >= 9.313225746154785e-10 && mag <= 1073741824.0)) {
+          break;
+        }
+        if (pyi::launch_spline6_weights(a.step, d_w, nullptr) != cudaSuccess ||
+            cudaMemcpy(g->w6[k], d_w, 12 * sizeof(double), cudaMemcpyDeviceToHost) != cudaSuccess) {
+          break;
+        }
+        ++have;
+      }
+      g->w_ok = have == 2;
+      cudaFree(d_w);
+    }
+    cudaGetLastError();
   }
   pyi_grid* raw = g.release();
   if (flags & PYI_GRID_PACK_CELLS) {
@@ -813,79 +839,18 @@ int pyi_windowed2d(const pyi_grid* grid, const pyi_windowed_config* cfg, int64_t
   if (st != PYI_OK) return st;
   if (!grid || !cfg || n < 0) return fail(PYI_BAD_ARG, "pyi_windowed2d: null argument");
   if (grid->ndim != 2) return fail(PYI_BAD_ARG, "pyi_windowed2d: bivariate requires 2D grid");
-  if (cfg->half_x < 1 || cfg->half_y < 1) {
-    return fail(PYI_BAD_ARG, "Half window sizes must be at least 1");  // cache.hpp:258-260
-  }
-  if (cfg->half_x > 16 || cfg->half_y > 16) {
-    return fail(PYI_BAD_ARG, "pyi_windowed2d: half window sizes above 16 are not supported");
-  }
   if (cfg->method != PYI_W_BICUBIC && cfg->method != PYI_W_BILINEAR) {
     return fail(PYI_BAD_ARG, "pyi_windowed2d: unknown method");
   }
-  if (n > 0 && (!x || !y || !out)) return fail(PYI_BAD_SHAPE, "pyi_windowed2d: missing array");
-  if (n == 0) return PYI_OK;
-  pyi::WinParams p{};
-  p.ax[0] = grid->dax[0];
-  p.ax[1] = grid->dax[1];
-  p.data = grid->d_data;
-  p.dtype = grid->dtype;
-  p.method = cfg->method;
-  p.half_x = cfg->half_x;
-  p.half_y = cfg->half_y;
-  p.boundary = cfg->boundary;
-  p.bounds_error = cfg->bounds_error;
-  for (int a = 0; a < 2; ++a) {
-    p.u6_ok[a] = grid->u6_ok[a];
-    std::memcpy(p.u6[a], grid->u6[a], sizeof(p.u6[a]));
-  }
-  const size_t out_elem = result_is_f64(grid->dtype) ? 8 : 4;
-  if (mem == PYI_MEM_DEVICE) {
-    cudaStream_t s = static_cast<cudaStream_t>(stream);
-    p.n = n;
-    p.x = x;
-    p.y = y;
-    p.out = out;
-    p.oob_key = grid->d_oob;
-    if (cfg->bounds_error) {
-      PYI_CUDA(cudaMemsetAsync(grid->d_oob, 0xff, sizeof(unsigned long long), s));
-    }
-    cudaError_t e = pyi::launch_windowed2d(p, s);
-    if (e != cudaSuccess) return cuda_fail(e, "windowed2d kernel");
-    if (cfg->bounds_error) {
-      unsigned long long key = pyi::kNoOob;
-      PYI_CUDA(cudaMemcpyAsync(&key, grid->d_oob, sizeof(key), cudaMemcpyDeviceToHost, s));
-      PYI_CUDA(cudaStreamSynchronize(s));
-      return report_oob(key, oob_index, oob_axis);
-    }
-    return PYI_OK;
-  }
-  std::vector<Column> cols(3);
-  cols[0].host_in = x;
-  cols[1].host_in = y;
-  cols[2].host_out = out;
-  cols[2].elem = out_elem;
-  Workspace& ws = workspace();
-  std::lock_guard<std::recursive_mutex> ws_lock(ws.mu);
-  st = ws.ensure(0, 0);
-  if (st != PYI_OK) return st;
-  PYI_CUDA(cudaMemset(ws.oob_key, 0xff, sizeof(unsigned long long)));
-  st = run_pipeline(n, cols, [&](cudaStream_t s, long long begin, long long count, char* dev) {
-    pyi::WinParams q = p;
-    q.n = count;
-    q.x = reinterpret_cast<const double*>(dev + cols[0].dev_off);
-    q.y = reinterpret_cast<const double*>(dev + cols[1].dev_off);
-    q.out = dev + cols[2].dev_off;
-    q.oob_key = ws.oob_key;
-    q.index_base = begin;
-    return pyi::launch_windowed2d(q, s);
-  });
-  if (st != PYI_OK) return st;
-  if (cfg->bounds_error) {
-    unsigned long long key = pyi::kNoOob;
-    PYI_CUDA(cudaMemcpy(&key, ws.oob_key, sizeof(key), cudaMemcpyDeviceToHost));
-    return report_oob(key, oob_index, oob_axis);
-  }
-  return PYI_OK;
+  // same kernels as the N-D entry (pyi_windowed_method == the first two pyi_spatial_method)
+  pyi_windowed_nd_config c{};
+  c.method = cfg->method;
+  c.half_x = cfg->half_x;
+  c.half_y = cfg->half_y;
+  c.boundary = cfg->boundary;
+  c.bounds_error = cfg->bounds_error;
+  c.num_threads = cfg->num_threads;
+  return pyi_windowed(grid, &c, n, x, y, nullptr, nullptr, out, mem, oob_index, oob_axis, stream);
 }
 
 int pyi_windowed(const pyi_grid* grid, const pyi_windowed_nd_config* cfg, int64_t n,
@@ -936,6 +901,8 @@ int pyi_windowed(const pyi_grid* grid, const pyi_windowed_nd_config* cfg, int64_
     if (st != PYI_OK) return st;
     p.planes = grid->d_planes;
   }
+  p.w_ok = grid->w_ok;
+  for (int a = 0; a < 2; ++a) std::memcpy(p.w6[a], grid->w6[a], sizeof(p.w6[a]));
   const size_t out_elem = result_is_f64(grid->dtype) ? 8 : 4;
   if (mem == PYI_MEM_DEVICE) {
     cudaStream_t s = static_cast<cudaStream_t>(stream);

@@ -74,6 +74,10 @@ struct WinNdParams {
   int32_t u6_ok[2];
   const void* planes;  // plane-major copy [z][u][x][y] (3-D / 4-D bicubic fast path) or null
   int32_t redo;        // generic kernel: recompute only the points tagged by the fast pass
+  // node-derivative weights of the six-node natural spline of the (uniform)
+  // x / y axes (pyi_bicubicw.cuh), valid when w_ok
+  int32_t w_ok;
+  double w6[2][12];
 };
 
 struct FindParams {
@@ -104,6 +108,8 @@ cudaError_t fill_multigrid(void* grid, int dtype, long long nx, long long ny, in
                            int periodic, unsigned long long max_iterations, double epsilon,
                            unsigned pre_smooth, unsigned post_smooth,
                            unsigned long long* iterations, double* residual, cudaStream_t stream);
+// six-node spline derivative weights of an axis (pyi_bicubicw.cuh)
+cudaError_t launch_spline6_weights(double step, double* out12, cudaStream_t stream);
 // plane-major copy of a 3-D / 4-D grid: [x][y][z][u] -> [z][u][x][y]
 cudaError_t launch_plane_major(const void* in, void* out, int elem_size, const long long* shape,
                                cudaStream_t stream);

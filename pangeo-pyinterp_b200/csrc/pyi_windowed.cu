@@ -7,6 +7,12 @@
 namespace pyi {
 // Debug knob for the parity tests: PYINTERP_B200_GENERIC=1 routes windowed calls
 // through the generic kernel so the fast path can be compared with it.
+// PYINTERP_B200_BICUBIC=exact keeps the bit-identical bicubic fast paths
+// (pyi_fastwin*.cuh) instead of the precomputed-weights kernel (pyi_bicubicw.cuh).
+static bool exact_bicubic() {
+  const char* e = getenv("PYINTERP_B200_BICUBIC");
+  return e != nullptr && e[0] == 'e';
+}
 static bool force_generic() {
   const char* e = getenv("PYINTERP_B200_GENERIC");
   return e != nullptr && e[0] == '1';
@@ -15,6 +21,7 @@ static bool force_generic() {
 #include "pyi_windowed.cuh"
 #include "pyi_fastwin.cuh"
 #include "pyi_fastwin_nd.cuh"
+#include "pyi_bicubicw.cuh"
 
 namespace pyi {
 // K6 (pyi_windowed_nd.cuh) is instantiated per window capacity in
@@ -27,6 +34,16 @@ extern template cudaError_t launch_windowed_nd_w<32>(const WinNdParams&, cudaStr
 
 cudaError_t launch_windowed_nd(const WinNdParams& p, cudaStream_t stream) {
   if (p.n <= 0) return cudaSuccess;
+  // bicubic on a 6 x 6 window, 2-D .. 4-D: precomputed-weights pass, then the
+  // generic kernel recomputes the points that pass tagged
+  if (p.ndim >= 2 && p.method == PYI_S_BICUBIC && p.half_x == 3 && p.half_y == 3 && p.w_ok &&
+      (p.ndim == 2 || p.planes) && !force_generic() && !exact_bicubic()) {
+    cudaError_t e = launch_bicubicw(p, stream);
+    if (e != cudaSuccess) return e;
+    WinNdParams q = p;
+    q.redo = 1;
+    return launch_windowed_nd_w<6>(q, stream);
+  }
   // 2-D bicubic / bilinear keep K4 and its fast path
   if (p.ndim == 2 && p.method <= PYI_S_BILINEAR) {
     WinParams q{};

@@ -37,3 +37,15 @@ def synthetic():
 def pyi():
     """The product package (needs the CUDA library; GPU tests only)."""
     return importlib.import_module("pangeo-pyinterp_b200")
+
+
+@pytest.fixture(params=["weights", "exact"])
+def bicubic_mode(request, monkeypatch):
+    """The two 6 x 6 bicubic fast paths: the default precomputed-weights kernel
+    (pyi_bicubicw.cuh; values within the north-star tolerance) and the
+    bit-identical one (PYINTERP_B200_BICUBIC=exact, pyi_fastwin*.cuh)."""
+    if request.param == "exact":
+        monkeypatch.setenv("PYINTERP_B200_BICUBIC", "exact")
+    else:
+        monkeypatch.delenv("PYINTERP_B200_BICUBIC", raising=False)
+    return request.param

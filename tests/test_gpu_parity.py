@@ -344,7 +344,7 @@ def test_bounds_error_first_point_and_axis(pyi, orc_best):
 @pytest.mark.parametrize("method", ["bicubic", "bilinear"])
 @pytest.mark.parametrize("boundary", ["undef", "shrink"])
 @pytest.mark.parametrize("half", [(3, 3), (2, 4), (1, 1), (5, 2), (8, 8)])
-def test_windowed2d(pyi, orc_best, method, boundary, half):
+def test_windowed2d(pyi, orc_best, bicubic_mode, method, boundary, half):
     n = 30_000
     for dtype, nan in (("float64", 0.0), ("float32", 0.002), ("int16", 0.0)):
         grid, caxes, g = _grid_pair(pyi, orc_best, 2, dtype, nan=nan)
@@ -355,8 +355,9 @@ def test_windowed2d(pyi, orc_best, method, boundary, half):
         want, _ = orc_best.windowed2d(caxes, g, q[0], q[1], method=0 if method == "bicubic" else 1,
                                       half_x=half[0], half_y=half[1], boundary=boundary, num_threads=0,
                                       stateless=True)
-        exact = close(got, want, 50.0, f"{method} {boundary} {half} {dtype}")
-        assert exact == 1.0  # identical operation sequence per spline solve
+        exact = close(got, want, 50.0, f"{method} {boundary} {half} {dtype}")  # 1e-12 / 1e-5 inside
+        # identical operation sequence per spline solve, except in the weights kernel
+        assert exact == 1.0 or (bicubic_mode == "weights" and method == "bicubic" and half == (3, 3))
 
 
 @pytest.mark.parametrize("case", [
@@ -452,10 +453,20 @@ def _bicubic_both(pyi, grid, x, y, **kw):
     return fast, generic
 
 
+def _same_or_close(mode, a, b, what):
+    """exact mode: bit for bit; weights mode: NaN positions identical, values
+    within 1e-12 (float64) / 1e-5 (float32) of max(|a|, |b|, 50)."""
+    if mode == "exact":
+        assert np.array_equal(a, b, equal_nan=True), what
+    else:
+        close(a, b, 50.0, what)
+
+
 @pytest.mark.parametrize("boundary", ["undef", "shrink"])
-def test_bicubic6_fast_path_full_grid(pyi, orc_best, boundary):
-    """The register-resident 6 x 6 bicubic kernel (pyi_fastwin.cuh) on the 0.25
-    degree grid: bit-identical to the generic kernel and to the oracle."""
+def test_bicubic6_fast_path_full_grid(pyi, orc_best, bicubic_mode, boundary):
+    """The 6 x 6 bicubic fast kernels on the 0.25 degree grid against the generic
+    kernel and the oracle: bit-identical (pyi_fastwin.cuh) or within tolerance
+    (pyi_bicubicw.cuh)."""
     s = pyi.synthetic
     lon, lat = s.lon_axis_values(), s.lat_axis_values()
     g = s.field(lon, lat)
@@ -468,15 +479,16 @@ def test_bicubic6_fast_path_full_grid(pyi, orc_best, boundary):
     x[2::1017] = np.inf
     y[3::1019] = 1e300
     fast, generic = _bicubic_both(pyi, grid, x, y, boundary_mode=boundary)
-    assert np.array_equal(fast, generic, equal_nan=True)
+    _same_or_close(bicubic_mode, fast, generic, "fast vs generic")
     caxes = [orc_best.axis(lon, period=360.0), orc_best.axis(lat)]
     want, _ = orc_best.windowed2d(caxes, g, x, y, boundary=boundary, num_threads=0, stateless=True)
-    assert np.array_equal(fast, want, equal_nan=True)
+    assert np.array_equal(generic, want, equal_nan=True)
+    _same_or_close(bicubic_mode, fast, want, "fast vs oracle")
     assert np.isfinite(fast).mean() > 0.95
 
 
 @pytest.mark.parametrize("dtype", ["float64", "float32", "int32", "uint8"])
-def test_bicubic6_fast_path_awkward_values(pyi, orc_best, dtype):
+def test_bicubic6_fast_path_awkward_values(pyi, orc_best, bicubic_mode, dtype):
     """Values for which the short division of the fast path is not proven
     (huge, tiny, subnormal, infinite, NaN) take the generic code; zeros and
     constant patches stay on the fast path.  Irregular and non-periodic axes."""
@@ -485,7 +497,11 @@ def test_bicubic6_fast_path_awkward_values(pyi, orc_best, dtype):
     lat = np.degrees(np.arcsin(np.linspace(-0.999, 0.999, 90)))
     g = rng.normal(size=(200, 90)) * 30
     if dtype == "float64":
-        g[rng.random(g.shape) < 0.01] = 1e250
+        if bicubic_mode == "exact":
+            # 1e250 next to O(30) values: the result is dominated by the rounding of
+            # whichever operation order is used; only the bit-identical path can be
+            # compared (the weights kernel agrees to ~1e-16 of the WINDOW's magnitude)
+            g[rng.random(g.shape) < 0.01] = 1e250
         g[rng.random(g.shape) < 0.01] = 1e-305
         g[rng.random(g.shape) < 0.01] = 5e-324
         g[rng.random(g.shape) < 0.005] = np.inf
@@ -498,10 +514,12 @@ def test_bicubic6_fast_path_awkward_values(pyi, orc_best, dtype):
         x = rng.uniform(-200, 500, 100_000)
         y = rng.uniform(-91, 91, 100_000)
         fast, generic = _bicubic_both(pyi, grid, x, y)
-        assert np.array_equal(fast, generic, equal_nan=True)
+        _same_or_close(bicubic_mode, fast, generic, "fast vs generic")
         caxes = [orc_best.axis(lon, **kw), orc_best.axis(lat)]
         want, _ = orc_best.windowed2d(caxes, g, x, y, num_threads=0, stateless=True)
-        assert np.array_equal(fast, want, equal_nan=True)
+        assert np.array_equal(generic, want, equal_nan=True)
+        _same_or_close(bicubic_mode, fast, want, "fast vs oracle")
+        assert np.array_equal(np.isinf(fast), np.isinf(want))
 
 
 def test_windowed2d_bounds_error_in_late_chunk(pyi, orc_best):
