@@ -80,6 +80,35 @@ __device__ __forceinline__ double dot6(const double* w, const double (&v)[6]) {
   return s;
 }
 
+// Six consecutive grid values from element `base`.  float64 grids: aligned
+// 16-byte loads covering the run (3 when base is even, 4 when odd) instead of
+// six 8-byte ones; `cells` bounds the over-read of the odd case.
+template <int DT>
+__device__ __forceinline__ void load_row6(const void* data, int dtype, long long base,
+                                          long long cells, bool ok, double (&v)[6]) {
+  if (DT == PYI_F64) {
+    const long long b0 = base & ~1LL;
+    const bool odd = (base & 1LL) != 0;
+    if (b0 + 8 <= cells) {
+      const double2* q = reinterpret_cast<const double2*>(static_cast<const double*>(data) + b0);
+      const double2 zero = make_double2(0.0, 0.0);
+      const double2 t0 = ok ? __ldg(q) : zero;
+      const double2 t1 = ok ? __ldg(q + 1) : zero;
+      const double2 t2 = ok ? __ldg(q + 2) : zero;
+      const double2 t3 = ok && odd ? __ldg(q + 3) : zero;
+      v[0] = odd ? t0.y : t0.x;
+      v[1] = odd ? t1.x : t0.y;
+      v[2] = odd ? t1.y : t1.x;
+      v[3] = odd ? t2.x : t1.y;
+      v[4] = odd ? t2.y : t2.x;
+      v[5] = odd ? t3.x : t2.y;
+      return;
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 6; ++j) v[j] = ok ? load_value<DT, double>(data, dtype, base + j) : 0.0;
+}
+
 // One query point.  Returns false when it has to be recomputed by the generic
 // kernel.
 template <int DT, int ND, typename ZT, typename R>
@@ -132,37 +161,61 @@ __device__ __forceinline__ bool bicubicw_point(const WinNdParams& p, double x, d
       const int pu = ND == 4 ? ((t & 1) ? iu1 : iu0) : 0;
       plane_offset = (pz * n3 + pu) * plane_cells;
     }
-    // rows: z and dz/dy at the columns 2, 3 of each of the six rows
-    double c_z2[6], c_z3[6], c_y2[6], c_y3[6];
-    {
-      const double* wy = p.w6[1];
+    // Row by row: z and dz/dy at the columns 2, 3 (dot products with Wy), folded
+    // at once into the four column derivatives d/dx at the rows 2, 3 (dot
+    // products with Wx, accumulated in row order = dot6's order).
+    const double* wy = p.w6[1];
+    const double* wx = p.w6[0];
+    double zz[4], zy_[4], zx_[4], zxy_[4];
 #pragma unroll
-      for (int i = 0; i < 6; ++i) {
-        const int ii = wx0 + i;
-        const long long base = plane_offset + (ii >= nx ? ii - nx : ii) * n1 + wy0;
-        double v[6];
+    for (int i = 0; i < 6; ++i) {
+      const int ii = wx0 + i;
+      const long long base = plane_offset + (ii >= nx ? ii - nx : ii) * n1 + wy0;
+      double v[6];
+      load_row6<DT>(data, p.dtype, base, p.cells, ok, v);
+      const double y2 = dot6(wy, v);
+      const double y3 = dot6(wy + 6, v);
+      if (DT != -1 && (y2 != y2 || y3 != y3)) {
+        // rare: a NaN (-> NaN result, cache.hpp:165-171) or an infinity (-> generic)
+        bool nan_here = false;
 #pragma unroll
-        for (int j = 0; j < 6; ++j) v[j] = ok ? load_value<DT, double>(data, p.dtype, base + j) : 0.0;
-        c_z2[i] = v[2];
-        c_z3[i] = v[3];
-        c_y2[i] = dot6(wy, v);
-        c_y3[i] = dot6(wy + 6, v);
-        if (DT != -1 && (c_y2[i] != c_y2[i] || c_y3[i] != c_y3[i])) {
-          // rare: a NaN (-> NaN result, cache.hpp:165-171) or an infinity (-> generic)
-          bool nan_here = false;
-#pragma unroll
-          for (int j = 0; j < 6; ++j) nan_here = nan_here || v[j] != v[j];
-          has_nan = has_nan || nan_here;
-          weird = weird || !nan_here;
-        }
+        for (int j = 0; j < 6; ++j) nan_here = nan_here || v[j] != v[j];
+        has_nan = has_nan || nan_here;
+        weird = weird || !nan_here;
+      }
+      if (i == 2) {
+        zz[0] = v[2];
+        zz[1] = v[3];
+        zy_[0] = y2;
+        zy_[1] = y3;
+      }
+      if (i == 3) {
+        zz[2] = v[2];
+        zz[3] = v[3];
+        zy_[2] = y2;
+        zy_[3] = y3;
+      }
+      // index 0: (i0,j0) 1: (i0,j1) 2: (i1,j0) 3: (i1,j1)
+      if (i == 0) {
+        zx_[0] = __dmul_rn(wx[0], v[2]);
+        zx_[1] = __dmul_rn(wx[0], v[3]);
+        zx_[2] = __dmul_rn(wx[6], v[2]);
+        zx_[3] = __dmul_rn(wx[6], v[3]);
+        zxy_[0] = __dmul_rn(wx[0], y2);
+        zxy_[1] = __dmul_rn(wx[0], y3);
+        zxy_[2] = __dmul_rn(wx[6], y2);
+        zxy_[3] = __dmul_rn(wx[6], y3);
+      } else {
+        zx_[0] = fma(wx[i], v[2], zx_[0]);
+        zx_[1] = fma(wx[i], v[3], zx_[1]);
+        zx_[2] = fma(wx[6 + i], v[2], zx_[2]);
+        zx_[3] = fma(wx[6 + i], v[3], zx_[3]);
+        zxy_[0] = fma(wx[i], y2, zxy_[0]);
+        zxy_[1] = fma(wx[i], y3, zxy_[1]);
+        zxy_[2] = fma(wx[6 + i], y2, zxy_[2]);
+        zxy_[3] = fma(wx[6 + i], y3, zxy_[3]);
       }
     }
-    // columns: d/dx of those four columns at the rows 2, 3
-    const double* wx = p.w6[0];
-    const double zz[4] = {c_z2[2], c_z3[2], c_z2[3], c_z3[3]};
-    const double zy_[4] = {c_y2[2], c_y3[2], c_y2[3], c_y3[3]};
-    const double zx_[4] = {dot6(wx, c_z2), dot6(wx, c_z3), dot6(wx + 6, c_z2), dot6(wx + 6, c_z3)};
-    const double zxy_[4] = {dot6(wx, c_y2), dot6(wx, c_y3), dot6(wx + 6, c_y2), dot6(wx + 6, c_y3)};
     f[t] = bicubic_cell(x, y, xc[0], xc[1], yc[0], yc[1], zz, zx_, zy_, zxy_);
   }
   if (!ok) return false;
@@ -195,8 +248,8 @@ __device__ __forceinline__ bool bicubicw_point(const WinNdParams& p, double x, d
   return true;
 }
 
-template <int DT, int ND, typename ZT, typename R>
-__global__ void __launch_bounds__(128)
+template <int DT, int ND, typename ZT, typename R, int MINB>
+__global__ void __launch_bounds__(128, MINB)
 bicubicw_kernel(const __grid_constant__ WinNdParams p) {
   const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
   R* __restrict__ out = static_cast<R*>(p.out);
@@ -212,26 +265,39 @@ bicubicw_kernel(const __grid_constant__ WinNdParams p) {
   }
 }
 
-template <int ND, typename ZT>
-static cudaError_t launch_bicubicw_z(const WinNdParams& p, cudaStream_t stream) {
-  const int blocks = grid_for(p.n, 128, 8);
+template <int ND, typename ZT, int MINB>
+static cudaError_t launch_bicubicw_m(const WinNdParams& p, cudaStream_t stream) {
+  const int blocks = grid_for(p.n, 128, MINB < 4 ? 8 : MINB);
   switch (p.dtype) {
     case PYI_F64:
-      bicubicw_kernel<PYI_F64, ND, ZT, double><<<blocks, 128, 0, stream>>>(p);
+      bicubicw_kernel<PYI_F64, ND, ZT, double, MINB><<<blocks, 128, 0, stream>>>(p);
       break;
     case PYI_F32:
-      bicubicw_kernel<PYI_F32, ND, ZT, float><<<blocks, 128, 0, stream>>>(p);
+      bicubicw_kernel<PYI_F32, ND, ZT, float, MINB><<<blocks, 128, 0, stream>>>(p);
       break;
     case PYI_I64:
     case PYI_U64:
-      bicubicw_kernel<-1, ND, ZT, double><<<blocks, 128, 0, stream>>>(p);
+      bicubicw_kernel<-1, ND, ZT, double, MINB><<<blocks, 128, 0, stream>>>(p);
       break;
     default:
-      bicubicw_kernel<-1, ND, ZT, float><<<blocks, 128, 0, stream>>>(p);
+      bicubicw_kernel<-1, ND, ZT, float, MINB><<<blocks, 128, 0, stream>>>(p);
       break;
   }
   g_launches.fetch_add(1);
   return cudaGetLastError();
+}
+
+template <int ND, typename ZT>
+static cudaError_t launch_bicubicw_z(const WinNdParams& p, cudaStream_t stream) {
+  // experiment knob: resident blocks per SM (register cap)
+  const char* e = getenv("PYINTERP_B200_W_MINB");
+  const int minb = e ? atoi(e) : 4;
+  if (minb == 1) return launch_bicubicw_m<ND, ZT, 1>(p, stream);
+  if (minb == 3) return launch_bicubicw_m<ND, ZT, 3>(p, stream);
+  if (minb == 5) return launch_bicubicw_m<ND, ZT, 5>(p, stream);
+  if (minb == 6) return launch_bicubicw_m<ND, ZT, 6>(p, stream);
+  if (minb == 8) return launch_bicubicw_m<ND, ZT, 8>(p, stream);
+  return launch_bicubicw_m<ND, ZT, 4>(p, stream);
 }
 
 // The weights pass; the caller follows it with the generic kernel in redo mode.

@@ -903,6 +903,8 @@ int pyi_windowed(const pyi_grid* grid, const pyi_windowed_nd_config* cfg, int64_
   }
   p.w_ok = grid->w_ok;
   for (int a = 0; a < 2; ++a) std::memcpy(p.w6[a], grid->w6[a], sizeof(p.w6[a]));
+  p.cells = 1;
+  for (int a = 0; a < nd; ++a) p.cells *= grid->shape[a];
   const size_t out_elem = result_is_f64(grid->dtype) ? 8 : 4;
   if (mem == PYI_MEM_DEVICE) {
     cudaStream_t s = static_cast<cudaStream_t>(stream);

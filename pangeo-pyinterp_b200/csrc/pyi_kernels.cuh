@@ -78,6 +78,7 @@ struct WinNdParams {
   // x / y axes (pyi_bicubicw.cuh), valid when w_ok
   int32_t w_ok;
   double w6[2][12];
+  long long cells;  // elements of the whole grid (bounds the vector loads)
 };
 
 struct FindParams {
