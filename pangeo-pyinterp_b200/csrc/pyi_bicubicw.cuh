@@ -289,15 +289,15 @@ static cudaError_t launch_bicubicw_m(const WinNdParams& p, cudaStream_t stream) 
 
 template <int ND, typename ZT>
 static cudaError_t launch_bicubicw_z(const WinNdParams& p, cudaStream_t stream) {
-  // experiment knob: resident blocks per SM (register cap)
+  // Resident blocks per SM (register cap).  2-D (L2-resident grid, latency
+  // bound): 5 blocks x 128 threads at 96 registers measured best of {4, 5, 6, 8}
+  // (12.3 / 13.2 / 12.5 / 10.8 Gpts/s).  3-D / 4-D (DRAM bound): no cap, the
+  // compiler keeps more loads in flight per thread.  PYINTERP_B200_W_MINB=1|5
+  // overrides for experiments.
   const char* e = getenv("PYINTERP_B200_W_MINB");
-  const int minb = e ? atoi(e) : 4;
-  if (minb == 1) return launch_bicubicw_m<ND, ZT, 1>(p, stream);
-  if (minb == 3) return launch_bicubicw_m<ND, ZT, 3>(p, stream);
+  const int minb = e ? atoi(e) : (ND == 2 ? 5 : 1);
   if (minb == 5) return launch_bicubicw_m<ND, ZT, 5>(p, stream);
-  if (minb == 6) return launch_bicubicw_m<ND, ZT, 6>(p, stream);
-  if (minb == 8) return launch_bicubicw_m<ND, ZT, 8>(p, stream);
-  return launch_bicubicw_m<ND, ZT, 4>(p, stream);
+  return launch_bicubicw_m<ND, ZT, 1>(p, stream);
 }
 
 // The weights pass; the caller follows it with the generic kernel in redo mode.
