@@ -109,6 +109,33 @@ __device__ __forceinline__ void load_row6(const void* data, int dtype, long long
   for (int j = 0; j < 6; ++j) v[j] = ok ? load_value<DT, double>(data, dtype, base + j) : 0.0;
 }
 
+// window6 (pyi_fastwin.cuh) that also recognises the windows for which the
+// generic code (window_indexes, pyi_windowed.cuh) certainly fails in the
+// "undef" boundary mode -- coordinate not bracketed by the axis, or a forward
+// bracket whose six-node window leaves a non-periodic axis: the result is then
+// NaN (cache_loader.hpp:69-80) and nothing has to be recomputed.
+__device__ __forceinline__ bool window6_or_nan(const DAxis& a, double c, int& w0, bool& is_nan) {
+  int p0, p1;
+  const int n = a.n;
+  if (!find_indexes<double>(a, c, p0, p1)) {
+    is_nan = is_nan || n != 1;  // singleton axes have their own rule (axis.hpp:823-832)
+    return false;
+  }
+  if (a.periodic) {
+    if (n < 6) return false;
+    const bool fwd = (p1 == p0 + 1) || (p0 == n - 1 && p1 == 0);
+    w0 = p0 - 2 < 0 ? p0 - 2 + n : p0 - 2;
+    return fwd;
+  }
+  if (p1 != p0 + 1) return false;
+  w0 = p0 - 2;
+  if (w0 < 0 || p1 + 2 >= n) {
+    is_nan = true;
+    return false;
+  }
+  return true;
+}
+
 // One query point.  Returns false when it has to be recomputed by the generic
 // kernel.
 template <int DT, int ND, typename ZT, typename R>
@@ -119,11 +146,25 @@ __device__ __forceinline__ bool bicubicw_point(const WinNdParams& p, double x, d
   int wx0 = 0, wy0 = 0, iz0 = 0, iz1 = 0, iu0 = 0, iu1 = 0;
   // norm_fast needs a positive period and quotients below 2^48
   bool ok = sane(x) && sane(y) && (ax.period == 0.0 || ax.period > 0.0078125);
-  ok = ok && window6(ax, x, wx0) && window6(ay, y, wy0);
+  // certain NaN: only without bounds_error (an out-of-bounds coordinate must be
+  // reported) and in the undef boundary mode (shrink keeps partial windows)
+  bool is_nan = false;
+  ok = window6_or_nan(ax, x, wx0, is_nan) && ok;
+  ok = window6_or_nan(ay, y, wy0, is_nan) && ok;
   ok = ok && !ay.periodic;  // rows of the window are contiguous in memory
-  if (ND >= 3) ok = ok && window_pair<ZT>(p.ax[2], z, iz0, iz1);
-  if (ND == 4) ok = ok && window_pair<double>(p.ax[3], u, iu0, iu1);
-  if (!PYI_ANY(ok)) return false;
+  if (ND >= 3 && !window_pair<ZT>(p.ax[2], z, iz0, iz1)) {
+    ok = false;
+    is_nan = true;  // window_pair only fails on a non-singleton axis
+  }
+  if (ND == 4 && !window_pair<double>(p.ax[3], u, iu0, iu1)) {
+    ok = false;
+    is_nan = true;
+  }
+  is_nan = is_nan && p.boundary == PYI_BOUNDARY_UNDEF && !p.bounds_error;
+  if (!PYI_ANY(ok)) {
+    res = RT<R>::nan();
+    return is_nan;
+  }
   wx0 = ok ? wx0 : 0;
   wy0 = ok ? wy0 : 0;
   const int nx = ax.n;
@@ -145,7 +186,10 @@ __device__ __forceinline__ bool bicubicw_point(const WinNdParams& p, double x, d
   // the bracket holds c strictly in the window's own order (window_usable)
   ok = ok && (xc[0] < xc[1] ? (xc[0] < x && x <= xc[1]) : (xc[0] > x && x >= xc[1]));
   ok = ok && (yc[0] < yc[1] ? (yc[0] < y && y <= yc[1]) : (yc[0] > y && y >= yc[1]));
-  if (!PYI_ANY(ok)) return false;
+  if (!PYI_ANY(ok)) {
+    res = RT<R>::nan();
+    return is_nan;
+  }
   const long long n1 = ay.n;
   const long long plane_cells = static_cast<long long>(nx) * n1;
   const long long n3 = ND == 4 ? p.ax[3].n : 1;
@@ -218,7 +262,10 @@ __device__ __forceinline__ bool bicubicw_point(const WinNdParams& p, double x, d
     }
     f[t] = bicubic_cell(x, y, xc[0], xc[1], yc[0], yc[1], zz, zx_, zy_, zxy_);
   }
-  if (!ok) return false;
+  if (!ok) {
+    res = RT<R>::nan();
+    return is_nan;
+  }
   if (has_nan) {
     res = RT<R>::nan();
     return true;

@@ -227,9 +227,6 @@ windowed_nd_kernel(const __grid_constant__ WinNdParams p) {
   const ZT* __restrict__ zs = static_cast<const ZT*>(p.z);
   for (long long k = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; k < p.n;
        k += stride) {
-    // redo mode (after the bicubic fast pass, pyi_fastwin_nd.cuh): only the
-    // points tagged by that pass are computed
-    if (p.redo && !RedoTag<R>::is(out[k])) continue;
     R res;
     const double y = ND >= 2 ? __ldg(p.y + k) : 0.0;
     const ZT z = ND >= 3 ? __ldg(zs + k) : ZT{};
@@ -247,10 +244,85 @@ windowed_nd_kernel(const __grid_constant__ WinNdParams p) {
   }
 }
 
+// Redo pass after a bicubic fast pass (pyi_bicubicw.cuh, pyi_fastwin_nd.cuh):
+// only the points that pass tagged are computed.  Tagged points are sparse
+// (window at an edge, out-of-bounds or non-finite input), so each warp scans
+// its share of the output, queues the tagged indexes in shared memory and
+// runs the generic code on 32 queued points at a time -- full warps instead of
+// one live lane per tagged point.
+template <int MAXW, int ND, typename ZT, typename R>
+__global__ void __launch_bounds__(128)
+windowed_nd_redo_kernel(const __grid_constant__ WinNdParams p) {
+  __shared__ long long queue[4][64];
+  const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  long long* q = queue[warp];
+  unsigned queued = 0;
+  unsigned long long key = kNoOob;
+  R* __restrict__ out = static_cast<R*>(p.out);
+  const ZT* __restrict__ zs = static_cast<const ZT*>(p.z);
+  auto compute = [&](long long k) {
+    R res;
+    const double y = ND >= 2 ? __ldg(p.y + k) : 0.0;
+    const ZT z = ND >= 3 ? __ldg(zs + k) : ZT{};
+    const double u = ND >= 4 ? __ldg(p.u + k) : 0.0;
+    const int bad = windowed_nd_point<MAXW, ND, ZT, R>(p, __ldg(p.x + k), y, z, u, res);
+    if (bad >= 0) {
+      const unsigned long long kk =
+          (static_cast<unsigned long long>(p.index_base + k) << 2) | bad;
+      key = kk < key ? kk : key;
+    }
+    out[k] = res;
+  };
+  // the scan reads kScan x 32 outputs per step so that the loads overlap
+  constexpr int kScan = 8;
+  const long long warps = static_cast<long long>(gridDim.x) * 4;
+  const long long first = (static_cast<long long>(blockIdx.x) * 4 + warp) * (32 * kScan);
+  for (long long base = first; base < p.n; base += warps * (32 * kScan)) {
+    R seen[kScan];
+#pragma unroll
+    for (int j = 0; j < kScan; ++j) {
+      const long long k = base + j * 32 + lane;
+      seen[j] = k < p.n ? __ldcs(out + k) : R(0);
+    }
+#pragma unroll
+    for (int j = 0; j < kScan; ++j) {
+      const long long k = base + j * 32 + lane;
+      const bool tagged = RedoTag<R>::is(seen[j]);
+      const unsigned mask = __ballot_sync(0xffffffffu, tagged);
+      if (mask == 0) continue;
+      if (tagged) q[queued + __popc(mask & ((1u << lane) - 1u))] = k;
+      queued += __popc(mask);
+      __syncwarp();
+      if (queued >= 32) {
+        const long long mine = q[lane];
+        const long long moved = lane + 32 < queued ? q[lane + 32] : 0;
+        __syncwarp();
+        q[lane] = moved;
+        queued -= 32;
+        __syncwarp();
+        compute(mine);
+      }
+    }
+  }
+  if (lane < queued) compute(q[lane]);
+  if (p.bounds_error && key != kNoOob) {
+    atomicMin(p.oob_key, key);
+  }
+}
+
 template <int MAXW, int ND, typename ZT>
 static cudaError_t launch_windowed_nd_r(const WinNdParams& p, cudaStream_t stream) {
   const int blocks = grid_for(p.n, 128, 8);
   const bool r64 = p.dtype == PYI_F64 || p.dtype == PYI_I64 || p.dtype == PYI_U64;
+  if (p.redo) {
+    if (r64) {
+      windowed_nd_redo_kernel<MAXW, ND, ZT, double><<<blocks, 128, 0, stream>>>(p);
+    } else {
+      windowed_nd_redo_kernel<MAXW, ND, ZT, float><<<blocks, 128, 0, stream>>>(p);
+    }
+    g_launches.fetch_add(1);
+    return cudaGetLastError();
+  }
   if (r64) {
     windowed_nd_kernel<MAXW, ND, ZT, double><<<blocks, 128, 0, stream>>>(p);
   } else {
