@@ -244,6 +244,24 @@ windowed_nd_kernel(const __grid_constant__ WinNdParams p) {
   }
 }
 
+// One tagged point of the redo pass (not inlined: two call sites, rare path).
+template <int MAXW, int ND, typename ZT, typename R>
+__device__ __noinline__ void redo_point(const WinNdParams& p, long long k,
+                                        unsigned long long& key) {
+  R* out = static_cast<R*>(p.out);
+  const ZT* zs = static_cast<const ZT*>(p.z);
+  R res;
+  const double y = ND >= 2 ? __ldg(p.y + k) : 0.0;
+  const ZT z = ND >= 3 ? __ldg(zs + k) : ZT{};
+  const double u = ND >= 4 ? __ldg(p.u + k) : 0.0;
+  const int bad = windowed_nd_point<MAXW, ND, ZT, R>(p, __ldg(p.x + k), y, z, u, res);
+  if (bad >= 0) {
+    const unsigned long long kk = (static_cast<unsigned long long>(p.index_base + k) << 2) | bad;
+    key = kk < key ? kk : key;
+  }
+  out[k] = res;
+}
+
 // Redo pass after a bicubic fast pass (pyi_bicubicw.cuh, pyi_fastwin_nd.cuh):
 // only the points that pass tagged are computed.  Tagged points are sparse
 // (window at an edge, out-of-bounds or non-finite input), so each warp scans
@@ -260,19 +278,7 @@ windowed_nd_redo_kernel(const __grid_constant__ WinNdParams p) {
   unsigned long long key = kNoOob;
   R* __restrict__ out = static_cast<R*>(p.out);
   const ZT* __restrict__ zs = static_cast<const ZT*>(p.z);
-  auto compute = [&](long long k) {
-    R res;
-    const double y = ND >= 2 ? __ldg(p.y + k) : 0.0;
-    const ZT z = ND >= 3 ? __ldg(zs + k) : ZT{};
-    const double u = ND >= 4 ? __ldg(p.u + k) : 0.0;
-    const int bad = windowed_nd_point<MAXW, ND, ZT, R>(p, __ldg(p.x + k), y, z, u, res);
-    if (bad >= 0) {
-      const unsigned long long kk =
-          (static_cast<unsigned long long>(p.index_base + k) << 2) | bad;
-      key = kk < key ? kk : key;
-    }
-    out[k] = res;
-  };
+  auto compute = [&](long long k) { redo_point<MAXW, ND, ZT, R>(p, k, key); };
   // the scan reads kScan x 32 outputs per step so that the loads overlap
   constexpr int kScan = 8;
   const long long warps = static_cast<long long>(gridDim.x) * 4;
@@ -315,13 +321,18 @@ static cudaError_t launch_windowed_nd_r(const WinNdParams& p, cudaStream_t strea
   const int blocks = grid_for(p.n, 128, 8);
   const bool r64 = p.dtype == PYI_F64 || p.dtype == PYI_I64 || p.dtype == PYI_U64;
   if (p.redo) {
-    if (r64) {
-      windowed_nd_redo_kernel<MAXW, ND, ZT, double><<<blocks, 128, 0, stream>>>(p);
+    // only the 6 x 6 bicubic fast passes (2-D .. 4-D) are followed by a redo pass
+    if constexpr (MAXW == 6 && ND >= 2) {
+      if (r64) {
+        windowed_nd_redo_kernel<MAXW, ND, ZT, double><<<blocks, 128, 0, stream>>>(p);
+      } else {
+        windowed_nd_redo_kernel<MAXW, ND, ZT, float><<<blocks, 128, 0, stream>>>(p);
+      }
+      g_launches.fetch_add(1);
+      return cudaGetLastError();
     } else {
-      windowed_nd_redo_kernel<MAXW, ND, ZT, float><<<blocks, 128, 0, stream>>>(p);
+      return cudaErrorInvalidValue;
     }
-    g_launches.fetch_add(1);
-    return cudaGetLastError();
   }
   if (r64) {
     windowed_nd_kernel<MAXW, ND, ZT, double><<<blocks, 128, 0, stream>>>(p);
