@@ -8,7 +8,8 @@ resident.  One "step" = one pass of the hot path over all points of the rank
 = ONE kernel launch.
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--points P]
-                    [--workload bilinear|bicubic|trivariate|quadrivariate]
+                    [--workload bilinear|bilinear_irrlat|bicubic|trivariate|quadrivariate]
+                    [--no-secondary]
                     [--impl b200|reference]
 
 Prints one JSON line (rank 0).  `value` is device-resident throughput over all
@@ -17,6 +18,11 @@ buffers (H2D + kernel + D2H inside the timed region); `roofline` is the
 algorithmic bytes of the dominant kernel over its CUDA-event duration against
 the measured HBM copy bandwidth; `cpu_baseline` is the reference's CPU path
 (oracle/_ref when built, else the C restatement) timed on this box's cores.
+With the default workload the line also carries `secondary`: short sub-runs
+(3 warm-up + 5 timed passes each, parity-checked against the oracle on every
+rank) of the other BASELINE configurations -- bicubic, trivariate,
+quadrivariate and bilinear on an irregular latitude axis with its point-count
+sweep -- each with its own roofline entry.
 """
 from __future__ import annotations
 
@@ -33,7 +39,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-BYTES_PER_POINT = {"bilinear": 24, "bicubic": 24, "trivariate": 60, "quadrivariate": 100,
+BYTES_PER_POINT = {"bilinear": 24, "bilinear_irrlat": 24, "bicubic": 24, "trivariate": 60, "quadrivariate": 100,
                    # K6: streams only; the windows are compute / L2 work
                    "c_spline2d": 24, "bicubic3d": 28}
 # windowed workloads: fitting model of the public API
@@ -52,11 +58,13 @@ def parse():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU-baseline sample time")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-secondary", action="store_true",
+                    help="skip the short sub-runs of the other BASELINE configurations")
     return ap.parse_args()
 
 
 def default_points(workload: str) -> int:
-    return {"bilinear": 1_000_000_000, "bicubic": 100_000_000, "trivariate": 100_000_000,
+    return {"bilinear": 1_000_000_000, "bilinear_irrlat": 1_000_000_000, "bicubic": 100_000_000, "trivariate": 100_000_000,
             "quadrivariate": 100_000_000, "c_spline2d": 20_000_000, "bicubic3d": 20_000_000}[workload]
 
 
@@ -89,7 +97,9 @@ def build_host_case(workload: str):
     """Axis values + grid array (numpy) of the workload."""
     syn = __import__("importlib").import_module("pangeo-pyinterp_b200.synthetic")
     lon, lat = syn.lon_axis_values(), syn.lat_axis_values()
-    if workload in ("bilinear", "bicubic", "c_spline2d"):
+    if workload == "bilinear_irrlat":  # BASELINE configs[4]: irregular latitude axis
+        lat = syn.irregular_lat_values()
+    if workload in ("bilinear", "bilinear_irrlat", "bicubic", "c_spline2d"):
         return dict(nd=2, lon=lon, lat=lat, grid=syn.field(lon, lat), dtype="f64")
     if workload in ("trivariate", "bicubic3d"):
         t = syn.time_axis_values(365)
@@ -108,6 +118,7 @@ def host_queries(case, n, seed):
 
 def workload_name(workload, n):
     shape = {"bilinear": "bivariate bilinear f64 Grid2D 1440x720 circular lon",
+             "bilinear_irrlat": "bivariate bilinear f64 Grid2D 1440x720 circular lon, irregular (Gaussian-like) latitude",
              "bicubic": "bivariate bicubic (6x6 window) f64 Grid2D 1440x720 circular lon",
              "trivariate": "trivariate bilinear f32 Grid3D 1440x720x365 int64 TemporalAxis",
              "c_spline2d": "bivariate windowed c_spline (6x6 window) f64 Grid2D 1440x720 circular lon",
@@ -267,140 +278,230 @@ class ClockSampler:
 # ---------------------------------------------------------------------------
 # GPU arm
 # ---------------------------------------------------------------------------
-def main():
-    args = parse()
-    if args.impl == "reference":
-        return run_reference_arm(args)
+class Env:
+    """Process-wide state of the GPU arm: rank, device, torch.distributed."""
 
-    import torch
-    import torch.distributed as dist
-    import pyinterp_b200 as pyi
+    def __init__(self):
+        import torch
+        import torch.distributed as dist
+        self.torch, self.dist = torch, dist
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        if not torch.cuda.is_available():
+            raise SystemExit("bench.py: no CUDA device (the product has no CPU fallback)")
+        torch.cuda.set_device(self.local)
+        self.dev = torch.device("cuda", self.local)
+        if self.world > 1:
+            # NCCL's banner / debug lines go to stderr: stdout carries the one JSON line
+            os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+            dist.init_process_group("nccl", device_id=self.dev)
+            warm = torch.zeros(1, device=self.dev)  # communicator set-up is a one-off of the process group
+            dist.all_reduce(warm)
+            torch.cuda.synchronize()
 
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device (the product has no CPU fallback)")
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    if world > 1:
-        # NCCL's banner / debug lines go to stderr: stdout carries the one JSON line
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
-        dist.init_process_group("nccl", device_id=dev)
-    n = int(args.points or default_points(args.workload))
-    case = build_host_case(args.workload)
-    nd = case["nd"]
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
 
-    # grid: generated on rank 0, replicated once over NVLink (one NCCL broadcast)
-    t_arr = torch.from_numpy(case["grid"]).to(dev) if rank == 0 else \
-        torch.empty(case["grid"].shape, dtype=torch.from_numpy(case["grid"][:1]).dtype, device=dev)
+    def max_over_ranks(self, v: float) -> float:
+        if self.world == 1:
+            return float(v)
+        t = self.torch.tensor([v], dtype=self.torch.float64, device=self.dev)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def min_over_ranks(self, v: float) -> float:
+        return -self.max_over_ranks(-v)
+
+
+def make_grid(env, pyi, case):
+    """Grid generated on rank 0 and replicated once over NVLink (one NCCL
+    broadcast per grid handle); returns (grid, broadcast ms)."""
+    torch = env.torch
+    t_arr = torch.from_numpy(case["grid"]).to(env.dev) if env.rank == 0 else \
+        torch.empty(case["grid"].shape, dtype=torch.from_numpy(case["grid"][:1]).dtype, device=env.dev)
     bcast_ms = None
-    if world > 1:
-        # communicator set-up is a one-off of the process group, not of the grid
-        warm = torch.zeros(1, device=dev)
-        dist.all_reduce(warm)
+    if env.world > 1:
         torch.cuda.synchronize()
         t0 = time.perf_counter()
         pyi.dist.broadcast_grid_array(t_arr)
         torch.cuda.synchronize()
         bcast_ms = 1e3 * (time.perf_counter() - t0)
     axes = [pyi.Axis(case["lon"], period=360.0), pyi.Axis(case["lat"])]
-    if nd >= 3:
+    if case["nd"] >= 3:
         axes.append(pyi.TemporalAxis(case["time"]))
-    if nd >= 4:
+    if case["nd"] >= 4:
         axes.append(pyi.Axis(case["depth"]))
-    grid = pyi.Grid(*axes, t_arr)
+    return pyi.Grid(*axes, t_arr), bcast_ms
 
-    # parity guard: a fixed 1e6-point sub-chunk against the CPU oracle before any number is recorded
-    if rank == 0 and not args.no_cpu:
-        q = host_queries(case, 1_000_000, 1001)
-        _, run = cpu_run(case, args.workload, None)
-        if args.workload in WINDOWED:
-            sys.path.insert(0, os.path.join(ROOT, "oracle"))
-            import orc
-            o = orc.Oracle("reference" if orc.available("reference") else "port")
-            oaxes = [o.axis(case["lon"], period=360.0), o.axis(case["lat"])]
-            qq = list(q)
-            if nd >= 3:
-                oaxes.append(o.axis(case["time"].astype("datetime64[ns]").astype(np.int64)))
-                qq[2] = qq[2].view("datetime64[ns]")
-            if args.workload == "bicubic":
-                want, _ = o.windowed2d(oaxes, case["grid"], q[0], q[1], num_threads=0, stateless=True)
-            else:
-                want, _ = o.windowed_nd(oaxes, case["grid"], *q, method=WINDOWED[args.workload], num_threads=0,
-                                        stateless=True)
-            got = {2: pyi.bivariate, 3: pyi.trivariate}[nd](grid, *qq, WINDOWED[args.workload])
+
+def oracle_guard(env, pyi, case, grid, workload):
+    """Parity guard, on EVERY rank: a fixed 1e6-point sub-chunk of the workload
+    (seed 1001 + rank) against the CPU oracle before any number is recorded."""
+    nd = case["nd"]
+    q = host_queries(case, 1_000_000, 1001 + env.rank)
+    kind, run = cpu_run(case, workload, None)
+    if workload in WINDOWED:
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import orc
+        o = orc.Oracle(kind)
+        oaxes = [o.axis(case["lon"], period=360.0), o.axis(case["lat"])]
+        if nd >= 3:
+            oaxes.append(o.axis(case["time"].astype("datetime64[ns]").astype(np.int64)))
+        if workload == "bicubic":
+            want, _ = o.windowed2d(oaxes, case["grid"], q[0], q[1], num_threads=0, stateless=True)
         else:
-            want, _ = run(q)
-            fn = {2: pyi.bivariate, 3: pyi.trivariate, 4: pyi.quadrivariate}[nd]
-            qq = list(q)
-            if nd >= 3:
-                qq[2] = qq[2].view("datetime64[ns]")
-            got = fn(grid, *qq)
-        tol = 1e-12 if got.dtype == np.float64 else 1e-5
-        nan_ok = np.array_equal(np.isnan(got), np.isnan(want))
-        m = ~np.isnan(want)
-        err = np.abs(got[m].astype(np.float64) - want[m].astype(np.float64))
-        if not nan_ok or np.any(err > tol * np.maximum(np.abs(want[m]), 1.0)):
-            raise SystemExit("bench.py: parity check against the CPU oracle FAILED; no number recorded")
-
-    # device-resident query points (synthetic, generated on the device)
-    gen = torch.Generator(device=dev)
-    gen.manual_seed(1005 + rank)
-    x = torch.rand(n, dtype=torch.float64, device=dev, generator=gen).mul_(720.0).sub_(180.0)
-    y = torch.rand(n, dtype=torch.float64, device=dev, generator=gen).mul_(180.0).sub_(90.0)
-    coords = [x, y]
+            want, _ = o.windowed_nd(oaxes, case["grid"], *q, method=WINDOWED[workload], num_threads=0,
+                                    stateless=True)
+    else:
+        want, _ = run(q)
+    qq = list(q)
     if nd >= 3:
+        qq[2] = qq[2].view("datetime64[ns]")
+    api = {2: pyi.bivariate, 3: pyi.trivariate, 4: pyi.quadrivariate}[nd]
+    got = api(grid, *qq, WINDOWED.get(workload, "bilinear"))
+    tol = 1e-12 if got.dtype == np.float64 else 1e-5
+    nan_ok = np.array_equal(np.isnan(got), np.isnan(want))
+    m = ~np.isnan(want)
+    err = np.abs(got[m].astype(np.float64) - want[m].astype(np.float64))
+    ok = bool(nan_ok and not np.any(err > tol * np.maximum(np.abs(want[m]), 1.0)))
+    if env.min_over_ranks(1.0 if ok else 0.0) < 1.0:
+        raise SystemExit(f"bench.py: parity check of '{workload}' against the CPU oracle FAILED on a rank; "
+                         "no number recorded")
+    return {"checked": "ok", "points": 1_000_000, "ranks": env.world, "oracle": kind,
+            "bit_identical_fraction": float((err == 0).mean()) if err.size else 1.0,
+            "max_abs_err": float(err.max()) if err.size else 0.0}
+
+
+def device_queries(env, case, n):
+    """Device-resident query points (synthetic, generated on the device)."""
+    torch = env.torch
+    gen = torch.Generator(device=env.dev)
+    gen.manual_seed(1005 + env.rank)
+    x = torch.rand(n, dtype=torch.float64, device=env.dev, generator=gen).mul_(720.0).sub_(180.0)
+    y = torch.rand(n, dtype=torch.float64, device=env.dev, generator=gen).mul_(180.0).sub_(90.0)
+    coords = [x, y]
+    if case["nd"] >= 3:
         tv = case["time"].astype("datetime64[ns]").astype(np.int64)
         day = 86_400_000_000_000
         lo, hi = int(tv.min()) - day, int(tv.max()) + day
-        z = torch.rand(n, dtype=torch.float64, device=dev, generator=gen).mul_(float(hi - lo)).to(torch.int64).add_(lo)
+        z = torch.rand(n, dtype=torch.float64, device=env.dev, generator=gen).mul_(float(hi - lo)).to(torch.int64).add_(lo)
         coords.append(z)
-    if nd >= 4:
-        coords.append(torch.rand(n, dtype=torch.float64, device=dev, generator=gen).mul_(5610.0).sub_(10.0))
-    fn = {2: pyi.core.bivariate, 3: pyi.core.trivariate, 4: pyi.core.quadrivariate}[nd]
-    if args.workload in WINDOWED:
-        cfg = getattr({2: pyi.windowed.Bivariate, 3: pyi.windowed.Trivariate}[nd], WINDOWED[args.workload])()
-    else:
-        cfg = {2: pyi.geometric.Bivariate, 3: pyi.geometric.Trivariate, 4: pyi.geometric.Quadrivariate}[nd].bilinear()
+    if case["nd"] >= 4:
+        coords.append(torch.rand(n, dtype=torch.float64, device=env.dev, generator=gen).mul_(5610.0).sub_(10.0))
+    return coords
 
-    def step():
-        return fn(grid, *coords, cfg)
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
+def make_config(pyi, case, workload):
+    nd = case["nd"]
+    if workload in WINDOWED:
+        return getattr({2: pyi.windowed.Bivariate, 3: pyi.windowed.Trivariate}[nd], WINDOWED[workload])()
+    return {2: pyi.geometric.Bivariate, 3: pyi.geometric.Trivariate, 4: pyi.geometric.Quadrivariate}[nd].bilinear()
 
-    for _ in range(max(3, args.warmup)):
-        out = step()
+
+def time_device(env, pyi, grid, coords, cfg, steps, warmup, sampler=None):
+    """`steps` timed passes over device-resident points: CUDA events on the
+    launching stream around every pass and around the whole region, barrier +
+    synchronize on both sides, max over ranks."""
+    torch = env.torch
+    fn = {2: pyi.core.bivariate, 3: pyi.core.trivariate, 4: pyi.core.quadrivariate}[grid.ndim]
+    out = None
+    for _ in range(max(3, warmup)):
+        out = fn(grid, *coords, cfg)
     del out
-    barrier()
+    env.barrier()
     launches0 = pyi.launch_count()
-    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    with ClockSampler(local) as clk:
-        t_all0 = torch.cuda.Event(enable_timing=True)
-        t_all1 = torch.cuda.Event(enable_timing=True)
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    t_all0, t_all1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+
+    def region():
         t_all0.record()
+        o = None
         for a, b in evs:
             a.record()
-            out = step()
+            o = fn(grid, *coords, cfg)
             b.record()
         t_all1.record()
-        barrier()
+        env.barrier()
+        return o
+
+    if sampler is not None:
+        with sampler:
+            out = region()
+    else:
+        out = region()
     launches = pyi.launch_count() - launches0
-    total_ms = t_all0.elapsed_time(t_all1)
+    total_ms = env.max_over_ranks(t_all0.elapsed_time(t_all1))
     kernel_ms = sorted(a.elapsed_time(b) for a, b in evs)
-    t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    total_ms = float(t.item())
-    ms_per_step = total_ms / args.steps
-    value = world * n * args.steps / (total_ms / 1e3) / 1e6
     finite = float(torch.isfinite(out).double().mean().item())
     del out
+    return total_ms, kernel_ms, int(launches), finite
 
-    # end to end: pinned host buffers -> public API (H2D + kernel + D2H per step)
+
+def roofline_entry(workload, n, kernel_ms):
+    peak, peak_src = peaks()
+    bpp = BYTES_PER_POINT[workload]
+    k_ms = sum(kernel_ms) / len(kernel_ms)
+    achieved = n * bpp / (k_ms / 1e3) / 1e9
+    tr = ncu_traffic(workload, n)
+    return {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+            "traffic": (tr or {}).get("bytes_per_launch"), "traffic_detail": tr, "peak_source": peak_src,
+            "bytes_per_point": bpp, "kernel_ms": k_ms, "secondary": (tr or {}).get("secondary")}
+
+
+def run_secondary(env, pyi, workload, n, steps, sweep=()):
+    """One short sub-run (3 warm-up + `steps` timed passes) of another BASELINE
+    configuration, parity-checked on every rank first."""
+    torch = env.torch
+    case = build_host_case(workload)
+    grid, bcast_ms = make_grid(env, pyi, case)
+    parity = oracle_guard(env, pyi, case, grid, workload)
+    coords = device_queries(env, case, n)
+    cfg = make_config(pyi, case, workload)
+    total_ms, kernel_ms, launches, finite = time_device(env, pyi, grid, coords, cfg, steps, 3)
+    entry = {"workload": workload_name(workload, n), "value": env.world * n * steps / (total_ms / 1e3) / 1e6,
+             "unit": METRIC, "ms_per_step": total_ms / steps, "steps": steps, "warmup": 3,
+             "gpu_launches": launches, "dtype": case["dtype"], "finite_fraction": finite,
+             "grid_broadcast_ms": bcast_ms, "roofline": roofline_entry(workload, n, kernel_ms), "parity": parity}
+    if sweep:
+        # point-count sweep (BASELINE configs[4]): same grid, the first m points
+        pts = []
+        for m in sweep:
+            if m > n:
+                continue
+            sub = [c[:m] for c in coords]
+            t_ms, k_ms, _, _ = time_device(env, pyi, grid, sub, cfg, steps, 3)
+            pts.append({"points_per_gpu": int(m), "value": env.world * m * steps / (t_ms / 1e3) / 1e6,
+                        "ms_per_step": t_ms / steps, "kernel_ms_min": k_ms[0]})
+        entry["sweep"] = pts
+    del coords, grid
+    torch.cuda.empty_cache()
+    return entry
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        return run_reference_arm(args)
+    import pyinterp_b200 as pyi
+    env = Env()
+    torch = env.torch
+    world, rank = env.world, env.rank
+    n = int(args.points or default_points(args.workload))
+    case = build_host_case(args.workload)
+    nd = case["nd"]
+    grid, bcast_ms = make_grid(env, pyi, case)
+    parity = None if args.no_cpu else oracle_guard(env, pyi, case, grid, args.workload)
+    coords = device_queries(env, case, n)
+    cfg = make_config(pyi, case, args.workload)
+    clk = ClockSampler(env.local)
+    total_ms, kernel_ms, launches, finite = time_device(env, pyi, grid, coords, cfg, args.steps, args.warmup, clk)
+    ms_per_step = total_ms / args.steps
+    value = world * n * args.steps / (total_ms / 1e3) / 1e6
+
+    # end to end: HOST buffers -> public API (H2D + kernel + D2H per step)
     ne = int(min(args.e2e_points, n))
     hq = []
     for c in coords:
@@ -412,50 +513,70 @@ def main():
     api = {2: pyi.bivariate, 3: pyi.trivariate, 4: pyi.quadrivariate}[nd]
     method = WINDOWED.get(args.workload, "bilinear")
     grid._resident = True
-    for _ in range(2):
-        r = api(grid, *hq, method)
-    barrier()
-    t0 = time.perf_counter()
-    e2e_steps = max(2, min(args.steps, 5))
-    for _ in range(e2e_steps):
-        r = api(grid, *hq, method)
-    torch.cuda.synchronize()
-    e2e_s = time.perf_counter() - t0
-    t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_value = world * ne * e2e_steps / float(t.item()) / 1e6
+
+    def time_e2e(host_arrays, steps):
+        r = None
+        for _ in range(2):
+            r = api(grid, *host_arrays, method)
+        env.barrier()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            r = api(grid, *host_arrays, method)
+        torch.cuda.synchronize()
+        dt = env.max_over_ranks(time.perf_counter() - t0)
+        return world * ne * steps / dt / 1e6, r
+
+    e2e_steps = max(3, min(args.steps, 10))
+    e2e_value, r = time_e2e(hq, e2e_steps)
     h2d = sum(int(h.nbytes) for h in hq)
     d2h = int(r.nbytes)
+    # the same call with plain (pageable) numpy inputs, as an unmodified caller passes them
+    pageable = [np.array(h, copy=True) for h in hq]
+    e2e_pageable, _ = time_e2e(pageable, e2e_steps)
+    del pageable, hq, r, coords
+    torch.cuda.empty_cache()
+
+    secondary = {}
+    if args.workload == "bilinear" and not args.no_secondary:
+        del grid
+        torch.cuda.empty_cache()
+        sub = [("bicubic", 100_000_000, ()), ("trivariate", 100_000_000, ()), ("quadrivariate", 100_000_000, ()),
+               ("bilinear_irrlat", 1_000_000_000, (1_000_000, 10_000_000, 100_000_000, 1_000_000_000))]
+        for name, m, sweep in sub:
+            m = int(min(m, args.points)) if args.points else m
+            try:
+                secondary[name] = run_secondary(env, pyi, name, m, 5, sweep)
+            except SystemExit:
+                raise
+            except Exception as e:  # a failed sub-run must not hide the headline
+                secondary[name] = {"error": f"{type(e).__name__}: {e}"}
+                torch.cuda.empty_cache()
 
     if rank == 0:
-        peak, peak_src = peaks()
-        bpp = BYTES_PER_POINT[args.workload]
-        k_ms = sum(kernel_ms) / len(kernel_ms)
-        achieved = n * bpp / (k_ms / 1e3) / 1e9
-        tr = ncu_traffic(args.workload, n)
         line = {
             "metric": METRIC, "value": value, "unit": METRIC, "n_gpus": world, "steps": args.steps,
             "warmup": max(3, args.warmup), "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": case["dtype"], "data": "synthetic",
             "config": {"workload": workload_name(args.workload, n), "points_per_gpu": n,
                        "l2": "inputs (x, y, out streams) are far larger than L2; no flush needed",
-                       "grid_broadcast_ms": bcast_ms, "finite_fraction": finite,
-                       "e2e_points_per_step": ne, "kernel_ms_min": kernel_ms[0], "kernel_ms_median": kernel_ms[len(kernel_ms) // 2]},
-            "e2e": {"value": e2e_value, "unit": METRIC, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+                       "grid_broadcast_ms": bcast_ms, "finite_fraction": finite, "parity": parity,
+                       "e2e_points_per_step": ne, "kernel_ms_min": kernel_ms[0],
+                       "kernel_ms_median": kernel_ms[len(kernel_ms) // 2]},
+            "e2e": {"value": e2e_value, "unit": METRIC, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "steps": e2e_steps, "input": "page-locked host arrays",
+                    "pageable": {"value": e2e_pageable, "unit": METRIC,
+                                 "input": "plain numpy arrays, staged through the library's pinned slots"}},
             "gpu_launches": int(launches),
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": (tr or {}).get("bytes_per_launch"), "traffic_detail": tr,
-                         "peak_source": peak_src,
-                         "bytes_per_point": bpp, "kernel_ms": k_ms,
-                         "secondary": (tr or {}).get("secondary")},
+            "roofline": roofline_entry(args.workload, n, kernel_ms),
             "clocks": clk.summary(),
         }
+        if secondary:
+            line["secondary"] = secondary
         if world == 1 and not args.no_cpu:
             line["cpu_baseline"] = cpu_baseline(case, args.workload, args.cpu_seconds)
         print(json.dumps(line), flush=True)
     if world > 1:
-        dist.destroy_process_group()
+        env.dist.destroy_process_group()
 
 
 if __name__ == "__main__":

@@ -34,7 +34,7 @@
 extern "C" {
 #endif
 
-#define PYI_ABI_VERSION 1
+#define PYI_ABI_VERSION 2
 
 /* ---- status codes -------------------------------------------------------- */
 typedef enum pyi_status {
@@ -104,6 +104,21 @@ typedef enum pyi_first_guess {
   PYI_FIRST_GUESS_ZONAL_AVERAGE = 0,
   PYI_FIRST_GUESS_ZERO = 1
 } pyi_first_guess;
+/* How interpolated VALUES are computed (index selection is bit-exact with the
+ * reference in every mode).  PYI_VALUES_EXACT: every rounding of the
+ * reference's evaluator is reproduced, values are bit-identical.
+ * PYI_VALUES_TOLERANCE: reciprocal-multiply and fused multiply-adds in the
+ * weights (bilinear), precomputed spline-derivative weights (bicubic 6 x 6):
+ * values within 1e-12 (float64) / 1e-5 (float32) relative of the reference,
+ * NaN positions identical.  PYI_VALUES_DEFAULT: tolerance where a tolerance
+ * kernel exists and the axes are well conditioned for it, else exact; the
+ * environment variables PYINTERP_B200_BILINEAR / PYINTERP_B200_BICUBIC
+ * (= "exact" | "tolerance") change what DEFAULT means for the process. */
+typedef enum pyi_value_mode {
+  PYI_VALUES_DEFAULT = 0,
+  PYI_VALUES_EXACT = 1,
+  PYI_VALUES_TOLERANCE = 2
+} pyi_value_mode;
 /* where caller buffers live */
 typedef enum pyi_mem { PYI_MEM_HOST = 0, PYI_MEM_DEVICE = 1 } pyi_mem;
 
@@ -153,6 +168,7 @@ typedef struct pyi_geometric_config {
   int32_t u_method;     /* pyi_axis_method (4-D) */
   int32_t bounds_error; /* 0: NaN, 1: report first out-of-bounds point */
   int32_t num_threads;  /* accepted for API parity, ignored on the GPU */
+  int32_t value_mode;   /* pyi_value_mode */
 } pyi_geometric_config;
 
 /* config/windowed.hpp: method, half window sizes (default 3/3, :244-247),
@@ -164,6 +180,7 @@ typedef struct pyi_windowed_config {
   int32_t boundary;     /* pyi_boundary */
   int32_t bounds_error;
   int32_t num_threads;
+  int32_t value_mode;   /* pyi_value_mode */
 } pyi_windowed_config;
 
 /* config/windowed.hpp Univariate / Bivariate / Trivariate / Quadrivariate in
@@ -180,6 +197,7 @@ typedef struct pyi_windowed_nd_config {
   int32_t z_method;     /* pyi_axis_method (3-D / 4-D) */
   int32_t u_method;     /* pyi_axis_method (4-D) */
   int32_t derivative;   /* 1-D only: 0 value, 1 first derivative */
+  int32_t value_mode;   /* pyi_value_mode */
 } pyi_windowed_nd_config;
 
 typedef struct pyi_axis pyi_axis; /* opaque */
@@ -191,6 +209,21 @@ int pyi_abi_version(void);
 int pyi_device_count(void);
 /* Bind the calling thread to `device`. PYI_NO_DEVICE when there is none. */
 int pyi_set_device(int device);
+/* Single-call multi-GPU sharding.  The reference's caller is ONE process whose
+ * parallel_for (cxx/include/pyinterp/parallel_for.hpp:30-78) splits the points
+ * of a call into contiguous chunks, one per worker.  After pyi_dist_init(n)
+ * every HOST-memory call of pyi_geometric / pyi_windowed2d / pyi_windowed
+ * splits its points the same way (n / G each, the first n % G shards one more)
+ * over the first G = min(n, device count) CUDA devices (n <= 0: all of them):
+ * the grid handle is replicated on each device on first use (peer copies over
+ * NVLink, refreshed after pyi_grid_update), every shard runs its own copy /
+ * kernel pipeline from its own host thread, results land in the caller's
+ * output array, and the bounds-error report is the minimum over the shards,
+ * i.e. the same point as on one device.  Small calls (fewer than 2^21 points
+ * per device) use fewer devices.  Returns the device count in effect (0
+ * without a CUDA device).  pyi_dist_size() reads it back. */
+int pyi_dist_init(int n_devices);
+int pyi_dist_size(void);
 /* Thread-local text of the last failure. */
 const char *pyi_last_error(void);
 

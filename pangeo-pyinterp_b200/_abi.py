@@ -29,6 +29,8 @@ RESOLUTIONS = {"Y": 0, "M": 1, "W": 2, "D": 3, "h": 4, "m": 5, "s": 6, "ms": 7, 
 FIRST_GUESS = {"zonal_average": 0, "zero": 1}
 PYI_BOUNDARY_UNDEF, PYI_BOUNDARY_SHRINK = 0, 1
 PYI_MEM_HOST, PYI_MEM_DEVICE = 0, 1
+PYI_VALUES_DEFAULT, PYI_VALUES_EXACT, PYI_VALUES_TOLERANCE = 0, 1, 2
+VALUE_MODES = {"default": 0, "exact": 1, "tolerance": 2}
 PYI_GRID_DEFAULT, PYI_GRID_PACK_CELLS, PYI_GRID_BORROW_DEVICE = 0, 1, 2
 
 #: numpy dtype name -> pyi_dtype (pybind/grid.hpp:604-606,819-879 of the reference)
@@ -73,6 +75,7 @@ class GeometricConfig(C.Structure):
         ("u_method", C.c_int32),
         ("bounds_error", C.c_int32),
         ("num_threads", C.c_int32),
+        ("value_mode", C.c_int32),
     ]
 
 
@@ -84,6 +87,7 @@ class WindowedConfig(C.Structure):
         ("boundary", C.c_int32),
         ("bounds_error", C.c_int32),
         ("num_threads", C.c_int32),
+        ("value_mode", C.c_int32),
     ]
 
 
@@ -98,6 +102,7 @@ class WindowedNdConfig(C.Structure):
         ("z_method", C.c_int32),
         ("u_method", C.c_int32),
         ("derivative", C.c_int32),
+        ("value_mode", C.c_int32),
     ]
 
 
@@ -122,6 +127,8 @@ SIGNATURES = {
     "pyi_device_count": (C.c_int, []),
     "pyi_set_device": (C.c_int, [C.c_int]),
     "pyi_last_error": (C.c_char_p, []),
+    "pyi_dist_init": (C.c_int, [C.c_int]),
+    "pyi_dist_size": (C.c_int, []),
     "pyi_axis_create_f64": (_P, [_P, C.c_int64, C.c_double, C.c_int, C.c_double, _IP]),
     "pyi_axis_create_i64": (_P, [_P, C.c_int64, C.c_int64, C.c_int, C.c_int64, _IP]),
     "pyi_axis_create_from_desc": (_P, [C.POINTER(AxisDesc), _IP]),
@@ -149,6 +156,7 @@ SIGNATURES = {
     "pyi_launch_count": (C.c_int64, []),
 }
 
+ABI_VERSION = 2
 LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc", "libpyinterp_b200.so")
 _lib = None
 
@@ -172,7 +180,7 @@ def load():
                 "(nvcc, sm_100a).  pyinterp_b200 has no CPU fallback."
             )
         _lib = bind(C.CDLL(LIB_PATH, mode=C.RTLD_GLOBAL))
-        if _lib.pyi_abi_version() != 1:
+        if _lib.pyi_abi_version() != ABI_VERSION:
             raise ImportError("libpyinterp_b200.so: ABI version mismatch")
     return _lib
 

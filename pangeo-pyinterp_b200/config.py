@@ -17,6 +17,7 @@ from . import _abi
 class _Common:
     _bounds_error = False
     _num_threads = 0
+    _value_mode = _abi.PYI_VALUES_DEFAULT
 
     def _clone(self):
         return copy.copy(self)
@@ -33,6 +34,20 @@ class _Common:
         c = self._clone()
         c._num_threads = int(value)
         return c
+
+    def with_value_mode(self, mode: str):
+        """Not in the reference: how VALUES are computed (``pyi_value_mode`` of
+        include/pyinterp_b200.h).  ``"exact"``: bit-identical to the reference;
+        ``"tolerance"``: FMA / reciprocal weights, within 1e-12 / 1e-5;
+        ``"default"``: tolerance where the axes are well conditioned for it.
+        Index selection is bit-exact in every mode."""
+        c = self._clone()
+        c._value_mode = _abi.VALUE_MODES[mode]
+        return c
+
+    @property
+    def value_mode(self) -> str:
+        return {v: k for k, v in _abi.VALUE_MODES.items()}[self._value_mode]
 
     @property
     def bounds_error(self) -> bool:
@@ -86,7 +101,7 @@ class _Geometric(_Common):
 
     def _pod(self) -> _abi.GeometricConfig:
         return _abi.GeometricConfig(self._method, self._exp, self._z_method, self._u_method,
-                                    int(self._bounds_error), self._num_threads)
+                                    int(self._bounds_error), self._num_threads, self._value_mode)
 
 
 class _GBivariate(_Geometric):
@@ -179,12 +194,12 @@ class _Windowed(_Common):
     def _pod(self) -> _abi.WindowedConfig:
         """POD of pyi_windowed2d (bicubic / bilinear on 2-D grids)."""
         return _abi.WindowedConfig(self._method, self._half_x, self._half_y, self._boundary,
-                                   int(self._bounds_error), self._num_threads)
+                                   int(self._bounds_error), self._num_threads, self._value_mode)
 
     def _pod_nd(self) -> _abi.WindowedNdConfig:
         return _abi.WindowedNdConfig(self._method, self._half_x, self._half_y, self._boundary,
                                      int(self._bounds_error), self._num_threads, self._z_method,
-                                     self._u_method, self._derivative)
+                                     self._u_method, self._derivative, self._value_mode)
 
 
 def _model_factory(name):

@@ -42,6 +42,15 @@ struct DAxis {
                         // ascending regular i64 axis with |start|, span < 2^61 (then
                         // inv_step = 1.0 / step and ispan = (n - 1) * step)
   long long ispan;
+  // tolerance-mode bilinear kernel (pyi_fast2d_tol.cuh): regular ascending f64
+  // axis whose brackets can be verified from t = (c - node(k)) / dx alone.
+  // 0: not eligible; 1: general (node(k), node(k+1) with the reference's two
+  // roundings); 2: exact nodes (fma(k, step, start) is the reference's node for
+  // every k and every spacing, the seam included, is exactly `step`).
+  int32_t tol_ok;
+  int32_t tol_xhi;         // periodic axes: exponent field (high word) bound of |x|, 2^28 steps
+  double tol_off;          // -(start * inv_step) - 0.5: rint(c * inv_step + tol_off) = floor guess
+  double tol_poff;         // -(min * inv_period) - 0.5, periodic axes
 };
 
 // ---------------------------------------------------------------------------

@@ -1,0 +1,326 @@
+// pyi_fast2d_tol.cuh -- K1t: bivariate bilinear on a float64-result 2-D grid in
+// TOLERANCE value mode (pyi_value_mode of include/pyinterp_b200.h).  Included by
+// pyi_kernels.cu after pyi_fast2d.cuh, whose pieces it reuses (cell-packed
+// gather, irregular bracket, generic redo).
+//
+// Same function as bivariate_single (pybind/geometric/bivariate.hpp:47-97) with
+// Bilinear::evaluate (math/interpolate/geometric/bivariate.hpp:110-132).  Index
+// selection stays bit-exact; the VALUE arithmetic is allowed to differ from the
+// reference by rounding (north star: 1e-12 relative on float64):
+//
+//   * bracket: k = rint(c * inv_step + off) with off = -(start * inv_step) - 0.5
+//     is a floor guess made with two additions of 1.5 * 2^52 (no 64-bit
+//     conversions, which issue at a quarter of the FP64 rate).  The cell is then
+//     VERIFIED from the nodes themselves: c0 = node(k) and c1 = node(k + 1) are
+//     the reference's coordinate_value (start + k * step, two roundings,
+//     container.hpp:480-483), and t = (c - c0) / (c1 - c0) lies strictly inside
+//     (2^-21, 1 - 2^-21) only if c0 < c < c1, which is the reference's bracket
+//     (math/axis.hpp:745-766, ascending axis).  Everything else -- a point on a
+//     node, a wrong guess, NaN, a coordinate outside the axis -- leaves the hot
+//     path: beyond the ends of a non-periodic axis the result is NaN, the rest is
+//     re-done by the generic code (slow_point, pyi_fast2d.cuh).
+//   * "exact nodes" axes (DAxis::tol_ok == 2, e.g. every multiple-of-2^-k grid
+//     such as the 0.25 degree one): the host has checked that fma(k, step, start)
+//     IS the reference's node for every k and that every spacing, the periodic
+//     seam included, is exactly `step`; then c0 is one fma and t = (c - c0) *
+//     inv_step, bit-identical to the reference's quotient when step is a power
+//     of two.
+//   * general regular axes: dx = c1 - c0 differs from `step` by the rounding of
+//     the nodes (relative e = 1 - dx * inv_step, |e| < 2^-26 by the host's
+//     gate), t = t0 + t0 * e with t0 = (c - c0) * inv_step: first-order exact,
+//     e^2 < 2^-52.
+//   * periodic x: the cell guess uses c = x - floor((x - min) / period) * period
+//     in one fma; the weight's numerator repeats the reference's own roundings
+//     (query normalised against the cell's x0, bivariate.hpp:83-88) so that t
+//     matches the reference to an ulp on any grid spacing.
+//   * evaluation: the reference's (1-t)((1-u) q00 + u q01) + t((1-u) q10 + u q11)
+//     with the inner sums contracted into fmas (same structure, so infinities and
+//     NaNs in the grid propagate as in the reference).
+//
+// Per point: ~27 FP64 instructions instead of ~72 (two correctly rounded
+// divisions, unfused products), four points per thread with 32-byte streaming
+// loads / stores.
+#pragma once
+
+namespace pyi {
+
+constexpr double kMagic = 6755399441055744.0;  // 1.5 * 2^52
+
+// rint(v) for |v| < 2^51 as a double, and its low 32 bits as an int
+__device__ __forceinline__ double rint_magic(double v, int& lo) {
+  const double m = __dadd_rn(v, kMagic);
+  lo = __double2loint(m);
+  return __dsub_rn(m, kMagic);
+}
+
+// |v| < 2^31 and finite, from the exponent field (integer pipe)
+__device__ __forceinline__ bool below_2p31(double v) {
+  return (static_cast<unsigned>(__double2hiint(v)) & 0x7ff00000u) < 0x41e00000u;
+}
+
+// One regular ascending axis.  MODE 1: general, 2: exact nodes.  WRAP: the
+// coordinate was normalised (x = c + jf * period; cell n-1 -> 0 exists when
+// a.periodic).  Returns the cell index and the weight t; `safe` is cleared
+// unless the bracket is verified.
+//
+// The numerator of t follows the reference's roundings: for y it is fl(y - y0);
+// for a periodic x the reference normalises the query against the cell's own
+// x0 (bivariate.hpp:83-88): px = fl(remainder(fl(x - x0), period) + x0), then
+// fl(px - x0).  remainder()'s quotient is jf for a point inside the cell, and
+// fma(-jf, period, d) is exact, so the same four roundings are made here.
+template <int MODE, bool WRAP>
+__device__ __forceinline__ void tol_regular(const DAxis& a, double c, double x, double jf, int& k,
+                                            double& t, bool& safe) {
+  const double q5 = fma(c, a.inv_step, a.tol_off);
+  const double kf = rint_magic(q5, k);
+  double c0, scale = a.inv_step;
+  if (MODE == 2) {
+    c0 = fma(kf, a.step, a.start);
+  } else {
+    c0 = __dadd_rn(a.start, __dmul_rn(kf, a.step));
+    double c1 = __dadd_rn(a.start, __dmul_rn(__dadd_rn(kf, 1.0), a.step));
+    if (WRAP) c1 = (k == a.n - 1) ? a.seam_c1 : c1;
+    // 1 / dx to first order in e = 1 - dx * inv_step (|e| < 2^-26, host gate)
+    const double e = fma(-__dsub_rn(c1, c0), a.inv_step, 1.0);
+    scale = fma(a.inv_step, e, a.inv_step);
+  }
+  double num;
+  if (WRAP) {
+    const double r = fma(-jf, a.period, __dsub_rn(x, c0));
+    num = __dsub_rn(__dadd_rn(r, c0), c0);
+  } else {
+    num = __dsub_rn(c, c0);
+  }
+  t = __dmul_rn(num, scale);
+  // t strictly inside (2^-21, 1 - 2^-21), tested on the high word (integer pipe;
+  // NaN and negative values fail).  The margin covers the roundings above and
+  // the distance between this kernel's normalised coordinate and the
+  // reference's (a few ulp of the coordinate, below 2^-24 of a step by the
+  // host's gate): the reference's bracket is (k, k + 1).
+  const int th = __double2hiint(t);
+  const unsigned cells = static_cast<unsigned>((WRAP && a.periodic) ? a.n : a.n - 1);
+  safe = safe && below_2p31(q5) && th > 0x3ea00000 && th < 0x3fefffff && static_cast<unsigned>(k) < cells;
+}
+
+// Irregular ascending y: the exact bracket of pyi_fast2d.cuh, weight through the
+// staged reciprocal spacings.
+__device__ __forceinline__ void tol_irregular(const DAxis& a, const double* __restrict__ sp,
+                                              const double* __restrict__ sinv,
+                                              const int* __restrict__ slut, double c, int& k,
+                                              double& t, bool& safe) {
+  bool ok = sane(c);
+  const RegBracket b = bracket_irregular(a, sp, slut, ok ? c : a.min, ok);
+  k = b.k;
+  t = __dmul_rn(b.dl, sinv[k]);
+  safe = safe && ok;
+}
+
+template <int PTS>
+struct VecIO;
+template <>
+struct VecIO<2> {
+  static __device__ __forceinline__ void load(const double* p, double (&v)[2]) {
+    const double2 t = __ldcs(reinterpret_cast<const double2*>(p));
+    v[0] = t.x;
+    v[1] = t.y;
+  }
+  static __device__ __forceinline__ void store(double* p, const double (&v)[2]) {
+    __stcs(reinterpret_cast<double2*>(p), make_double2(v[0], v[1]));
+  }
+};
+template <>
+struct VecIO<4> {
+  static __device__ __forceinline__ void load(const double* p, double (&v)[4]) {
+    asm volatile("ld.global.cs.v4.f64 {%0,%1,%2,%3}, [%4];"
+                 : "=d"(v[0]), "=d"(v[1]), "=d"(v[2]), "=d"(v[3])
+                 : "l"(p));
+  }
+  static __device__ __forceinline__ void store(double* p, const double (&v)[4]) {
+    asm volatile("st.global.cs.v4.f64 [%0], {%1,%2,%3,%4};" ::"l"(p), "d"(v[0]), "d"(v[1]),
+                 "d"(v[2]), "d"(v[3])
+                 : "memory");
+  }
+};
+
+// XM: 1 general / 2 exact nodes (x is always regular); YM: 0 irregular,
+// 1 general regular, 2 exact-nodes regular.  PTS consecutive points per thread.
+template <bool PER, int XM, int YM, int PTS, int MINB>
+__global__ void __launch_bounds__(kFastThreads, MINB)
+bilinear2d_tol_kernel(const __grid_constant__ GeoParams p) {
+  __shared__ double s_points[YM == 0 ? kFastMaxIrregular : 1];
+  __shared__ double s_inv[YM == 0 ? kFastMaxIrregular : 1];
+  __shared__ int s_lut[YM == 0 ? kFastMaxLut : 1];
+  if (YM == 0) {
+    const double* gp = static_cast<const double*>(p.ax[1].points);
+    const int ny = p.ax[1].n;
+    for (int i = threadIdx.x; i < ny; i += blockDim.x) {
+      const double a = __ldg(gp + i);
+      s_points[i] = a;
+      // reciprocal spacing of cell i (the last entry is never addressed)
+      s_inv[i] = i + 1 < ny ? __ddiv_rn(1.0, __dsub_rn(__ldg(gp + i + 1), a)) : 0.0;
+    }
+    for (int i = threadIdx.x; i <= p.ax[1].lut_bins; i += blockDim.x) s_lut[i] = __ldg(p.ax[1].lut + i);
+    __syncthreads();
+  }
+  const DAxis& ax = p.ax[0];
+  const DAxis& ay = p.ax[1];
+  const unsigned groups = static_cast<unsigned>(p.n / PTS);  // the launcher keeps n below 2^32
+  const unsigned stride = gridDim.x * blockDim.x;
+  double* __restrict__ out = static_cast<double*>(p.out);
+  for (unsigned g = blockIdx.x * blockDim.x + threadIdx.x; g < groups; g += stride) {
+    const size_t base = static_cast<size_t>(g) * PTS;
+    double x[PTS], y[PTS], t[PTS], u[PTS], o[PTS];
+    long long cell[PTS];
+    bool safe[PTS];
+    VecIO<PTS>::load(p.x + base, x);
+    VecIO<PTS>::load(p.y + base, y);
+    bool all_safe = true;
+#pragma unroll
+    for (int i = 0; i < PTS; ++i) {
+      double c = x[i], jf = 0.0;
+      bool s = true;
+      if (PER) {
+        // c = x - floor((x - min) / period) * period, one rounding: only the
+        // cell guess depends on it
+        int unused;
+        jf = rint_magic(fma(x[i], ax.inv_period, ax.tol_poff), unused);
+        c = fma(-jf, ax.period, x[i]);
+        // |x| below 2^28 steps (and 2^40): c is then within 2^-24 of a step of
+        // the reference's normalised coordinate; farther points are re-done
+        s = static_cast<int>(static_cast<unsigned>(__double2hiint(x[i])) & 0x7ff00000u) < ax.tol_xhi;
+      }
+      int kx, ky;
+      tol_regular<XM, PER>(ax, c, x[i], jf, kx, t[i], s);
+      if (YM == 0) {
+        tol_irregular(ay, s_points, s_inv, s_lut, y[i], ky, u[i], s);
+      } else {
+        tol_regular<YM, false>(ay, y[i], y[i], 0.0, ky, u[i], s);
+      }
+      safe[i] = s;
+      all_safe = all_safe && s;
+      cell[i] = s ? static_cast<long long>(kx) * ay.n + ky : 0LL;  // cell 0 is always a legal address
+    }
+    Cell<double> q[PTS];
+#pragma unroll
+    for (int i = 0; i < PTS; ++i) q[i].load(p.packed, cell[i]);
+#pragma unroll
+    for (int i = 0; i < PTS; ++i) {
+      const double omt = __dsub_rn(1.0, t[i]);
+      const double omu = __dsub_rn(1.0, u[i]);
+      const double a = fma(u[i], q[i].v01, __dmul_rn(omu, q[i].v00));
+      const double b = fma(u[i], q[i].v11, __dmul_rn(omu, q[i].v10));
+      o[i] = fma(t[i], b, __dmul_rn(omt, a));
+    }
+    if (!all_safe) {  // rare: on a node, outside an axis, NaN
+#pragma unroll
+      for (int i = 0; i < PTS; ++i) {
+        if (safe[i]) continue;
+        // a finite coordinate beyond the ends of an axis that does not wrap is
+        // NaN (see beyond_ends); with bounds_error the generic code reports it
+        bool far = false;
+        if (!p.bounds_error && sane(x[i]) && sane(y[i])) {
+          far = beyond_ends(ay, y[i]) || (!PER && beyond_ends(ax, x[i]));
+        }
+        o[i] = far ? RT<double>::nan() : slow_point<double>(p, x[i], y[i], static_cast<long long>(base) + i);
+      }
+    }
+    VecIO<PTS>::store(out + base, o);
+  }
+  // tail: n % PTS points
+  if (blockIdx.x == 0 && threadIdx.x < static_cast<unsigned>(p.n % PTS)) {
+    const long long k = static_cast<long long>(groups) * PTS + threadIdx.x;
+    out[k] = slow_point<double>(p, __ldg(p.x + k), __ldg(p.y + k), k);
+  }
+}
+
+// PYINTERP_B200_BILINEAR = exact | tolerance: what PYI_VALUES_DEFAULT means
+// (read per launch: the tests switch it)
+static int bilinear_default_mode() {
+  const char* e = std::getenv("PYINTERP_B200_BILINEAR");
+  return (e != nullptr && e[0] == 'e') ? PYI_VALUES_EXACT : PYI_VALUES_TOLERANCE;
+}
+
+// Tuning variant: PYI_TOL_VARIANT = <points per thread: 2|4><min blocks per SM: 2..6>
+// (read per launch so that one process can sweep them)
+static void tol2d_variant(int& pts, int& minb) {
+  pts = 2;  // round-2 sweep on B200 (profiles/r2_k1_sweep.txt): 2 points x 3 blocks per SM
+  minb = 3;
+  const char* e = std::getenv("PYI_TOL_VARIANT");
+  if (e && (e[0] == '2' || e[0] == '4') && e[1] >= '2' && e[1] <= '6') {
+    pts = e[0] - '0';
+    minb = e[1] - '0';
+  }
+}
+
+static bool tol2d_eligible(const GeoParams& p) {
+  const int mode = p.value_mode == PYI_VALUES_DEFAULT ? bilinear_default_mode() : p.value_mode;
+  if (mode != PYI_VALUES_TOLERANCE) return false;
+  if (p.dtype != PYI_F64 && p.dtype != PYI_I64 && p.dtype != PYI_U64) return false;  // float64 results
+  if (!fast2d_eligible(p)) return false;
+  if (!p.ax[0].tol_ok) return false;
+  if (p.ax[1].kind == 0 && !p.ax[1].tol_ok) return false;
+  const uintptr_t align = reinterpret_cast<uintptr_t>(p.x) | reinterpret_cast<uintptr_t>(p.y) |
+                          reinterpret_cast<uintptr_t>(p.out);
+  return (align & 31) == 0;
+}
+
+template <bool PER, int XM, int YM>
+static void launch_tol2d_v(const GeoParams& p, cudaStream_t stream) {
+  int pts, minb;
+  tol2d_variant(pts, minb);
+  const int blocks = grid_for((p.n + pts - 1) / pts, kFastThreads, minb);
+#define PYI_LAUNCH(P, B) bilinear2d_tol_kernel<PER, XM, YM, P, B><<<blocks, kFastThreads, 0, stream>>>(p)
+  if (pts == 2) {
+    switch (minb) {
+      case 2: PYI_LAUNCH(2, 2); break;
+      case 3: PYI_LAUNCH(2, 3); break;
+      case 4: PYI_LAUNCH(2, 4); break;
+      case 5: PYI_LAUNCH(2, 5); break;
+      default: PYI_LAUNCH(2, 6); break;
+    }
+  } else {
+    switch (minb) {
+      case 2: PYI_LAUNCH(4, 2); break;
+      case 3: PYI_LAUNCH(4, 3); break;
+      case 4: PYI_LAUNCH(4, 4); break;
+      case 5: PYI_LAUNCH(4, 5); break;
+      default: PYI_LAUNCH(4, 6); break;
+    }
+  }
+#undef PYI_LAUNCH
+}
+
+template <bool PER>
+static void launch_tol2d_p(const GeoParams& p, cudaStream_t stream) {
+  const int xm = p.ax[0].tol_ok;
+  const int ym = p.ax[1].kind != 0 ? 0 : p.ax[1].tol_ok;
+  if (xm == 2) {
+    if (ym == 2) launch_tol2d_v<PER, 2, 2>(p, stream);
+    else if (ym == 1) launch_tol2d_v<PER, 2, 1>(p, stream);
+    else launch_tol2d_v<PER, 2, 0>(p, stream);
+  } else {
+    if (ym == 2) launch_tol2d_v<PER, 1, 2>(p, stream);
+    else if (ym == 1) launch_tol2d_v<PER, 1, 1>(p, stream);
+    else launch_tol2d_v<PER, 1, 0>(p, stream);
+  }
+}
+
+static cudaError_t launch_tol2d(const GeoParams& p, cudaStream_t stream) {
+  const long long chunk = 1LL << 31;  // multiple of 4: keeps the 32-byte alignment of the slices
+  for (long long begin = 0; begin < p.n; begin += chunk) {
+    GeoParams q = p;
+    q.n = p.n - begin < chunk ? p.n - begin : chunk;
+    q.index_base = p.index_base + begin;
+    q.x = p.x + begin;
+    q.y = p.y + begin;
+    q.out = static_cast<char*>(p.out) + begin * 8;
+    if (p.ax[0].period != 0.0) launch_tol2d_p<true>(q, stream);
+    else launch_tol2d_p<false>(q, stream);
+    g_launches.fetch_add(1);
+    const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+  }
+  return cudaSuccess;
+}
+
+}  // namespace pyi

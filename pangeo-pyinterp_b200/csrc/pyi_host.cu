@@ -6,10 +6,13 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <atomic>
 #include <charconv>
 #include <cmath>
+#include <condition_variable>
 #include <cstdio>
 #include <cstring>
+#include <map>
 #include <memory>
 #include <mutex>
 #include <string>
@@ -82,11 +85,68 @@ double host_normalize(double x, double min, double period) {
   return x;
 }
 
+// a - b exactly representable? (TwoSum residual of the subtraction)
+bool exact_difference(double a, double b, double& diff) {
+  const volatile double s = a - b;
+  const volatile double bb = s - a;
+  const volatile double err = (a - (s - bb)) + (-b - bb);
+  diff = s;
+  return err == 0.0;
+}
+
+// Constants of the tolerance-mode bilinear kernel (pyi_fast2d_tol.cuh) for a
+// regular ascending float64 axis that already passed the fast-path checks.
+void tol_constants(const pyi_axis_desc& d, pyi::DAxis& out) {
+  out.tol_ok = 0;
+  const double step = d.step.f, start = d.start.f;
+  const double maxabs = std::max({std::fabs(d.min_value.f), std::fabs(d.max_value.f),
+                                  std::fabs(d.min_value.f + d.period.f)});
+  // |1 - dx / step| < 2^-26 for every spacing dx (the kernel's first-order
+  // reciprocal), and cell numbers far below 2^31
+  if (!(maxabs / step < 67108864.0) || d.size >= (1LL << 30)) return;
+  if (d.period.f != 0.0 && !(d.period.f >= 9.765625e-4)) return;  // |x| < 2^40 => |x / period| < 2^50
+  const double last = start + static_cast<double>(d.size - 1) * step;
+  const bool wraps = d.is_periodic != 0;
+  if (wraps) {
+    const volatile double e = 1.0 - (out.seam_c1 - last) * d.inv_step;
+    if (!(std::fabs(e) < 1.4901161193847656e-08)) return;
+  }
+  {
+    int ex = 0;
+    std::frexp(step, &ex);                    // step = m * 2^ex, m in [0.5, 1)
+    const int bound = std::min(40, ex - 1 + 28);  // |x| < 2^bound <= 2^28 * step
+    out.tol_xhi = (1023 + bound) << 20;
+  }
+  out.tol_off = -(start * d.inv_step) - 0.5;
+  out.tol_poff = d.period.f != 0.0 ? -(d.min_value.f * (1.0 / d.period.f)) - 0.5 : 0.0;
+  out.tol_ok = 1;
+  // exact nodes: fma(k, step, start) is the reference's node (two roundings)
+  // for every k, and every spacing is exactly `step`
+  bool exact = true;
+  double prev = start;
+  for (int64_t k = 0; exact && k < d.size; ++k) {
+    const volatile double prod = static_cast<double>(k) * step;
+    const volatile double node = start + prod;
+    exact = std::fma(static_cast<double>(k), step, start) == node;
+    double diff;
+    if (exact && k > 0) exact = exact_difference(node, prev, diff) && diff == step;
+    prev = node;
+  }
+  if (exact && wraps) {
+    double diff;
+    exact = exact_difference(out.seam_c1, last, diff) && diff == step;
+  }
+  if (exact) out.tol_ok = 2;
+}
+
 // Per-axis constants of the bilinear fast path (pyi_fast2d.cuh).
 void fast_constants(const pyi_axis* a, pyi::DAxis& out) {
   const pyi_axis_desc& d = a->d;
   out.hi = out.seam_c1 = out.seam_c1_f32 = 0.0;
   out.fast_ok = 0;
+  out.tol_ok = 0;
+  out.tol_xhi = 0;
+  out.tol_off = out.tol_poff = 0.0;
   out.ispan = 0;
   if (d.coord_type == PYI_COORD_I64) {
     // regular ascending int64 (temporal) axis without period: pyi_fastnd.cuh
@@ -125,6 +185,7 @@ void fast_constants(const pyi_axis* a, pyi::DAxis& out) {
   }
   out.hi = d.min_value.f + d.period.f;
   out.fast_ok = ok ? 1 : 0;
+  if (ok && d.kind == PYI_AXIS_REGULAR) tol_constants(d, out);
 }
 
 // Device mirror of an axis on the current device (uploaded once per device).
@@ -230,9 +291,17 @@ void parallel_memcpy(void* dst, const void* src, size_t bytes) {
 // H2D -> kernel -> D2H through kSlots stream slots, so the two copy engines
 // and the SMs overlap.  Caller buffers that are already page-locked are copied
 // directly; pageable ones are staged through page-locked buffers.
+//
+// Re-entrancy (the reference releases the GIL around the drivers and supports
+// free-threaded CPython: concurrent calls from several threads are legal): a
+// call checks a Workspace out of a per-device pool for its duration -- streams,
+// device chunk buffers, staging and the bounds-error key all belong to the
+// call.  Nothing is released when the calling thread's device changes.
 // ---------------------------------------------------------------------------
 constexpr int kSlots = 3;
-constexpr long long kChunk = 1LL << 23;  // points per chunk
+constexpr long long kChunk = 1LL << 23;     // points per chunk, upper bound
+constexpr long long kChunkMin = 1LL << 20;  // lower bound (calls above it are cut in >= 8 chunks)
+constexpr int kMaxWorkspacesPerDevice = 4;
 
 struct Slot {
   cudaStream_t stream{nullptr};
@@ -245,38 +314,20 @@ struct Slot {
 
 struct Workspace {
   int device{-1};
+  bool in_use{false};
   Slot slot[kSlots];
+  cudaEvent_t ready{nullptr};
   size_t dev_bytes{0};
   size_t pinned_bytes{0};
-  unsigned long long* oob_key{nullptr};       // device
-  unsigned long long* oob_host{nullptr};      // pinned
-  std::recursive_mutex mu;
-  ~Workspace() { release(); }
-  void release() {
-    for (auto& s : slot) {
-      if (s.stream) cudaStreamDestroy(s.stream);
-      if (s.done) cudaEventDestroy(s.done);
-      cudaFree(s.dev);
-      cudaFreeHost(s.pinned);
-      s = Slot{};
-    }
-    cudaFree(oob_key);
-    cudaFreeHost(oob_host);
-    oob_key = nullptr;
-    oob_host = nullptr;
-    dev_bytes = pinned_bytes = 0;
-  }
+  unsigned long long* oob_key{nullptr};   // device
+  unsigned long long* oob_host{nullptr};  // pinned
+  // the calling thread's current device must be `device`
   int ensure(size_t need_dev, size_t need_pinned) {
-    int dev = 0;
-    PYI_CUDA(cudaGetDevice(&dev));
-    if (dev != device) {
-      release();
-      device = dev;
-    }
     if (!oob_key) {
       PYI_CUDA(cudaMalloc(reinterpret_cast<void**>(&oob_key), sizeof(unsigned long long)));
       PYI_CUDA(cudaMallocHost(reinterpret_cast<void**>(&oob_host), sizeof(unsigned long long)));
     }
+    if (!ready) PYI_CUDA(cudaEventCreateWithFlags(&ready, cudaEventDisableTiming));
     for (auto& s : slot) {
       if (!s.stream) PYI_CUDA(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
       if (!s.done) PYI_CUDA(cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
@@ -285,26 +336,108 @@ struct Workspace {
       for (auto& s : slot) {
         cudaFree(s.dev);
         s.dev = nullptr;
-        PYI_CUDA(cudaMalloc(reinterpret_cast<void**>(&s.dev), need_dev));
       }
+      dev_bytes = 0;
+      for (auto& s : slot) PYI_CUDA(cudaMalloc(reinterpret_cast<void**>(&s.dev), need_dev));
       dev_bytes = need_dev;
     }
     if (need_pinned > pinned_bytes) {
       for (auto& s : slot) {
         cudaFreeHost(s.pinned);
         s.pinned = nullptr;
-        PYI_CUDA(cudaMallocHost(reinterpret_cast<void**>(&s.pinned), need_pinned));
       }
+      pinned_bytes = 0;
+      for (auto& s : slot) PYI_CUDA(cudaMallocHost(reinterpret_cast<void**>(&s.pinned), need_pinned));
       pinned_bytes = need_pinned;
     }
     return PYI_OK;
   }
+  // Every exit path of a call ends here: whatever is still in flight on the
+  // slot streams is waited for and the slots are marked idle, so a failed call
+  // cannot leave stale begin / count behind for the next one.
+  void quiesce() {
+    for (auto& s : slot) {
+      if (s.busy && s.stream) cudaStreamSynchronize(s.stream);
+      s.busy = false;
+      s.begin = s.count = 0;
+    }
+    cudaGetLastError();
+  }
 };
 
-Workspace& workspace() {
-  static Workspace w;
-  return w;
+class WorkspacePool {
+ public:
+  Workspace* acquire(int device) {
+    std::unique_lock<std::mutex> lock(mu_);
+    for (;;) {
+      int have = 0;
+      for (auto& w : all_) {
+        if (w->device != device) continue;
+        ++have;
+        if (!w->in_use) {
+          w->in_use = true;
+          return w.get();
+        }
+      }
+      if (have < kMaxWorkspacesPerDevice) {
+        all_.push_back(std::make_unique<Workspace>());
+        Workspace* w = all_.back().get();
+        w->device = device;
+        w->in_use = true;
+        return w;
+      }
+      cv_.wait(lock);
+    }
+  }
+  void release(Workspace* w) {
+    {
+      std::lock_guard<std::mutex> lock(mu_);
+      w->in_use = false;
+    }
+    cv_.notify_all();
+  }
+
+ private:
+  std::mutex mu_;
+  std::condition_variable cv_;
+  std::vector<std::unique_ptr<Workspace>> all_;
+};
+
+// never destroyed: no CUDA calls during static destruction
+WorkspacePool& pool() {
+  static WorkspacePool* p = new WorkspacePool();
+  return *p;
 }
+
+// A workspace of `device` for the duration of one call (the calling thread's
+// current device must be `device`).
+struct Lease {
+  Workspace* ws;
+  explicit Lease(int device) : ws(pool().acquire(device)) {}
+  Lease(const Lease&) = delete;
+  Lease& operator=(const Lease&) = delete;
+  ~Lease() {
+    ws->quiesce();
+    pool().release(ws);
+  }
+};
+
+// Binds the calling thread to `device` and restores the previous one.
+struct DeviceGuard {
+  int prev{-1};
+  bool switched{false};
+  cudaError_t err{cudaSuccess};
+  explicit DeviceGuard(int device) {
+    err = cudaGetDevice(&prev);
+    if (err == cudaSuccess && prev != device) {
+      err = cudaSetDevice(device);
+      switched = err == cudaSuccess;
+    }
+  }
+  ~DeviceGuard() {
+    if (switched) cudaSetDevice(prev);
+  }
+};
 
 // One input or output stream of a pipelined call.
 struct Column {
@@ -315,12 +448,19 @@ struct Column {
   size_t dev_off{0};  // offset inside the slot buffers
 };
 
-// Runs `launch(slot_stream, begin, count, dev_ptrs...)` over all chunks.
+long long chunk_points(long long n) {
+  if (n <= kChunkMin) return std::max<long long>(n, 1);
+  long long c = std::min(kChunk, std::max(kChunkMin, (n + 7) / 8));
+  return (c + 63) & ~63LL;  // keeps every chunk start 512-byte aligned in the streams
+}
+
+// Runs `launch(slot_stream, begin, count, dev_buffer)` over all chunks of the n
+// points the columns describe.  With `reset_key` the workspace's bounds-error
+// key is reset on the first slot's stream and every other slot waits for it.
 template <typename Launch>
-int run_pipeline(long long n, std::vector<Column>& cols, Launch&& launch) {
-  Workspace& ws = workspace();
-  std::unique_lock<std::recursive_mutex> lock(ws.mu);
-  const long long chunk = std::min<long long>(kChunk, std::max<long long>(n, 1));
+int run_pipeline(Workspace& ws, long long n, std::vector<Column>& cols, bool reset_key,
+                 Launch&& launch) {
+  const long long chunk = chunk_points(n);
   size_t off = 0;
   bool need_staging = false;
   for (auto& c : cols) {
@@ -331,6 +471,11 @@ int run_pipeline(long long n, std::vector<Column>& cols, Launch&& launch) {
   }
   int st = ws.ensure(off, need_staging ? off : 0);
   if (st != PYI_OK) return st;
+  if (reset_key) {
+    PYI_CUDA(cudaMemsetAsync(ws.oob_key, 0xff, sizeof(unsigned long long), ws.slot[0].stream));
+    PYI_CUDA(cudaEventRecord(ws.ready, ws.slot[0].stream));
+    for (int k = 1; k < kSlots; ++k) PYI_CUDA(cudaStreamWaitEvent(ws.slot[k].stream, ws.ready, 0));
+  }
 
   auto drain = [&](Slot& s) -> int {
     if (!s.busy) return PYI_OK;
@@ -353,6 +498,7 @@ int run_pipeline(long long n, std::vector<Column>& cols, Launch&& launch) {
     const long long count = std::min(chunk, n - begin);
     s.begin = begin;
     s.count = count;
+    s.busy = true;  // from here on the slot's stream may hold work of this call
     for (auto& c : cols) {
       if (!c.host_in) continue;
       const size_t bytes = static_cast<size_t>(count) * c.elem;
@@ -373,7 +519,6 @@ int run_pipeline(long long n, std::vector<Column>& cols, Launch&& launch) {
       PYI_CUDA(cudaMemcpyAsync(dst, s.dev + c.dev_off, bytes, cudaMemcpyDeviceToHost, s.stream));
     }
     PYI_CUDA(cudaEventRecord(s.done, s.stream));
-    s.busy = true;
   }
   for (int k = 0; k < kSlots; ++k) {
     st = drain(ws.slot[(which + k) % kSlots]);
@@ -381,6 +526,19 @@ int run_pipeline(long long n, std::vector<Column>& cols, Launch&& launch) {
   }
   return PYI_OK;
 }
+
+// Reads the workspace's bounds-error key once every chunk has drained.
+int read_key(Workspace& ws, unsigned long long& key) {
+  PYI_CUDA(cudaMemcpyAsync(ws.oob_host, ws.oob_key, sizeof(unsigned long long), cudaMemcpyDeviceToHost,
+                           ws.slot[0].stream));
+  PYI_CUDA(cudaStreamSynchronize(ws.slot[0].stream));
+  key = *ws.oob_host;
+  return PYI_OK;
+}
+
+// pyi_dist_init: how many devices one host-memory call may be sharded over
+std::atomic<int> g_dist_devices{1};
+constexpr long long kShardMinPoints = 1LL << 21;  // per device
 
 // Shared tail of the compute entry points: decode the atomicMin key.
 int report_oob(unsigned long long key, int64_t* oob_index, int* oob_axis) {
@@ -392,12 +550,23 @@ int report_oob(unsigned long long key, int64_t* oob_index, int* oob_axis) {
 
 }  // namespace
 
+// Device copies of a grid on a device other than the one it was created on
+// (single-call multi-GPU sharding, pyi_dist_init).
+struct GridReplica {
+  void* d_data{nullptr};
+  void* d_packed{nullptr};
+  void* d_planes{nullptr};
+  pyi::DAxis dax[4];
+  uint64_t version{0};
+};
+
 struct pyi_grid {
   int ndim{0};
   int dtype{0};
   int device{0};
   int64_t shape[4]{1, 1, 1, 1};
   size_t bytes{0};
+  size_t packed_bytes{0};
   std::unique_ptr<pyi_axis> axes[4];
   pyi::DAxis dax[4];
   void* d_data{nullptr};
@@ -408,7 +577,10 @@ struct pyi_grid {
   mutable void* d_planes{nullptr};
   mutable bool planes_tried{false};
   mutable std::mutex planes_mu;
-  unsigned long long* d_oob{nullptr};  // for device-memory calls
+  // bumped whenever a device copy on `device` changes; replicas re-sync lazily
+  mutable std::atomic<uint64_t> version{1};
+  mutable std::mutex rep_mu;
+  mutable std::map<int, std::unique_ptr<GridReplica>> replicas;
   // natural-spline constants of a uniformly spaced six-node window on x / y
   // (regular axes with moderate steps), computed on the device at creation
   double u6[2][24]{};
@@ -417,6 +589,188 @@ struct pyi_grid {
   int w_ok{0};
   double w6[2][12]{};
 };
+
+namespace {
+
+// What a kernel launch on one device reads of a grid.
+struct GridView {
+  const void* data{nullptr};
+  const void* packed{nullptr};
+  const void* planes{nullptr};
+  const pyi::DAxis* dax{nullptr};
+};
+
+void free_replica(int device, GridReplica& r) {
+  DeviceGuard guard(device);
+  cudaFree(r.d_data);
+  cudaFree(r.d_packed);
+  cudaFree(r.d_planes);
+  r = GridReplica{};
+}
+
+// View of `grid` on `device` (the calling thread's current device).  On the
+// grid's own device that is the handle itself; elsewhere a replica is created
+// or refreshed with peer copies (NVLink when peer access is available).
+int grid_view(const pyi_grid* grid, int device, GridView& view) {
+  if (device == grid->device) {
+    view.data = grid->d_data;
+    view.packed = grid->d_packed;
+    view.planes = grid->d_planes;
+    view.dax = grid->dax;
+    return PYI_OK;
+  }
+  std::lock_guard<std::mutex> lock(grid->rep_mu);
+  auto& slot = grid->replicas[device];
+  if (!slot) slot = std::make_unique<GridReplica>();
+  GridReplica& r = *slot;
+  const uint64_t version = grid->version.load();
+  if (r.version != version) {
+    int can = 0;
+    if (cudaDeviceCanAccessPeer(&can, device, grid->device) == cudaSuccess && can) {
+      const cudaError_t e = cudaDeviceEnablePeerAccess(grid->device, 0);
+      if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+    }
+    cudaGetLastError();
+    auto mirror = [&](void*& dst, const void* src, size_t bytes) -> int {
+      if (!src) {
+        if (dst) cudaFree(dst);
+        dst = nullptr;
+        return PYI_OK;
+      }
+      if (!dst) PYI_CUDA(cudaMalloc(&dst, std::max<size_t>(bytes, 64)));
+      PYI_CUDA(cudaMemcpyPeer(dst, device, src, grid->device, bytes));
+      return PYI_OK;
+    };
+    int st = mirror(r.d_data, grid->d_data, grid->bytes);
+    if (st == PYI_OK) st = mirror(r.d_packed, grid->d_packed, grid->packed_bytes);
+    if (st == PYI_OK) st = mirror(r.d_planes, grid->d_planes, grid->bytes);
+    for (int k = 0; st == PYI_OK && k < grid->ndim; ++k) st = device_axis(grid->axes[k].get(), r.dax[k]);
+    if (st != PYI_OK) return st;
+    PYI_CUDA(cudaDeviceSynchronize());
+    r.version = version;
+  }
+  view.data = r.d_data;
+  view.packed = r.d_packed;
+  view.planes = r.d_planes;
+  view.dax = r.dax;
+  return PYI_OK;
+}
+
+// Devices a host-memory call of n points is sharded over: the grid's own
+// device first, then the others below pyi_dist_init's count; at least
+// kShardMinPoints per device.
+std::vector<int> shard_devices(const pyi_grid* grid, long long n) {
+  std::vector<int> devices{grid->device};
+  const int limit = std::min(g_dist_devices.load(), device_count_cached());
+  const long long want = std::max<long long>(1, n / kShardMinPoints);
+  for (int d = 0; d < limit && static_cast<long long>(devices.size()) < want &&
+                  static_cast<int>(devices.size()) < limit; ++d) {
+    if (d != grid->device) devices.push_back(d);
+  }
+  return devices;
+}
+
+// A host-memory call: the n points are split into contiguous shards, one per
+// device, exactly as the reference's parallel_for splits them over threads
+// (parallel_for.hpp:46-53: n / G each, the first n % G shards take one more);
+// every shard runs its own chunk pipeline on its own workspace from its own
+// host thread.  `launch_on(view, oob_key, stream, global_begin, count, dev)`
+// enqueues the kernel of one chunk.  `key` receives the minimum bounds-error
+// key over all devices (indexes are global, so the lowest offending point wins
+// whatever the sharding).
+template <typename LaunchOn>
+int run_host_call(const pyi_grid* grid, long long n, const std::vector<Column>& cols, bool want_key,
+                  unsigned long long& key, LaunchOn&& launch_on) {
+  struct ShardResult {
+    int status{PYI_OK};
+    std::string error;
+    unsigned long long key{pyi::kNoOob};
+  };
+  const std::vector<int> devices = shard_devices(grid, n);
+  const int shards = static_cast<int>(devices.size());
+  std::vector<ShardResult> results(shards);
+  auto work = [&](int r) {
+    ShardResult& out = results[r];
+    auto run = [&]() -> int {
+      DeviceGuard guard(devices[r]);
+      if (guard.err != cudaSuccess) return cuda_fail(guard.err, "cudaSetDevice");
+      GridView view;
+      int st = grid_view(grid, devices[r], view);
+      if (st != PYI_OK) return st;
+      const long long each = n / shards, rem = n % shards;
+      const long long begin = r * each + std::min<long long>(r, rem);
+      const long long count = each + (r < rem ? 1 : 0);
+      if (count == 0) return PYI_OK;
+      std::vector<Column> mine = cols;
+      for (auto& c : mine) {
+        const size_t shift = static_cast<size_t>(begin) * c.elem;
+        if (c.host_in) c.host_in = static_cast<const char*>(c.host_in) + shift;
+        if (c.host_out) c.host_out = static_cast<char*>(c.host_out) + shift;
+      }
+      Lease lease(devices[r]);
+      Workspace& ws = *lease.ws;
+      st = run_pipeline(ws, count, mine, true,
+                        [&](cudaStream_t s, long long b, long long c, char* dev) {
+                          return launch_on(view, ws.oob_key, s, begin + b, c, dev, mine);
+                        });
+      if (st != PYI_OK) return st;
+      if (want_key) return read_key(ws, out.key);
+      return PYI_OK;
+    };
+    out.status = run();
+    if (out.status != PYI_OK) out.error = g_error;
+  };
+  if (shards == 1) {
+    work(0);
+  } else {
+    std::vector<std::thread> threads;
+    for (int r = 1; r < shards; ++r) threads.emplace_back(work, r);
+    work(0);
+    for (auto& t : threads) t.join();
+  }
+  key = pyi::kNoOob;
+  for (const auto& r : results) {
+    if (r.status != PYI_OK) return fail(r.status, r.error);
+    key = std::min(key, r.key);
+  }
+  return PYI_OK;
+}
+
+// Per-call bounds-error key of a device-memory call, from the stream-ordered
+// allocator: concurrent calls on different streams do not share it.
+struct DeviceKey {
+  unsigned long long* ptr{nullptr};
+  cudaStream_t stream{nullptr};
+  int open(cudaStream_t s) {
+    stream = s;
+    PYI_CUDA(cudaMallocAsync(reinterpret_cast<void**>(&ptr), sizeof(unsigned long long), s));
+    PYI_CUDA(cudaMemsetAsync(ptr, 0xff, sizeof(unsigned long long), s));
+    return PYI_OK;
+  }
+  int read(unsigned long long& key) {
+    key = pyi::kNoOob;
+    PYI_CUDA(cudaMemcpyAsync(&key, ptr, sizeof(key), cudaMemcpyDeviceToHost, stream));
+    PYI_CUDA(cudaStreamSynchronize(stream));
+    return PYI_OK;
+  }
+  ~DeviceKey() {
+    if (ptr) cudaFreeAsync(ptr, stream);
+  }
+};
+
+// A device-memory call works on the caller's buffers: they live on the
+// calling thread's current device, which must be the grid's.
+int require_grid_device(const pyi_grid* grid) {
+  int dev = -1;
+  PYI_CUDA(cudaGetDevice(&dev));
+  if (dev != grid->device) {
+    return fail(PYI_BAD_ARG, "device-memory call: the current device (" + std::to_string(dev) +
+                                 ") is not the grid's device (" + std::to_string(grid->device) + ")");
+  }
+  return PYI_OK;
+}
+
+}  // namespace
 
 extern "C" {
 
@@ -431,6 +785,24 @@ int pyi_set_device(int device) {
   PYI_CUDA(cudaSetDevice(device));
   return PYI_OK;
 }
+
+// Single-call multi-GPU sharding (the reference's drop-in
+// caller is ONE process whose parallel_for splits a call's points over its
+// workers, parallel_for.hpp:30-78): from now on every host-memory
+// interpolation call of this process is split into contiguous shards over the
+// first `n_devices` CUDA devices.  Returns the count in effect.
+int pyi_dist_init(int n_devices) {
+  const int have = device_count_cached();
+  if (have <= 0) {
+    fail(PYI_NO_DEVICE, "no CUDA device: pyinterp_b200 runs on the GPU only (no CPU fallback)");
+    return 0;
+  }
+  const int n = n_devices <= 0 ? have : std::min(n_devices, have);
+  g_dist_devices.store(n);
+  return n;
+}
+
+int pyi_dist_size(void) { return std::min(g_dist_devices.load(), std::max(1, device_count_cached())); }
 
 // ---- axes -----------------------------------------------------------------
 pyi_axis* pyi_axis_create_f64(const double* values, int64_t n, double epsilon, int has_period,
@@ -524,11 +896,14 @@ static int axis_lookup(const pyi_axis* axis_c, int64_t n, const void* coords, in
   cols[0].elem = 8;
   cols[1].host_out = out;
   cols[1].elem = out_elem;
-  return run_pipeline(n, cols, [&](cudaStream_t s, long long, long long count, char* dev) {
+  int dev = 0;
+  PYI_CUDA(cudaGetDevice(&dev));
+  Lease lease(dev);
+  return run_pipeline(*lease.ws, n, cols, false, [&](cudaStream_t s, long long, long long count, char* d) {
     pyi::FindParams q = p;
     q.n = count;
-    q.coords = dev + cols[0].dev_off;
-    q.out = reinterpret_cast<long long*>(dev + cols[1].dev_off);
+    q.coords = d + cols[0].dev_off;
+    q.out = reinterpret_cast<long long*>(d + cols[1].dev_off);
     return pairs ? pyi::launch_find_indexes(q, s) : pyi::launch_find_index(q, s);
   });
 }
@@ -594,7 +969,10 @@ pyi_grid* pyi_grid_create(int ndim, const pyi_axis* const* axes, int dtype, cons
     int st = device_axis(g->axes[k].get(), g->dax[k]);
     if (st != PYI_OK) return set(st);
   }
-  if (mem == PYI_MEM_DEVICE && (flags & PYI_GRID_BORROW_DEVICE)) {
+  // a borrowed pointer must satisfy the 16-byte vector loads of the windowed
+  // kernels; anything else is copied into an aligned allocation
+  if (mem == PYI_MEM_DEVICE && (flags & PYI_GRID_BORROW_DEVICE) &&
+      (reinterpret_cast<uintptr_t>(data) & 15) == 0) {
     g->d_data = const_cast<void*>(data);
     g->borrowed = true;
   } else {
@@ -607,8 +985,6 @@ pyi_grid* pyi_grid_create(int ndim, const pyi_axis* const* axes, int dtype, cons
       return set(cuda_fail(e, "cudaMemcpy(grid)"));
     }
   }
-  cudaError_t e = cudaMalloc(reinterpret_cast<void**>(&g->d_oob), sizeof(unsigned long long));
-  if (e != cudaSuccess) return set(cuda_fail(e, "cudaMalloc(oob)"));
   if (ndim >= 2) {
     double* d_tmp = nullptr;
     if (cudaMalloc(reinterpret_cast<void**>(&d_tmp), 24 * sizeof(double)) == cudaSuccess) {
@@ -635,7 +1011,12 @@ pyi_grid* pyi_grid_create(int ndim, const pyi_axis* const* axes, int dtype, cons
         const pyi::DAxis& a = g->dax[k];
         const double mag = std::fabs(a.step);
         const bool closes = !a.periodic || std::fabs(static_cast<double>(a.n) * a.step) == a.period;
-        if (a.coord_i64 || a.n < 6 || a.kind != 0 || !closes ||
+        // the weights are those of exactly uniform nodes k * step; the
+        // reference's nodes start + k * step are rounded to ulp(|coordinate|),
+        // a relative derivative error of ~ulp(|coordinate|) / |step|: only
+        // axes with max |coordinate| / |step| < 2^16 take the weights kernel
+        const double reach = std::max(std::fabs(a.min), std::fabs(a.max)) / mag;
+        if (a.coord_i64 || a.n < 6 || a.kind != 0 || !closes || !(reach < 65536.0) ||
             !(mag >= 9.313225746154785e-10 && mag <= 1073741824.0)) {
           break;
         }
@@ -676,23 +1057,33 @@ static int grid_planes(const pyi_grid* grid, bool refresh) {
     PYI_CUDA(cudaMemGetInfo(&free_b, &total_b));
     if (grid->bytes > free_b / 2) return PYI_OK;
     PYI_CUDA(cudaMalloc(&grid->d_planes, std::max<size_t>(grid->bytes, 64)));
+    refresh = true;
   }
   const long long shape[4] = {grid->shape[0], grid->shape[1], grid->shape[2], grid->shape[3]};
   cudaError_t e = pyi::launch_plane_major(grid->d_data, grid->d_planes,
                                           static_cast<int>(dtype_size(grid->dtype)), shape, nullptr);
   if (e != cudaSuccess) return cuda_fail(e, "plane_major");
   PYI_CUDA(cudaStreamSynchronize(nullptr));
+  if (refresh) grid->version.fetch_add(1);
   return PYI_OK;
 }
 
 int pyi_grid_update(pyi_grid* grid, const void* data, int mem) {
   if (!grid || !data) return fail(PYI_BAD_ARG, "null argument");
-  if (grid->borrowed) {
+  DeviceGuard guard(grid->device);
+  if (guard.err != cudaSuccess) return cuda_fail(guard.err, "cudaSetDevice");
+  if (grid->borrowed && (reinterpret_cast<uintptr_t>(data) & 15) == 0 && mem == PYI_MEM_DEVICE) {
     grid->d_data = const_cast<void*>(data);
   } else {
+    if (grid->borrowed) {  // the new pointer cannot be borrowed: own a copy from now on
+      grid->d_data = nullptr;
+      grid->borrowed = false;
+      PYI_CUDA(cudaMalloc(&grid->d_data, std::max<size_t>(grid->bytes, 16)));
+    }
     PYI_CUDA(cudaMemcpy(grid->d_data, data, grid->bytes,
                         mem == PYI_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice));
   }
+  grid->version.fetch_add(1);
   if (grid->d_planes) {
     int st = grid_planes(grid, true);
     if (st != PYI_OK) return st;
@@ -712,6 +1103,8 @@ int pyi_grid_pack(pyi_grid* grid) {
   }
   const size_t elem = result_is_f64(grid->dtype) ? 8 : 4;
   const size_t bytes = (cells << grid->ndim) * elem;
+  DeviceGuard guard(grid->device);
+  if (guard.err != cudaSuccess) return cuda_fail(guard.err, "cudaSetDevice");
   if (!grid->d_packed) {
     // The packed copy is 2^ndim x the grid (in the result type).  It is an
     // optimisation: when it would not leave room for the query streams the
@@ -725,18 +1118,26 @@ int pyi_grid_pack(pyi_grid* grid) {
                                          grid->d_packed, nullptr);
   if (e != cudaSuccess) return cuda_fail(e, "pack_cells");
   PYI_CUDA(cudaStreamSynchronize(nullptr));
+  grid->packed_bytes = bytes;
+  grid->version.fetch_add(1);
   return PYI_OK;
 }
 
 void pyi_grid_destroy(pyi_grid* grid) {
   if (!grid) return;
-  if (!grid->borrowed) cudaFree(grid->d_data);
-  cudaFree(grid->d_packed);
-  cudaFree(grid->d_planes);
-  cudaFree(grid->d_oob);
+  {
+    DeviceGuard guard(grid->device);
+    if (!grid->borrowed) cudaFree(grid->d_data);
+    cudaFree(grid->d_packed);
+    cudaFree(grid->d_planes);
+  }
+  for (auto& kv : grid->replicas) {
+    if (kv.second) free_replica(kv.first, *kv.second);
+  }
   for (auto& a : grid->axes) {
     if (a) free_axis_device(a.get());
   }
+  cudaGetLastError();
   delete grid;
 }
 
@@ -753,10 +1154,10 @@ int pyi_geometric(const pyi_grid* grid, const pyi_geometric_config* cfg, int64_t
   if (cfg->method < PYI_BILINEAR || cfg->method > PYI_NEAREST) {
     return fail(PYI_BAD_ARG, "pyi_geometric: unknown method");
   }
+  if (cfg->value_mode < PYI_VALUES_DEFAULT || cfg->value_mode > PYI_VALUES_TOLERANCE) {
+    return fail(PYI_BAD_ARG, "pyi_geometric: unknown value mode");
+  }
   pyi::GeoParams p{};
-  for (int k = 0; k < grid->ndim; ++k) p.ax[k] = grid->dax[k];
-  p.data = grid->d_data;
-  p.packed = grid->d_packed;
   p.dtype = grid->dtype;
   p.ndim = grid->ndim;
   p.method = cfg->method;
@@ -764,27 +1165,40 @@ int pyi_geometric(const pyi_grid* grid, const pyi_geometric_config* cfg, int64_t
   p.z_method = cfg->z_method;
   p.u_method = cfg->u_method;
   p.bounds_error = cfg->bounds_error;
+  p.value_mode = cfg->value_mode;
   if (n == 0) return PYI_OK;
   const size_t out_elem = result_is_f64(grid->dtype) ? 8 : 4;
+  auto bind = [&](pyi::GeoParams& q, const GridView& v) {
+    for (int k = 0; k < grid->ndim; ++k) q.ax[k] = v.dax[k];
+    q.data = v.data;
+    q.packed = v.packed;
+  };
 
   if (mem == PYI_MEM_DEVICE) {
+    st = require_grid_device(grid);
+    if (st != PYI_OK) return st;
     cudaStream_t s = static_cast<cudaStream_t>(stream);
+    GridView view;
+    grid_view(grid, grid->device, view);
+    bind(p, view);
     p.n = n;
     p.x = x;
     p.y = y;
     p.z = z;
     p.u = u;
     p.out = out;
-    p.oob_key = grid->d_oob;
+    DeviceKey key_buf;
     if (cfg->bounds_error) {
-      PYI_CUDA(cudaMemsetAsync(grid->d_oob, 0xff, sizeof(unsigned long long), s));
+      st = key_buf.open(s);
+      if (st != PYI_OK) return st;
+      p.oob_key = key_buf.ptr;
     }
     cudaError_t e = pyi::launch_geometric(p, s);
     if (e != cudaSuccess) return cuda_fail(e, "geometric kernel");
     if (cfg->bounds_error) {
       unsigned long long key = pyi::kNoOob;
-      PYI_CUDA(cudaMemcpyAsync(&key, grid->d_oob, sizeof(key), cudaMemcpyDeviceToHost, s));
-      PYI_CUDA(cudaStreamSynchronize(s));
+      st = key_buf.read(key);
+      if (st != PYI_OK) return st;
       return report_oob(key, oob_index, oob_axis);
     }
     return PYI_OK;
@@ -805,30 +1219,24 @@ int pyi_geometric(const pyi_grid* grid, const pyi_geometric_config* cfg, int64_t
   co.elem = out_elem;
   cols.push_back(co);
   const size_t cout_ = cols.size() - 1;
-  Workspace& ws = workspace();
-  // the key lives in the workspace; the lock is held for the whole call
-  std::lock_guard<std::recursive_mutex> ws_lock(ws.mu);
-  st = ws.ensure(0, 0);
+  unsigned long long key = pyi::kNoOob;
+  st = run_host_call(grid, n, cols, cfg->bounds_error != 0, key,
+                     [&](const GridView& view, unsigned long long* oob_key, cudaStream_t s,
+                         long long begin, long long count, char* dev, const std::vector<Column>& c) {
+                       pyi::GeoParams q = p;
+                       bind(q, view);
+                       q.n = count;
+                       q.x = reinterpret_cast<const double*>(dev + c[cx].dev_off);
+                       q.y = reinterpret_cast<const double*>(dev + c[cy].dev_off);
+                       if (grid->ndim >= 3) q.z = dev + c[cz].dev_off;
+                       if (grid->ndim >= 4) q.u = reinterpret_cast<const double*>(dev + c[cu].dev_off);
+                       q.out = dev + c[cout_].dev_off;
+                       q.oob_key = oob_key;
+                       q.index_base = begin;
+                       return pyi::launch_geometric(q, s);
+                     });
   if (st != PYI_OK) return st;
-  PYI_CUDA(cudaMemset(ws.oob_key, 0xff, sizeof(unsigned long long)));
-  st = run_pipeline(n, cols, [&](cudaStream_t s, long long begin, long long count, char* dev) {
-    pyi::GeoParams q = p;
-    q.n = count;
-    q.x = reinterpret_cast<const double*>(dev + cols[cx].dev_off);
-    q.y = reinterpret_cast<const double*>(dev + cols[cy].dev_off);
-    if (grid->ndim >= 3) q.z = dev + cols[cz].dev_off;
-    if (grid->ndim >= 4) q.u = reinterpret_cast<const double*>(dev + cols[cu].dev_off);
-    q.out = dev + cols[cout_].dev_off;
-    q.oob_key = ws.oob_key;
-    q.index_base = begin;
-    return pyi::launch_geometric(q, s);
-  });
-  if (st != PYI_OK) return st;
-  if (cfg->bounds_error) {
-    unsigned long long key = pyi::kNoOob;
-    PYI_CUDA(cudaMemcpy(&key, ws.oob_key, sizeof(key), cudaMemcpyDeviceToHost));
-    return report_oob(key, oob_index, oob_axis);
-  }
+  if (cfg->bounds_error) return report_oob(key, oob_index, oob_axis);
   return PYI_OK;
 }
 
@@ -850,6 +1258,7 @@ int pyi_windowed2d(const pyi_grid* grid, const pyi_windowed_config* cfg, int64_t
   c.boundary = cfg->boundary;
   c.bounds_error = cfg->bounds_error;
   c.num_threads = cfg->num_threads;
+  c.value_mode = cfg->value_mode;
   return pyi_windowed(grid, &c, n, x, y, nullptr, nullptr, out, mem, oob_index, oob_axis, stream);
 }
 
@@ -872,6 +1281,9 @@ int pyi_windowed(const pyi_grid* grid, const pyi_windowed_nd_config* cfg, int64_
   if (nd == 1 && cfg->method < PYI_S_AKIMA) {
     return fail(PYI_BAD_ARG, "pyi_windowed: a 1-D grid takes a univariate fitting model");
   }
+  if (cfg->value_mode < PYI_VALUES_DEFAULT || cfg->value_mode > PYI_VALUES_TOLERANCE) {
+    return fail(PYI_BAD_ARG, "pyi_windowed: unknown value mode");
+  }
   if (cfg->derivative && nd != 1) {
     return fail(PYI_BAD_ARG, "pyi_windowed: derivatives are defined for 1-D grids only");
   }
@@ -880,8 +1292,6 @@ int pyi_windowed(const pyi_grid* grid, const pyi_windowed_nd_config* cfg, int64_
   }
   if (n == 0) return PYI_OK;
   pyi::WinNdParams p{};
-  for (int k = 0; k < nd; ++k) p.ax[k] = grid->dax[k];
-  p.data = grid->d_data;
   p.dtype = grid->dtype;
   p.ndim = nd;
   p.method = cfg->method;
@@ -892,38 +1302,54 @@ int pyi_windowed(const pyi_grid* grid, const pyi_windowed_nd_config* cfg, int64_
   p.z_method = cfg->z_method;
   p.u_method = cfg->u_method;
   p.derivative = cfg->derivative;
+  p.value_mode = cfg->value_mode;
   for (int a = 0; a < 2; ++a) {
     p.u6_ok[a] = grid->u6_ok[a];
     std::memcpy(p.u6[a], grid->u6[a], sizeof(p.u6[a]));
   }
-  if (nd >= 3 && cfg->method == PYI_S_BICUBIC && cfg->half_x == 3 && cfg->half_y == 3) {
+  const bool want_planes =
+      nd >= 3 && cfg->method == PYI_S_BICUBIC && cfg->half_x == 3 && cfg->half_y == 3;
+  if (want_planes) {
+    DeviceGuard guard(grid->device);
+    if (guard.err != cudaSuccess) return cuda_fail(guard.err, "cudaSetDevice");
     st = grid_planes(grid, false);
     if (st != PYI_OK) return st;
-    p.planes = grid->d_planes;
   }
   p.w_ok = grid->w_ok;
   for (int a = 0; a < 2; ++a) std::memcpy(p.w6[a], grid->w6[a], sizeof(p.w6[a]));
   p.cells = 1;
   for (int a = 0; a < nd; ++a) p.cells *= grid->shape[a];
   const size_t out_elem = result_is_f64(grid->dtype) ? 8 : 4;
+  auto bind = [&](pyi::WinNdParams& q, const GridView& v) {
+    for (int k = 0; k < nd; ++k) q.ax[k] = v.dax[k];
+    q.data = v.data;
+    q.planes = want_planes ? v.planes : nullptr;
+  };
   if (mem == PYI_MEM_DEVICE) {
+    st = require_grid_device(grid);
+    if (st != PYI_OK) return st;
     cudaStream_t s = static_cast<cudaStream_t>(stream);
+    GridView view;
+    grid_view(grid, grid->device, view);
+    bind(p, view);
     p.n = n;
     p.x = x;
     p.y = y;
     p.z = z;
     p.u = u;
     p.out = out;
-    p.oob_key = grid->d_oob;
+    DeviceKey key_buf;
     if (cfg->bounds_error) {
-      PYI_CUDA(cudaMemsetAsync(grid->d_oob, 0xff, sizeof(unsigned long long), s));
+      st = key_buf.open(s);
+      if (st != PYI_OK) return st;
+      p.oob_key = key_buf.ptr;
     }
     cudaError_t e = pyi::launch_windowed_nd(p, s);
     if (e != cudaSuccess) return cuda_fail(e, "windowed kernel");
     if (cfg->bounds_error) {
       unsigned long long key = pyi::kNoOob;
-      PYI_CUDA(cudaMemcpyAsync(&key, grid->d_oob, sizeof(key), cudaMemcpyDeviceToHost, s));
-      PYI_CUDA(cudaStreamSynchronize(s));
+      st = key_buf.read(key);
+      if (st != PYI_OK) return st;
       return report_oob(key, oob_index, oob_axis);
     }
     return PYI_OK;
@@ -944,29 +1370,24 @@ int pyi_windowed(const pyi_grid* grid, const pyi_windowed_nd_config* cfg, int64_
   co.elem = out_elem;
   cols.push_back(co);
   const size_t cout_ = cols.size() - 1;
-  Workspace& ws = workspace();
-  std::lock_guard<std::recursive_mutex> ws_lock(ws.mu);
-  st = ws.ensure(0, 0);
+  unsigned long long key = pyi::kNoOob;
+  st = run_host_call(grid, n, cols, cfg->bounds_error != 0, key,
+                     [&](const GridView& view, unsigned long long* oob_key, cudaStream_t s,
+                         long long begin, long long count, char* dev, const std::vector<Column>& c) {
+                       pyi::WinNdParams q = p;
+                       bind(q, view);
+                       q.n = count;
+                       q.x = reinterpret_cast<const double*>(dev + c[cx].dev_off);
+                       if (nd >= 2) q.y = reinterpret_cast<const double*>(dev + c[cy].dev_off);
+                       if (nd >= 3) q.z = dev + c[cz].dev_off;
+                       if (nd >= 4) q.u = reinterpret_cast<const double*>(dev + c[cu].dev_off);
+                       q.out = dev + c[cout_].dev_off;
+                       q.oob_key = oob_key;
+                       q.index_base = begin;
+                       return pyi::launch_windowed_nd(q, s);
+                     });
   if (st != PYI_OK) return st;
-  PYI_CUDA(cudaMemset(ws.oob_key, 0xff, sizeof(unsigned long long)));
-  st = run_pipeline(n, cols, [&](cudaStream_t s, long long begin, long long count, char* dev) {
-    pyi::WinNdParams q = p;
-    q.n = count;
-    q.x = reinterpret_cast<const double*>(dev + cols[cx].dev_off);
-    if (nd >= 2) q.y = reinterpret_cast<const double*>(dev + cols[cy].dev_off);
-    if (nd >= 3) q.z = dev + cols[cz].dev_off;
-    if (nd >= 4) q.u = reinterpret_cast<const double*>(dev + cols[cu].dev_off);
-    q.out = dev + cols[cout_].dev_off;
-    q.oob_key = ws.oob_key;
-    q.index_base = begin;
-    return pyi::launch_windowed_nd(q, s);
-  });
-  if (st != PYI_OK) return st;
-  if (cfg->bounds_error) {
-    unsigned long long key = pyi::kNoOob;
-    PYI_CUDA(cudaMemcpy(&key, ws.oob_key, sizeof(key), cudaMemcpyDeviceToHost));
-    return report_oob(key, oob_index, oob_axis);
-  }
+  if (cfg->bounds_error) return report_oob(key, oob_index, oob_axis);
   return PYI_OK;
 }
 
@@ -988,10 +1409,6 @@ int pyi_datetime_convert(int src, int dst, int64_t n, const int64_t* in, int64_t
     return fail(PYI_OVERFLOW, (key & 3) == 1 ? "integer overflow in multiplication"
                                               : "integer overflow in addition");
   };
-  Workspace& ws = workspace();
-  std::lock_guard<std::recursive_mutex> ws_lock(ws.mu);
-  st = ws.ensure(0, 0);
-  if (st != PYI_OK) return st;
   if (mem == PYI_MEM_DEVICE) {
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     if (src == dst) {  // dateutils.hpp:824-826
@@ -1000,14 +1417,16 @@ int pyi_datetime_convert(int src, int dst, int64_t n, const int64_t* in, int64_t
       }
       return PYI_OK;
     }
-    PYI_CUDA(cudaMemsetAsync(ws.oob_key, 0xff, sizeof(unsigned long long), s));
+    DeviceKey key_buf;
+    st = key_buf.open(s);
+    if (st != PYI_OK) return st;
     cudaError_t e = pyi::launch_datetime_convert(reinterpret_cast<const long long*>(in),
                                                  reinterpret_cast<long long*>(out), n, 0, src, dst,
-                                                 ws.oob_key, s);
+                                                 key_buf.ptr, s);
     if (e != cudaSuccess) return cuda_fail(e, "datetime kernel");
     unsigned long long key = pyi::kNoOob;
-    PYI_CUDA(cudaMemcpyAsync(&key, ws.oob_key, sizeof(key), cudaMemcpyDeviceToHost, s));
-    PYI_CUDA(cudaStreamSynchronize(s));
+    st = key_buf.read(key);
+    if (st != PYI_OK) return st;
     return report(key);
   }
   if (src == dst) {
@@ -1017,15 +1436,19 @@ int pyi_datetime_convert(int src, int dst, int64_t n, const int64_t* in, int64_t
   std::vector<Column> cols(2);
   cols[0].host_in = in;
   cols[1].host_out = out;
-  PYI_CUDA(cudaMemset(ws.oob_key, 0xff, sizeof(unsigned long long)));
-  st = run_pipeline(n, cols, [&](cudaStream_t s, long long begin, long long count, char* dev) {
-    return pyi::launch_datetime_convert(reinterpret_cast<const long long*>(dev + cols[0].dev_off),
-                                        reinterpret_cast<long long*>(dev + cols[1].dev_off), count,
+  int dev = 0;
+  PYI_CUDA(cudaGetDevice(&dev));
+  Lease lease(dev);
+  Workspace& ws = *lease.ws;
+  st = run_pipeline(ws, n, cols, true, [&](cudaStream_t s, long long begin, long long count, char* d) {
+    return pyi::launch_datetime_convert(reinterpret_cast<const long long*>(d + cols[0].dev_off),
+                                        reinterpret_cast<long long*>(d + cols[1].dev_off), count,
                                         begin, src, dst, ws.oob_key, s);
   });
   if (st != PYI_OK) return st;
   unsigned long long key = pyi::kNoOob;
-  PYI_CUDA(cudaMemcpy(&key, ws.oob_key, sizeof(key), cudaMemcpyDeviceToHost));
+  st = read_key(ws, key);
+  if (st != PYI_OK) return st;
   return report(key);
 }
 
@@ -1078,18 +1501,22 @@ int fill_entry(bool multigrid, void* grid, int dtype, int64_t nx, int64_t ny,
     return PYI_OK;
   }
   const size_t bytes = static_cast<size_t>(nx) * static_cast<size_t>(ny) * dtype_size(dtype);
-  Workspace& ws = workspace();
-  std::lock_guard<std::recursive_mutex> ws_lock(ws.mu);
+  int dev = 0;
+  PYI_CUDA(cudaGetDevice(&dev));
+  Lease lease(dev);
+  Workspace& ws = *lease.ws;
   st = ws.ensure(bytes, 0);
   if (st != PYI_OK) return st;
   Slot& slot = ws.slot[0];
+  slot.busy = true;
   PYI_CUDA(cudaMemcpyAsync(slot.dev, grid, bytes, cudaMemcpyHostToDevice, slot.stream));
   cudaError_t e = run(slot.dev, slot.stream);
   if (e != cudaSuccess) return cuda_fail(e, "fill kernels");
-  if (its > 0) {
-    PYI_CUDA(cudaMemcpyAsync(grid, slot.dev, bytes, cudaMemcpyDeviceToHost, slot.stream));
-  }
+  // always copied back: with max_iterations == 0 the reference still leaves
+  // the first guess in the undefined cells (gauss_seidel.hpp:184-199)
+  PYI_CUDA(cudaMemcpyAsync(grid, slot.dev, bytes, cudaMemcpyDeviceToHost, slot.stream));
   PYI_CUDA(cudaStreamSynchronize(slot.stream));
+  slot.busy = false;
   *iterations = its;
   *max_residual = res;
   return PYI_OK;

@@ -164,12 +164,16 @@ static cudaError_t launch_geometric_nd(const GeoParams& p, cudaStream_t stream) 
 // K1 fast path (pyi_fast2d.cuh)
 static bool fast2d_eligible(const GeoParams& p);
 static cudaError_t launch_fast2d(const GeoParams& p, cudaStream_t stream);
+// K1 in tolerance value mode (pyi_fast2d_tol.cuh)
+static bool tol2d_eligible(const GeoParams& p);
+static cudaError_t launch_tol2d(const GeoParams& p, cudaStream_t stream);
 // K2 / K3 fast path (pyi_fastnd.cuh)
 static bool fastnd_eligible(const GeoParams& p);
 static cudaError_t launch_fastnd(const GeoParams& p, cudaStream_t stream);
 
 cudaError_t launch_geometric(const GeoParams& p, cudaStream_t stream) {
   if (p.n <= 0) return cudaSuccess;
+  if (tol2d_eligible(p)) return launch_tol2d(p, stream);
   if (fast2d_eligible(p)) return launch_fast2d(p, stream);
   if (fastnd_eligible(p)) return launch_fastnd(p, stream);
   const bool zi64 = p.ndim >= 3 && p.ax[2].coord_i64;
@@ -368,4 +372,5 @@ cudaError_t launch_pack_cells(const void* data, int dtype, int ndim, const int* 
 }  // namespace pyi
 
 #include "pyi_fast2d.cuh"
+#include "pyi_fast2d_tol.cuh"
 #include "pyi_fastnd.cuh"

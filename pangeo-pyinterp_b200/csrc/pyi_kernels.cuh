@@ -20,6 +20,7 @@ struct GeoParams {
   int32_t ndim;
   int32_t method, idw_exp, z_method, u_method;
   int32_t bounds_error;
+  int32_t value_mode;  // pyi_value_mode as given by the caller (DEFAULT resolved at launch)
   long long n;
   long long index_base;  // global index of point 0 (chunked host calls)
   const double* x;
@@ -62,6 +63,7 @@ struct WinNdParams {
   int32_t bounds_error;
   int32_t z_method, u_method;
   int32_t derivative;
+  int32_t value_mode;  // pyi_value_mode as given by the caller
   long long n;
   long long index_base;
   const double* x;

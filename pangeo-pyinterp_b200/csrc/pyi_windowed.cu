@@ -9,8 +9,9 @@ namespace pyi {
 // through the generic kernel so the fast path can be compared with it.
 // PYINTERP_B200_BICUBIC=exact keeps the bit-identical bicubic fast paths
 // (pyi_fastwin*.cuh) instead of the precomputed-weights kernel (pyi_bicubicw.cuh).
-static bool exact_bicubic() {
-  const char* e = getenv("PYINTERP_B200_BICUBIC");
+static bool exact_bicubic(const WinNdParams& p) {
+  if (p.value_mode != PYI_VALUES_DEFAULT) return p.value_mode == PYI_VALUES_EXACT;
+  const char* e = getenv("PYINTERP_B200_BICUBIC");  // per launch: the tests switch it
   return e != nullptr && e[0] == 'e';
 }
 static bool force_generic() {
@@ -37,7 +38,7 @@ cudaError_t launch_windowed_nd(const WinNdParams& p, cudaStream_t stream) {
   // bicubic on a 6 x 6 window, 2-D .. 4-D: precomputed-weights pass, then the
   // generic kernel recomputes the points that pass tagged
   if (p.ndim >= 2 && p.method == PYI_S_BICUBIC && p.half_x == 3 && p.half_y == 3 && p.w_ok &&
-      (p.ndim == 2 || p.planes) && !force_generic() && !exact_bicubic()) {
+      (p.ndim == 2 || p.planes) && !force_generic() && !exact_bicubic(p)) {
     cudaError_t e = launch_bicubicw(p, stream);
     if (e != cudaSuccess) return e;
     WinNdParams q = p;

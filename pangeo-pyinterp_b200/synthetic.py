@@ -28,25 +28,31 @@ def depth_axis_values(n: int = 50) -> np.ndarray:
 
 
 def field(lon, lat, nz: int = 0, nu: int = 0, dtype="float64", seed: int = 42, noise: float = 1e-3):
-    """sin(lon) cos(lat) (1 + 0.1 k_z + 0.01 k_u) + noise, C-order [lon][lat][z][u]."""
+    """sin(lon) cos(lat) (1 + 0.1 k_z + 0.01 k_u) + noise, C-order [lon][lat][z][u].
+    Built slab by slab along lon (float64 arithmetic, then the cast) so that a
+    2.5 GB float32 4-D grid does not need a 5 GB float64 temporary; values and
+    the noise stream are those of the one-shot expression."""
     rng = np.random.Generator(np.random.PCG64(seed))
-    base = np.sin(np.radians(lon))[:, None] * np.cos(np.radians(lat))[None, :]
-    shape = [lon.size, lat.size]
-    g = base
-    if nz:
-        g = g[..., None] * (1.0 + 0.1 * np.arange(nz))
-        shape.append(nz)
-    if nu:
-        g = g[..., None] * (1.0 + 0.01 * np.arange(nu)) if nz else g
-        shape.append(nu)
-    g = np.ascontiguousarray(np.broadcast_to(g, shape)).astype(np.float64)
-    if noise:
-        g = g + noise * rng.standard_normal(g.shape)
     dt = np.dtype(dtype)
-    if dt.kind in "iu":
-        info = np.iinfo(dt)
-        g = np.clip(np.round(g * 1000.0), info.min, info.max)
-    return np.ascontiguousarray(g.astype(dt))
+    shape = [lon.size, lat.size] + ([nz] if nz else []) + ([nu] if nu else [])
+    out = np.empty(shape, dtype=dt)
+    sin_lon = np.sin(np.radians(lon))
+    cos_lat = np.cos(np.radians(lat))
+    rows = max(1, (1 << 24) // max(1, int(np.prod(shape[1:]))))
+    for a in range(0, lon.size, rows):
+        g = sin_lon[a:a + rows, None] * cos_lat[None, :]
+        if nz:
+            g = g[..., None] * (1.0 + 0.1 * np.arange(nz))
+        if nu:
+            g = g[..., None] * (1.0 + 0.01 * np.arange(nu)) if nz else g
+        g = np.ascontiguousarray(np.broadcast_to(g, [g.shape[0]] + shape[1:])).astype(np.float64)
+        if noise:
+            g = g + noise * rng.standard_normal(g.shape)
+        if dt.kind in "iu":
+            info = np.iinfo(dt)
+            g = np.clip(np.round(g * 1000.0), info.min, info.max)
+        out[a:a + rows] = g.astype(dt)
+    return out
 
 
 def queries(n: int, seed: int, ndim: int = 2, time_values=None, depth_max: float = 5600.0,

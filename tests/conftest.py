@@ -49,3 +49,17 @@ def bicubic_mode(request, monkeypatch):
     else:
         monkeypatch.delenv("PYINTERP_B200_BICUBIC", raising=False)
     return request.param
+
+
+@pytest.fixture(params=["tolerance", "exact"])
+def bilinear_mode(request, monkeypatch):
+    """The two value modes of geometric bilinear on float64-result 2-D grids:
+    the default tolerance kernel (pyi_fast2d_tol.cuh: verified brackets, FMA /
+    reciprocal weights, values within the north-star 1e-12) and the
+    bit-identical one (PYINTERP_B200_BILINEAR=exact, pyi_fast2d.cuh).  Every
+    other kernel is bit-identical in both modes."""
+    if request.param == "exact":
+        monkeypatch.setenv("PYINTERP_B200_BILINEAR", "exact")
+    else:
+        monkeypatch.delenv("PYINTERP_B200_BILINEAR", raising=False)
+    return request.param

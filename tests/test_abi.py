@@ -35,15 +35,20 @@ def test_library_exports_every_declared_symbol():
     missing = [n for n in _declared() if not hasattr(lib, n)]
     assert not missing, f"declared in the header but not exported: {missing}"
     lib.pyi_abi_version.restype = C.c_int
-    assert lib.pyi_abi_version() == 1
+    assert lib.pyi_abi_version() == 2
 
 
 def test_ctypes_mirror_matches_header_layout():
     abi = importlib.import_module("pangeo-pyinterp_b200._abi")
     # pyi_axis_desc: 2 x i32, i64, 2 x i32, 5 x 8-byte unions, f64, i64, pointer
     assert C.sizeof(abi.AxisDesc) == 4 + 4 + 8 + 4 + 4 + 5 * 8 + 8 + 8 + 8
-    assert C.sizeof(abi.GeometricConfig) == 6 * 4
-    assert C.sizeof(abi.WindowedConfig) == 6 * 4
+    assert C.sizeof(abi.GeometricConfig) == 7 * 4
+    assert C.sizeof(abi.WindowedConfig) == 7 * 4
+    assert C.sizeof(abi.WindowedNdConfig) == 10 * 4
+    # value_mode is the LAST field of every configuration POD: the oracle's
+    # checkers (orc_abi.h) read the same structs and ignore it
+    for pod in (abi.GeometricConfig, abi.WindowedConfig, abi.WindowedNdConfig):
+        assert pod._fields_[-1][0] == "value_mode"
 
 
 def test_axes_are_host_objects(port):
