@@ -440,6 +440,20 @@ def time_device(env, pyi, grid, coords, cfg, steps, warmup, sampler=None):
     return total_ms, kernel_ms, int(launches), finite
 
 
+def e2e_bound(n_gpus, gbs):
+    """Names the limiter of the host-fed path from the committed copy-only probe
+    (tools/pcie_probe.cu -> profiles/r2_pcie_probe.json: the best aggregate
+    GB/s of 16 B in + 8 B out per point with no kernel at this GPU count)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r2_pcie_probe.json")) as f:
+            probe = json.load(f)
+        e = probe["gpus"][str(n_gpus)]
+        return {"bound": e["bound"], "probe_ceiling_gbs": e["gbs"], "frac_of_probe": gbs / e["gbs"],
+                "probe_source": probe["source"]}
+    except Exception:
+        return {"bound": "pcie", "probe_ceiling_gbs": None, "frac_of_probe": None, "probe_source": None}
+
+
 def roofline_entry(workload, n, kernel_ms):
     peak, peak_src = peaks()
     bpp = BYTES_PER_POINT[workload]
@@ -501,38 +515,69 @@ def main():
     ms_per_step = total_ms / args.steps
     value = world * n * args.steps / (total_ms / 1e3) / 1e6
 
-    # end to end: HOST buffers -> public API (H2D + kernel + D2H per step)
-    ne = int(min(args.e2e_points, n))
-    hq = []
-    for c in coords:
-        h = torch.empty(ne, dtype=c.dtype, pin_memory=True)
-        h.copy_(c[:ne])
-        hq.append(h.numpy())
-    if nd >= 3:
-        hq[2] = hq[2].view("datetime64[ns]")
+    # end to end: HOST buffers -> public API (H2D + kernel + D2H per step).
+    # N > 1: ONE process (rank 0) hands ONE call of N x ne points to the library,
+    # which shards it over the N devices (pyi_dist_init) -- the shape of the
+    # reference's drop-in caller, one process whose parallel_for splits a call's
+    # points; the other ranks idle at the barrier.  `ranks` is the other way to
+    # feed N GPUs: every torchrun rank calling with its own ne points.
     api = {2: pyi.bivariate, 3: pyi.trivariate, 4: pyi.quadrivariate}[nd]
     method = WINDOWED.get(args.workload, "bilinear")
     grid._resident = True
+    ne = int(min(args.e2e_points if world == 1 else args.e2e_points / 2, n))
+    e2e_steps = max(3, min(args.steps, 10))
 
-    def time_e2e(host_arrays, steps):
+    def pinned_copy(count):
+        hq = []
+        for c in coords:
+            h = torch.empty(count, dtype=c.dtype, pin_memory=True)
+            h.copy_(c[:count])
+            hq.append(h.numpy())
+        if nd >= 3:
+            hq[2] = hq[2].view("datetime64[ns]")
+        return hq
+
+    def time_calls(host_arrays, steps, active=True):
+        """Wall clock of `steps` API calls between two barriers, max over ranks."""
         r = None
-        for _ in range(2):
-            r = api(grid, *host_arrays, method)
+        if active:
+            for _ in range(2):
+                r = api(grid, *host_arrays, method)
         env.barrier()
         t0 = time.perf_counter()
-        for _ in range(steps):
-            r = api(grid, *host_arrays, method)
-        torch.cuda.synchronize()
+        if active:
+            for _ in range(steps):
+                r = api(grid, *host_arrays, method)
+            torch.cuda.synchronize()
         dt = env.max_over_ranks(time.perf_counter() - t0)
-        return world * ne * steps / dt / 1e6, r
+        return dt, r
 
-    e2e_steps = max(3, min(args.steps, 10))
-    e2e_value, r = time_e2e(hq, e2e_steps)
-    h2d = sum(int(h.nbytes) for h in hq)
-    d2h = int(r.nbytes)
+    e2e_ranks = None
+    if world > 1:
+        hq = pinned_copy(ne)
+        dt, r = time_calls(hq, e2e_steps)
+        e2e_ranks = {"value": world * ne * e2e_steps / dt / 1e6, "unit": METRIC,
+                     "how": f"{world} torchrun ranks, each calling with its own {ne} points"}
+        del hq, r
+    total = ne * world
+    lead = rank == 0
+    if lead:
+        pyi.dist.init(world)
+        hq = pinned_copy(min(total, n))
+        total = hq[0].size
+    else:
+        hq = None
+    dt, r = time_calls(hq, e2e_steps, active=lead)
+    e2e_value = total * e2e_steps / dt / 1e6
+    h2d = sum(int(h.nbytes) for h in hq) if lead else 0
+    d2h = int(r.nbytes) if lead else 0
+    e2e_gbs = (h2d + d2h) * e2e_steps / dt / 1e9
     # the same call with plain (pageable) numpy inputs, as an unmodified caller passes them
-    pageable = [np.array(h, copy=True) for h in hq]
-    e2e_pageable, _ = time_e2e(pageable, e2e_steps)
+    pageable = [np.array(h, copy=True) for h in hq] if lead else None
+    dt, _ = time_calls(pageable, e2e_steps, active=lead)
+    e2e_pageable = total * e2e_steps / dt / 1e6
+    if lead:
+        pyi.dist.init(1)
     del pageable, hq, r, coords
     torch.cuda.empty_cache()
 
@@ -560,12 +605,16 @@ def main():
             "config": {"workload": workload_name(args.workload, n), "points_per_gpu": n,
                        "l2": "inputs (x, y, out streams) are far larger than L2; no flush needed",
                        "grid_broadcast_ms": bcast_ms, "finite_fraction": finite, "parity": parity,
-                       "e2e_points_per_step": ne, "kernel_ms_min": kernel_ms[0],
+                       "e2e_points_per_step": total, "kernel_ms_min": kernel_ms[0],
                        "kernel_ms_median": kernel_ms[len(kernel_ms) // 2]},
             "e2e": {"value": e2e_value, "unit": METRIC, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "steps": e2e_steps, "input": "page-locked host arrays",
+                    "steps": e2e_steps, "points_per_step": total, "input": "page-locked host arrays",
+                    "how": f"one process, one API call per step, sharded over {world} device(s) inside the C-ABI "
+                           "(pyi_dist_init)",
+                    "host_link_gbs": e2e_gbs, **e2e_bound(world, e2e_gbs),
                     "pageable": {"value": e2e_pageable, "unit": METRIC,
-                                 "input": "plain numpy arrays, staged through the library's pinned slots"}},
+                                 "input": "plain numpy arrays, staged through the library's pinned slots"},
+                    "ranks": e2e_ranks},
             "gpu_launches": int(launches),
             "roofline": roofline_entry(args.workload, n, kernel_ms),
             "clocks": clk.summary(),

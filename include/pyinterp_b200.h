@@ -352,6 +352,16 @@ int pyi_fill_multigrid(void *grid, int dtype, int64_t nx, int64_t ny,
 int pyi_format_bounds_error(const pyi_grid *grid, int axis, const void *coord,
                             char *buf, size_t len);
 
+/* TemporalAxis::coordinate_repr (math/temporal_axis.hpp:80-83,150-156;
+ * dateutils::datetime64_to_string / timedelta64_to_string,
+ * dateutils.hpp:729-812): the text the reference prints for an int64
+ * coordinate of a temporal axis -- ISO-8601 in the axis resolution
+ * (pyi_resolution) for datetime64, "<n> <unit>s" for timedelta64.  Used to
+ * build the bounds-error message of a temporal z axis.  Returns the length
+ * written (excluding NUL), -1 on a bad argument. */
+int pyi_format_temporal(int is_timedelta, int resolution, int64_t value,
+                        char *buf, size_t len);
+
 /* Number of kernel launches issued by this library in this process. */
 int64_t pyi_launch_count(void);
 

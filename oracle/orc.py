@@ -52,6 +52,7 @@ _SIG = {
                                   C.c_char_p, C.c_size_t]),
     "orc_univariate": (C.c_double, [C.c_int, _P, _P, C.c_int, C.c_double, C.c_int]),
     "orc_datetime_convert": (C.c_int, [C.c_int, C.c_int, C.c_int64, _P, _P, C.c_char_p, C.c_size_t]),
+    "orc_temporal_repr": (C.c_int, [C.c_int, C.c_int, C.c_int64, C.c_char_p, C.c_size_t]),
     "orc_fill_gauss_seidel": (C.c_int, [_P, C.c_int, C.c_int64, C.c_int64, C.c_int, C.c_int, C.c_uint64,
                                         C.c_double, C.c_double, C.c_int, C.POINTER(C.c_uint64),
                                         C.POINTER(C.c_double), C.c_char_p, C.c_size_t]),
@@ -254,6 +255,13 @@ class Oracle:
             raise OverflowError(msg.value.decode())
         assert st == 0, (st, msg.value)
         return out
+
+    def temporal_repr(self, value: int, unit: str, timedelta: bool = False) -> str:
+        """TemporalAxis::coordinate_repr: the reference's text of an int64 coordinate."""
+        buf = C.create_string_buffer(128)
+        n = self.lib.orc_temporal_repr(int(timedelta), _abi.RESOLUTIONS[unit], int(value), buf, 128)
+        assert n >= 0
+        return buf.value.decode()
 
     def _fill_args(self, grid):
         assert isinstance(grid, np.ndarray) and grid.ndim == 2 and grid.flags.c_contiguous

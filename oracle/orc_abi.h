@@ -111,6 +111,12 @@ double orc_univariate(int method, const double *xa, const double *ya, int n,
 int orc_datetime_convert(int src, int dst, int64_t n, const int64_t *in,
                          int64_t *out, char *msg, size_t msglen);
 
+/* TemporalAxis::coordinate_repr (math/temporal_axis.hpp:80-83,150-156;
+ * dateutils::datetime64_to_string / timedelta64_to_string,
+ * dateutils.hpp:729-812).  Returns the length written, -1 on a bad argument. */
+int orc_temporal_repr(int is_timedelta, int unit, int64_t value, char *buf,
+                      size_t len);
+
 /* fill::gauss_seidel (fill/gauss_seidel.hpp:166-211) and fill::multigrid
  * (fill/multi_grid.hpp:276-334) in place on a row-major (nx, ny) grid of dtype
  * PYI_F32 / PYI_F64.  first_guess: pyi_first_guess.  num_threads <= 0: all

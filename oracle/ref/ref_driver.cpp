@@ -1212,6 +1212,26 @@ extern "C" int orc_datetime_convert(int src, int dst, int64_t n,
   return PYI_OK;
 }
 
+// TemporalAxis::coordinate_repr (math/temporal_axis.hpp:80-83,150-156): the
+// reference's own dateutils::datetime64_to_string / timedelta64_to_string
+// (dateutils.hpp:729-812), which is all format_temporal forwards to.
+extern "C" int orc_temporal_repr(int is_timedelta, int unit, int64_t value, char* buf,
+                                 size_t len) {
+  static const char* units[] = {"Y",  "M",  "W",  "D",  "h",  "m", "s",
+                                "ms", "us", "ns", "ps", "fs", "as"};
+  if (unit < 0 || unit > 12 || !buf || len == 0) return -1;
+  try {
+    const ref::dateutils::DType d(std::string(is_timedelta ? "timedelta64[" : "datetime64[") +
+                                  units[unit] + "]");
+    const std::string s = is_timedelta ? ref::dateutils::timedelta64_to_string(value, d)
+                                       : ref::dateutils::datetime64_to_string(value, d);
+    set_err(buf, len, s.c_str());
+    return static_cast<int>(s.size());
+  } catch (const std::exception&) {
+    return -1;
+  }
+}
+
 // ---------------------------------------------------------------------------
 // fill::gauss_seidel / fill::multigrid (fill/gauss_seidel.hpp:166-211,
 // fill/multi_grid.hpp:276-334), the reference's own functions, in place on a

@@ -335,12 +335,15 @@ class TemporalAxis(Axis):
         return self.cast_to_int64(coordinates)
 
     def coordinate_repr(self, value: int) -> str:
-        """math/temporal_axis.hpp:80-83: ISO-8601 text in the axis resolution."""
-        if self._dtype.kind == "M":
-            return str(np.int64(value).view(self._dtype))
-        names = {"Y": "years", "M": "months", "W": "weeks", "D": "days", "h": "hours", "m": "minutes",
-                 "s": "seconds", "ms": "milliseconds", "us": "microseconds", "ns": "nanoseconds"}
-        return f"{int(value)} {names.get(np.datetime_data(self._dtype)[0], '')}".strip()
+        """math/temporal_axis.hpp:80-83: the reference's own text of a coordinate
+        (ISO-8601 in the axis resolution, ``"<n> <unit>s"`` for timedelta64),
+        formatted by the library (``pyi_format_temporal``)."""
+        buf = C.create_string_buffer(128)
+        n = _lib().pyi_format_temporal(int(self._dtype.kind == "m"),
+                                       _abi.RESOLUTIONS[np.datetime_data(self._dtype)[0]], int(value), buf, 128)
+        if n < 0:
+            raise ValueError(f"unsupported temporal dtype {self._dtype}")
+        return buf.value.decode()
 
 
 def convert_resolution(values, src: str, dst: str):

@@ -1535,6 +1535,108 @@ int pyi_fill_multigrid(void* grid, int dtype, int64_t nx, int64_t ny, const pyi_
   return fill_entry(true, grid, dtype, nx, ny, cfg, mem, iterations, max_residual, stream);
 }
 
+// TemporalAxis::coordinate_repr (math/temporal_axis.hpp:80-83,150-156) =
+// dateutils::datetime64_to_string / timedelta64_to_string
+// (dateutils.hpp:729-812): ISO-8601 text of an int64 in a numpy resolution.
+namespace {
+
+struct CivilDate {
+  long long year;
+  unsigned month, day;
+};
+
+// proleptic Gregorian date of a day count since 1970-01-01 (the era / day-of-era
+// decomposition the reference uses, dateutils.hpp:563-584)
+CivilDate civil_from_days(long long days) {
+  days += 719468;
+  const long long era = (days >= 0 ? days : days - 146096) / 146097;
+  const unsigned doe = static_cast<unsigned>(days - era * 146097);
+  const unsigned yoe = (doe - doe / 1460 + doe / 36524 - doe / 146096) / 365;
+  const unsigned doy = doe - (365 * yoe + yoe / 4 - yoe / 100);
+  const unsigned mp = (5 * doy + 2) / 153;
+  const unsigned day = doy - (153 * mp + 2) / 5 + 1;
+  const unsigned month = mp < 10 ? mp + 3 : mp - 9;
+  // the reference narrows the year to int (dateutils.hpp:580-582)
+  const int year = (static_cast<int>(yoe) + static_cast<int>(era) * 400) + (month <= 2 ? 1 : 0);
+  return {year, month, day};
+}
+
+// floor division / modulo by a positive divisor
+void floor_divmod(long long v, long long d, long long& q, long long& r) {
+  q = v / d;
+  r = v % d;
+  if (r < 0) {
+    r += d;
+    q -= 1;
+  }
+}
+
+std::string two(unsigned v) {
+  char b[16];
+  std::snprintf(b, sizeof(b), "%02u", v);
+  return b;
+}
+
+std::string date_text(const CivilDate& d) {
+  return std::to_string(d.year) + "-" + two(d.month) + "-" + two(d.day);
+}
+
+std::string temporal_text(bool timedelta, int res, long long value) {
+  static const char* plural[] = {"years",        "months",       "weeks",       "days",        "hours",
+                                 "minutes",      "seconds",      "milliseconds", "microseconds", "nanoseconds",
+                                 "picoseconds",  "femtoseconds", "attoseconds"};
+  if (timedelta) return std::to_string(value) + " " + plural[res];
+  long long q = 0, r = 0;
+  switch (res) {
+    case PYI_RES_YEAR:
+      return std::to_string(static_cast<int>(1970 + value));
+    case PYI_RES_MONTH: {
+      floor_divmod(value, 12, q, r);
+      return std::to_string(static_cast<int>(1970 + q)) + "-" + two(static_cast<unsigned>(r + 1));
+    }
+    case PYI_RES_WEEK:
+      return date_text(civil_from_days(value * 7));
+    case PYI_RES_DAY:
+      return date_text(civil_from_days(value));
+    case PYI_RES_HOUR: {
+      floor_divmod(value, 24, q, r);
+      return date_text(civil_from_days(q)) + "T" + two(static_cast<unsigned>(r));
+    }
+    case PYI_RES_MINUTE: {
+      floor_divmod(value, 1440, q, r);
+      return date_text(civil_from_days(q)) + "T" + two(static_cast<unsigned>(r / 60)) + ":" +
+             two(static_cast<unsigned>(r % 60));
+    }
+    default: {
+      // seconds and below: value = seconds * 10^digits + fraction (floored)
+      const int digits = 3 * (res - PYI_RES_SECOND);
+      long long magnitude = 1;
+      for (int k = 0; k < digits; ++k) magnitude *= 10;
+      long long sec = 0, frac = 0, days = 0, in_day = 0;
+      floor_divmod(value, magnitude, sec, frac);
+      floor_divmod(sec, 86400, days, in_day);
+      std::string out = date_text(civil_from_days(days)) + "T" + two(static_cast<unsigned>(in_day / 3600)) +
+                        ":" + two(static_cast<unsigned>(in_day % 3600 / 60)) + ":" +
+                        two(static_cast<unsigned>(in_day % 60));
+      if (digits > 0) {
+        char b[32];
+        std::snprintf(b, sizeof(b), "%0*lld", digits, frac);
+        out += std::string(".") + b;
+      }
+      return out;
+    }
+  }
+}
+
+}  // namespace
+
+int pyi_format_temporal(int is_timedelta, int resolution, int64_t value, char* buf, size_t len) {
+  if (!buf || len == 0 || resolution < PYI_RES_YEAR || resolution > PYI_RES_ATTOSECOND) return -1;
+  const std::string s = temporal_text(is_timedelta != 0, resolution, value);
+  std::snprintf(buf, len, "%s", s.c_str());
+  return static_cast<int>(s.size());
+}
+
 // "{coord} is out of bounds for axis {label} [{min}, ..., {max}]"
 // (pybind/grid.hpp:362-371).  Doubles are printed like std::format("{}"):
 // shortest round-trip digits via std::to_chars.  int64 coordinates are printed

@@ -10,6 +10,30 @@ from __future__ import annotations
 
 import numpy as np
 
+from . import _abi
+
+
+def init(n_gpus: int = 0) -> int:
+    """Single-process multi-GPU: from now on every host-array call of
+    ``bivariate`` / ``trivariate`` / ``quadrivariate`` is split into contiguous
+    shards over the first ``n_gpus`` CUDA devices (0: all of them) INSIDE the
+    one C-ABI call (``pyi_dist_init``): the grid handle is replicated per
+    device over NVLink peer copies, each shard runs its own pipelined copies
+    and kernels, the result array and the bounds-error report are those of a
+    one-device call.  This is the drop-in shape of the reference, whose
+    ``parallel_for`` splits one call's points over the workers of one process
+    (cxx/include/pyinterp/parallel_for.hpp:30-78).  Returns the device count in
+    effect."""
+    n = int(_abi.load().pyi_dist_init(int(n_gpus)))
+    if n <= 0:
+        raise _abi.PyiError("dist.init: no CUDA device (pyinterp_b200 has no CPU fallback)")
+    return n
+
+
+def size() -> int:
+    """Device count host-array calls are sharded over (1 until ``init``)."""
+    return int(_abi.load().pyi_dist_size())
+
 
 def shard_bounds(n: int, world_size: int, rank: int) -> tuple[int, int]:
     """[start, end) of `rank`: n // W points each, the first n % W ranks take

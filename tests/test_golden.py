@@ -113,3 +113,32 @@ def test_reference_vectors(orc_any, name):
     d = gu.load_vectors(name)
     got = gu.run_case_on_oracle(orc_any, name, d)
     gu.compare(name, got, d, exact=True)
+
+
+def test_temporal_repr_golden(orc_any):
+    """TemporalAxis::coordinate_repr (math/temporal_axis.hpp:80-83) texts of the
+    reference build, committed as tests/golden/ref_temporal_repr.json."""
+    cases = json.load(open(os.path.join(HERE, "golden", "ref_temporal_repr.json")))["cases"]
+    assert len(cases) > 500
+    for c in cases:
+        assert orc_any.temporal_repr(c["value"], c["unit"], bool(c["timedelta"])) == c["text"], c
+
+
+def test_temporal_repr_product_matches_golden():
+    """The product's formatter (pyi_format_temporal: host logic of the C-ABI,
+    no kernel, no GPU needed) against the same golden texts, and against
+    numpy's own ISO text where numpy prints the same form."""
+    import importlib
+    pyi = importlib.import_module("pangeo-pyinterp_b200")
+    cases = json.load(open(os.path.join(HERE, "golden", "ref_temporal_repr.json")))["cases"]
+    axes = {}
+    for c in cases:
+        kind = "timedelta64" if c["timedelta"] else "datetime64"
+        key = (kind, c["unit"])
+        if key not in axes:
+            pts = np.arange(3).astype(f"{kind}[{c['unit']}]")
+            axes[key] = pyi.TemporalAxis(pts)
+        assert axes[key].coordinate_repr(c["value"]) == c["text"], c
+    ax = axes[("datetime64", "ns")]
+    v = int(np.datetime64("2021-03-04T05:06:07.123456789", "ns").astype(np.int64))
+    assert ax.coordinate_repr(v) == "2021-03-04T05:06:07.123456789" == str(np.datetime64(v, "ns"))

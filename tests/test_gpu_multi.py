@@ -1,0 +1,190 @@
+"""Single-call multi-GPU sharding (pyi_dist_init) and re-entrancy of the host
+path.  The sharding tests need two CUDA devices (run with `gpurun --gpus 2`);
+the threading tests also run on one.
+
+Reference behaviour mirrored: parallel_for (cxx/include/pyinterp/
+parallel_for.hpp:30-78) splits one call's points into contiguous chunks over
+the workers of ONE process and reports the first failing chunk's error; the
+drivers release the GIL (src/pybind/geometric/bivariate_geometric.cpp:36), so
+concurrent calls from several Python threads are legal."""
+import threading
+import time
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _grids(pyi, synthetic):
+    lon, lat = synthetic.lon_axis_values(), synthetic.lat_axis_values()
+    g2 = synthetic.field(lon, lat)
+    g2[::37, ::11] = np.nan
+    t = synthetic.time_axis_values(24)
+    g3 = synthetic.field(lon, lat, nz=24, dtype="float32", noise=0.0)
+    grid2 = pyi.Grid(pyi.Axis(lon, period=360.0), pyi.Axis(lat), g2, resident=True)
+    grid3 = pyi.Grid(pyi.Axis(lon, period=360.0), pyi.Axis(lat), pyi.TemporalAxis(t), g3, resident=True)
+    return grid2, grid3, t
+
+
+@pytest.fixture
+def two_devices(pyi):
+    if pyi.device_count() < 2:
+        pytest.skip("needs two CUDA devices")
+    yield
+    pyi.dist.init(1)
+
+
+def test_sharded_call_equals_one_device(pyi, synthetic, two_devices):
+    """One call sharded over every device == the same call on one device, bit
+    for bit: bilinear (both value modes), bicubic, trivariate, pageable and
+    page-locked inputs, a size that does not divide evenly."""
+    import torch
+    grid2, grid3, t = _grids(pyi, synthetic)
+    n = 9_000_007
+    x, y, z = synthetic.queries(n, 77, ndim=3, time_values=t)
+    zz = z.view("datetime64[ns]")
+    calls = {
+        "bilinear": lambda: pyi.bivariate(grid2, x, y),
+        "bilinear_exact": lambda: pyi.core.bivariate(
+            grid2, x, y, pyi.geometric.Bivariate.bilinear().with_value_mode("exact")),
+        "bicubic": lambda: pyi.bivariate(grid2, x, y, "bicubic"),
+        "nearest": lambda: pyi.bivariate(grid2, x, y, "nearest"),
+        "trivariate": lambda: pyi.trivariate(grid3, x, y, zz),
+        "bicubic3d": lambda: pyi.trivariate(grid3, x[:2_500_000], y[:2_500_000], zz[:2_500_000], "bicubic"),
+    }
+    assert pyi.dist.size() == 1
+    want = {k: f() for k, f in calls.items()}
+    g = pyi.dist.init(0)
+    assert g == pyi.device_count() == pyi.dist.size()
+    before = pyi.launch_count()
+    for k, f in calls.items():
+        got = f()
+        assert np.array_equal(got, want[k], equal_nan=True), k
+    assert pyi.launch_count() - before >= 2 * len(calls)
+    # page-locked inputs take the direct-DMA path
+    xp, yp = (torch.from_numpy(a).pin_memory().numpy() for a in (x, y))
+    assert np.array_equal(pyi.bivariate(grid2, xp, yp), want["bilinear"], equal_nan=True)
+    # a refreshed grid reaches every replica
+    arr = grid2.array
+    arr[100:110, 200:210] += 1.0
+    grid2.refresh()
+    got = pyi.bivariate(grid2, x, y)
+    pyi.dist.init(1)
+    assert np.array_equal(got, pyi.bivariate(grid2, x, y), equal_nan=True)
+    assert not np.array_equal(got, want["bilinear"], equal_nan=True)
+
+
+def test_sharded_bounds_error_reports_the_same_point(pyi, synthetic, two_devices):
+    """The first offending point is the global minimum over the shards: put
+    one in the LAST shard only, then an earlier one in the first."""
+    grid2, grid3, t = _grids(pyi, synthetic)
+    n = 8_400_000
+    x = np.full(n, 10.0)
+    y = np.full(n, 0.0)
+    y[n - 5] = 95.0
+    cfg = pyi.geometric.Bivariate.bilinear().with_bounds_error(True)
+    wcfg = pyi.windowed.Bivariate.bicubic().with_bounds_error(True)
+    msgs = {}
+    for g in (1, 0):
+        pyi.dist.init(g)
+        with pytest.raises(ValueError) as ei:
+            pyi.core.bivariate(grid2, x, y, cfg)
+        msgs[g] = str(ei.value)
+        with pytest.raises(IndexError) as ei:
+            pyi.core.bivariate(grid2, x, y, wcfg)
+        assert str(ei.value) == msgs[g]
+    assert msgs[0] == msgs[1] and msgs[0].startswith("95 is out of bounds for axis y")
+    y[7] = -97.0
+    pyi.dist.init(0)
+    with pytest.raises(ValueError) as ei:
+        pyi.core.bivariate(grid2, x, y, cfg)
+    assert str(ei.value).startswith("-97 is out of bounds for axis y")
+
+
+def _serial_and_threaded(pyi, jobs, n_threads):
+    want = [f() for f in jobs]  # also warms every workspace / replica
+    for f in jobs:  # leaves free page-locked result blocks in torch's host cache for the timed passes
+        f()
+    t0 = time.perf_counter()
+    for f in jobs:
+        f()
+    serial = time.perf_counter() - t0
+    got = [None] * len(jobs)
+
+    def worker(k):
+        for j in range(k, len(jobs), n_threads):
+            got[j] = jobs[j]()
+
+    def run_threads():
+        threads = [threading.Thread(target=worker, args=(k,)) for k in range(n_threads)]
+        t0 = time.perf_counter()
+        for th in threads:
+            th.start()
+        for th in threads:
+            th.join()
+        return time.perf_counter() - t0
+
+    run_threads()  # concurrent calls check out more workspaces: allocate them outside the timed pass
+    threaded = run_threads()
+    for a, b in zip(got, want):
+        assert np.array_equal(a, b, equal_nan=True)
+    return serial, threaded
+
+
+def test_concurrent_calls_from_python_threads(pyi, synthetic):
+    """Four Python threads, interleaved bivariate / trivariate host calls on
+    the same grids: results bit-identical to the serial run (the host path is
+    re-entrant: per-call workspaces, no call-long lock)."""
+    grid2, grid3, t = _grids(pyi, synthetic)
+    n = 3_000_000
+    qs = [synthetic.queries(n, 200 + k, ndim=3, time_values=t) for k in range(4)]
+    jobs = []
+    for k in range(8):
+        x, y, z = qs[k % 4]
+        if k % 2 == 0:
+            jobs.append(lambda x=x, y=y: pyi.bivariate(grid2, x, y))
+        else:
+            jobs.append(lambda x=x, y=y, z=z: pyi.trivariate(grid3, x, y, z.view("datetime64[ns]")))
+    serial, threaded = _serial_and_threaded(pyi, jobs, 4)
+    print(f"serial {serial:.3f} s, 4 threads {threaded:.3f} s")
+
+
+def test_threads_on_two_devices_overlap(pyi, synthetic, two_devices):
+    """Four threads x interleaved bivariate / trivariate calls on two devices
+    (two grids per device): bit-identical to serial and faster than 0.6 x
+    serial (the old global workspace serialised them and thrashed its
+    allocations on every device switch)."""
+    import torch
+    pyi.dist.init(1)
+    lon, lat = synthetic.lon_axis_values(), synthetic.lat_axis_values()
+    t = synthetic.time_axis_values(24)
+    g2 = synthetic.field(lon, lat)
+    g3 = synthetic.field(lon, lat, nz=24, dtype="float32", noise=0.0)
+    grids = []
+    for d in (0, 1):
+        with torch.cuda.device(d):
+            grids.append((pyi.Grid(pyi.Axis(lon, period=360.0), pyi.Axis(lat), g2, resident=True),
+                          pyi.Grid(pyi.Axis(lon, period=360.0), pyi.Axis(lat), pyi.TemporalAxis(t), g3,
+                                   resident=True)))
+    n = 6_000_000
+    qs = []
+    for k in range(4):
+        x, y, z = synthetic.queries(n, 300 + k, ndim=3, time_values=t)
+        qs.append(tuple(torch.from_numpy(a).pin_memory().numpy() for a in (x, y, z)))
+    jobs = []
+    for k in range(16):
+        x, y, z = qs[k % 4]
+        d = k % 2
+        if (k // 2) % 2 == 0:
+            def job(x=x, y=y, d=d):
+                with torch.cuda.device(d):
+                    return pyi.bivariate(grids[d][0], x, y)
+        else:
+            def job(x=x, y=y, z=z, d=d):
+                with torch.cuda.device(d):
+                    return pyi.trivariate(grids[d][1], x, y, z.view("datetime64[ns]"))
+        jobs.append(job)
+    serial, threaded = _serial_and_threaded(pyi, jobs, 4)
+    print(f"serial {serial:.3f} s, 4 threads on 2 devices {threaded:.3f} s")
+    assert threaded < 0.6 * serial, (serial, threaded)
