@@ -144,7 +144,7 @@ struct VecIO<4> {
 
 // XM: 1 general / 2 exact nodes (x is always regular); YM: 0 irregular,
 // 1 general regular, 2 exact-nodes regular.  PTS consecutive points per thread.
-template <bool PER, int XM, int YM, int PTS, int MINB>
+template <bool PER, int XM, int YM, int PTS, int MINB, bool PREFETCH>
 __global__ void __launch_bounds__(kFastThreads, MINB)
 bilinear2d_tol_kernel(const __grid_constant__ GeoParams p) {
   __shared__ double s_points[YM == 0 ? kFastMaxIrregular : 1];
@@ -167,13 +167,26 @@ bilinear2d_tol_kernel(const __grid_constant__ GeoParams p) {
   const unsigned groups = static_cast<unsigned>(p.n / PTS);  // the launcher keeps n below 2^32
   const unsigned stride = gridDim.x * blockDim.x;
   double* __restrict__ out = static_cast<double*>(p.out);
-  for (unsigned g = blockIdx.x * blockDim.x + threadIdx.x; g < groups; g += stride) {
+  // software pipeline: the coordinates of the next iteration are in flight while
+  // this one is computed (ncu, round 2: 52 % of the stall samples sat on the
+  // first use of x, the DRAM latency of the stream loads)
+  unsigned g = blockIdx.x * blockDim.x + threadIdx.x;
+  double x[PTS], y[PTS];
+  if (g < groups) {
+    VecIO<PTS>::load(p.x + static_cast<size_t>(g) * PTS, x);
+    VecIO<PTS>::load(p.y + static_cast<size_t>(g) * PTS, y);
+  }
+  while (g < groups) {
     const size_t base = static_cast<size_t>(g) * PTS;
-    double x[PTS], y[PTS], t[PTS], u[PTS], o[PTS];
+    const unsigned gn = g + stride;  // groups <= 2^30: no wrap
+    double xn[PTS], yn[PTS];
+    if (PREFETCH && gn < groups) {
+      VecIO<PTS>::load(p.x + static_cast<size_t>(gn) * PTS, xn);
+      VecIO<PTS>::load(p.y + static_cast<size_t>(gn) * PTS, yn);
+    }
+    double t[PTS], u[PTS], o[PTS];
     long long cell[PTS];
     bool safe[PTS];
-    VecIO<PTS>::load(p.x + base, x);
-    VecIO<PTS>::load(p.y + base, y);
     bool all_safe = true;
 #pragma unroll
     for (int i = 0; i < PTS; ++i) {
@@ -225,6 +238,17 @@ bilinear2d_tol_kernel(const __grid_constant__ GeoParams p) {
       }
     }
     VecIO<PTS>::store(out + base, o);
+    g = gn;
+    if (PREFETCH) {
+#pragma unroll
+      for (int i = 0; i < PTS; ++i) {
+        x[i] = xn[i];
+        y[i] = yn[i];
+      }
+    } else if (g < groups) {
+      VecIO<PTS>::load(p.x + static_cast<size_t>(g) * PTS, x);
+      VecIO<PTS>::load(p.y + static_cast<size_t>(g) * PTS, y);
+    }
   }
   // tail: n % PTS points
   if (blockIdx.x == 0 && threadIdx.x < static_cast<unsigned>(p.n % PTS)) {
@@ -240,15 +264,17 @@ static int bilinear_default_mode() {
   return (e != nullptr && e[0] == 'e') ? PYI_VALUES_EXACT : PYI_VALUES_TOLERANCE;
 }
 
-// Tuning variant: PYI_TOL_VARIANT = <points per thread: 2|4><min blocks per SM: 2..6>
-// (read per launch so that one process can sweep them)
-static void tol2d_variant(int& pts, int& minb) {
-  pts = 2;  // round-2 sweep on B200 (profiles/r2_k1_sweep.txt): 2 points x 3 blocks per SM
+// Tuning variant: PYI_TOL_VARIANT = <points per thread: 2|4><min blocks per SM: 2..5>[n]
+// ("n": no register prefetch); read per launch so that one process can sweep them
+static void tol2d_variant(int& pts, int& minb, bool& prefetch) {
+  pts = 2;  // round-2 sweeps on B200 (profiles/r2_k1_sweep*.txt)
   minb = 3;
+  prefetch = true;
   const char* e = std::getenv("PYI_TOL_VARIANT");
-  if (e && (e[0] == '2' || e[0] == '4') && e[1] >= '2' && e[1] <= '6') {
+  if (e && (e[0] == '2' || e[0] == '4') && e[1] >= '2' && e[1] <= '5') {
     pts = e[0] - '0';
     minb = e[1] - '0';
+    prefetch = e[2] != 'n';
   }
 }
 
@@ -267,27 +293,43 @@ static bool tol2d_eligible(const GeoParams& p) {
 template <bool PER, int XM, int YM>
 static void launch_tol2d_v(const GeoParams& p, cudaStream_t stream) {
   int pts, minb;
-  tol2d_variant(pts, minb);
+  bool prefetch;
+  tol2d_variant(pts, minb, prefetch);
+  // the tuning variants exist for the benchmark configurations only (periodic
+  // exact-node x; exact-node or irregular y); every other axis combination is
+  // compiled once, with the default variant
+  constexpr bool kSweep = PER && XM == 2 && YM != 1;
+  if (!kSweep) {
+    pts = 2;
+    minb = 3;
+    prefetch = true;
+  }
   const int blocks = grid_for((p.n + pts - 1) / pts, kFastThreads, minb);
-#define PYI_LAUNCH(P, B) bilinear2d_tol_kernel<PER, XM, YM, P, B><<<blocks, kFastThreads, 0, stream>>>(p)
+  if constexpr (!kSweep) {
+    bilinear2d_tol_kernel<PER, XM, YM, 2, 3, true><<<blocks, kFastThreads, 0, stream>>>(p);
+    return;
+  } else {
+#define PYI_LAUNCH(P, B)                                                                        \
+  do {                                                                                          \
+    if (prefetch) bilinear2d_tol_kernel<PER, XM, YM, P, B, true><<<blocks, kFastThreads, 0, stream>>>(p); \
+    else bilinear2d_tol_kernel<PER, XM, YM, P, B, false><<<blocks, kFastThreads, 0, stream>>>(p);         \
+  } while (0)
   if (pts == 2) {
     switch (minb) {
       case 2: PYI_LAUNCH(2, 2); break;
       case 3: PYI_LAUNCH(2, 3); break;
       case 4: PYI_LAUNCH(2, 4); break;
-      case 5: PYI_LAUNCH(2, 5); break;
-      default: PYI_LAUNCH(2, 6); break;
+      default: PYI_LAUNCH(2, 5); break;
     }
   } else {
     switch (minb) {
       case 2: PYI_LAUNCH(4, 2); break;
       case 3: PYI_LAUNCH(4, 3); break;
-      case 4: PYI_LAUNCH(4, 4); break;
-      case 5: PYI_LAUNCH(4, 5); break;
-      default: PYI_LAUNCH(4, 6); break;
+      default: PYI_LAUNCH(4, 4); break;
     }
   }
 #undef PYI_LAUNCH
+  }
 }
 
 template <bool PER>

@@ -578,3 +578,127 @@ def test_cuda_array_interface_inputs(pyi):
     assert np.array_equal(got.cpu().numpy(), pyi.bivariate(host_grid, x, y, "c_spline"), equal_nan=True)
     idx = grid.x.find_indexes(dx)
     assert idx.is_cuda and np.array_equal(idx.cpu().numpy(), host_grid.x.find_indexes(x))
+
+
+@pytest.mark.parametrize("unit", ["ns", "s", "h", "D", "W"])
+def test_temporal_bounds_error_message_is_the_reference_text(pyi, orc_best, unit):
+    """The whole bounds-error message of a temporal z axis: coordinate and axis
+    limits printed by TemporalAxis::coordinate_repr (math/temporal_axis.hpp:80-83,
+    dateutils.hpp:729-772) in the axis resolution, compared with the reference
+    build's own strings (the geometric driver, pybind/grid.hpp:362-371,376-381,
+    and the windowed one)."""
+    lon, lat = np.arange(36) * 10.0, -85.0 + np.arange(18) * 10.0
+    t = (np.datetime64("2021-01-04", unit) + np.arange(8) * np.timedelta64(3, unit)).astype(f"datetime64[{unit}]")
+    g = np.random.default_rng(2).normal(size=(36, 18, 8))
+    grid = pyi.Grid(pyi.Axis(lon, period=360.0), pyi.Axis(lat), pyi.TemporalAxis(t), g)
+    ti = t.astype(np.int64)
+    x, y = np.array([5.0, 15.0, 25.0]), np.array([0.0, 10.0, -20.0])
+    z = np.array([ti[2], ti[-1] + 5, ti[0] - 1], dtype=np.int64).view(f"datetime64[{unit}]")
+    want = (f"{orc_best.temporal_repr(int(ti[-1]) + 5, unit)} is out of bounds for axis z "
+            f"[{orc_best.temporal_repr(int(ti[0]), unit)}, ..., {orc_best.temporal_repr(int(ti[-1]), unit)}]")
+    with pytest.raises(ValueError) as ei:
+        pyi.trivariate(grid, x, y, z, bounds_error=True)
+    assert str(ei.value) == want
+    with pytest.raises(IndexError) as ei:
+        pyi.trivariate(grid, x, y, z, "bicubic", bounds_error=True, half_window_size_x=2,
+                       half_window_size_y=2, boundary_mode="shrink")
+    assert str(ei.value) == want
+    # numpy prints the same ISO text for these resolutions
+    assert orc_best.temporal_repr(int(ti[0]), unit) == str(t[0])
+    # a coarser-resolution query array is converted to the axis resolution first
+    assert grid.z.coordinate_repr(int(ti[3])) == str(t[3])
+
+
+@pytest.mark.parametrize("method", ["bilinear", "bicubic"])
+def test_offset_axes_keep_the_bit_identical_path(pyi, orc_best, method):
+    """Axes with a large |coordinate| / step ratio (start = 1e7, step = 0.01):
+    the tolerance kernels assume nodes that are uniform to rounding, which such
+    axes are not (ulp(1e7) / 0.01 = 1.9e-7 relative spacing error), so the
+    library must route them through the bit-identical kernels in the DEFAULT
+    value mode (bicubic weights kernel: max |coordinate| / |step| < 2^16;
+    bilinear tolerance kernel: < 2^26).  A field crossing zero makes any
+    derivative error visible."""
+    xs = 1.0e7 + np.arange(400) * 0.01
+    ys = -3.0e6 + np.arange(300) * 0.01
+    rng = np.random.default_rng(12)
+    g = np.sin(np.arange(400) * 0.3)[:, None] * np.cos(np.arange(300) * 0.2)[None, :] * 50.0 + rng.normal(size=(400, 300))
+    grid = pyi.Grid(pyi.Axis(xs), pyi.Axis(ys), g)
+    cax = [orc_best.axis(xs), orc_best.axis(ys)]
+    n = 200_000
+    x = rng.uniform(xs[0] - 0.05, xs[-1] + 0.05, n)
+    y = rng.uniform(ys[0] - 0.05, ys[-1] + 0.05, n)
+    x[::17] = xs[rng.integers(0, xs.size, x[::17].size)]
+    if method == "bilinear":
+        want, _ = orc_best.geometric(cax, g, x, y, method=0, num_threads=0)
+    else:
+        want, _ = orc_best.windowed2d(cax, g, x, y, num_threads=0, stateless=True)
+    got = pyi.bivariate(grid, x, y, method)
+    assert np.isfinite(want).mean() > 0.5
+    assert np.array_equal(got, want, equal_nan=True)
+
+
+@pytest.mark.parametrize("kind", ["step_0p1", "offset_1000", "lon_0p1_periodic", "lon_180_0p05"])
+def test_bilinear_tolerance_kernel_on_inexact_nodes(pyi, orc_best, kind):
+    """The general variant of the tolerance kernel (nodes start + k * step that
+    are NOT exactly representable, spacings that differ from `step` by
+    rounding): indexes identical, values within 1e-12 of the reference on a
+    rough field with zero crossings, scaled by the cell's own magnitude."""
+    rng = np.random.default_rng(5)
+    per = None
+    if kind == "step_0p1":
+        xs, ys = np.arange(900) * 0.1 + 0.03, -40.0 + np.arange(700) * 0.1
+    elif kind == "offset_1000":
+        xs, ys = 1000.3 + np.arange(500) * 0.1, 5000.7 + np.arange(400) * 0.3
+    elif kind == "lon_0p1_periodic":
+        xs, ys, per = np.arange(3600) * 0.1, -89.95 + np.arange(1800) * 0.1, 360.0
+    else:
+        xs, ys, per = -180.0 + np.arange(7200) * 0.05, -60.0 + np.arange(500) * 0.05, 360.0
+    g = rng.normal(size=(xs.size, ys.size)) * 50.0
+    g[::31, ::7] = np.nan
+    grid = pyi.Grid(pyi.Axis(xs, period=per), pyi.Axis(ys), g)
+    cax = [orc_best.axis(xs, period=per), orc_best.axis(ys)]
+    n = 500_000
+    lo, hi = (xs[0] - 400.0, xs[-1] + 400.0) if per else (xs[0] - 1.0, xs[-1] + 1.0)
+    x = rng.uniform(lo, hi, n)
+    y = rng.uniform(ys[0] - 0.5, ys[-1] + 0.5, n)
+    x[::19] = xs[rng.integers(0, xs.size, x[::19].size)]
+    y[3::23] = ys[rng.integers(0, ys.size, y[3::23].size)]
+    x[5::1009] = rng.uniform(-1e9, 1e9, x[5::1009].size)
+    want, _ = orc_best.geometric(cax, g, x, y, method=0, num_threads=0)
+    tol = pyi.core.bivariate(grid, x, y, pyi.geometric.Bivariate.bilinear().with_value_mode("tolerance"))
+    exact = pyi.core.bivariate(grid, x, y, pyi.geometric.Bivariate.bilinear().with_value_mode("exact"))
+    assert np.array_equal(exact, want, equal_nan=True)
+    assert np.array_equal(np.isnan(tol), np.isnan(want))
+    m = ~np.isnan(want)
+    assert m.mean() > 0.3
+    err = np.abs(tol[m] - want[m])
+    assert np.all(err <= 1e-12 * np.maximum(np.abs(want[m]), 50.0)), err.max()
+    # rounding only: a few ulp of the cell's values (|q| up to ~250)
+    assert err.max() < 5e-13, err.max()
+
+
+def test_bicubic_reference_order_vs_stateless_near_the_seam(pyi, orc_best):
+    """the reference keeps a per-thread window cache whose
+    contents depend on the previous point (cache_loader.hpp:110-133,194-203);
+    the product is stateless.  Quantify the gap where it can exist -- queries
+    hopping across the 0 / 360 seam -- between the reference-order run (one
+    thread, points in order) and the stateless form, and hold the product to
+    the stateless form."""
+    lon, lat = np.arange(144) * 2.5, -88.75 + np.arange(72) * 2.5
+    g = pyi.synthetic.field(lon, lat)
+    cax = [orc_best.axis(lon, period=360.0), orc_best.axis(lat)]
+    rng = np.random.default_rng(8)
+    n = 60_000
+    x = np.where(rng.random(n) < 0.5, rng.uniform(350.0, 360.0, n), rng.uniform(0.0, 10.0, n))
+    x[::3] += 360.0 * rng.integers(-2, 3, x[::3].size)
+    y = rng.uniform(-80.0, 80.0, n)
+    stateless, _ = orc_best.windowed2d(cax, g, x, y, num_threads=1, stateless=True)
+    grid = pyi.Grid(pyi.Axis(lon, period=360.0), pyi.Axis(lat), g)
+    got = pyi.core.bivariate(grid, x, y, pyi.windowed.Bivariate.bicubic().with_value_mode("exact"))
+    assert np.array_equal(got, stateless, equal_nan=True)
+    if orc_best.kind == "reference":
+        stateful, _ = orc_best.windowed2d(cax, g, x, y, num_threads=1, stateless=False)
+        assert np.array_equal(np.isnan(stateful), np.isnan(stateless))
+        gap = np.nanmax(np.abs(stateful - stateless))
+        print(f"max |reference-order - stateless| near the seam: {gap:.3e}")
+        assert gap <= 1e-12
