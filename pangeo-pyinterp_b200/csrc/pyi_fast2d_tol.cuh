@@ -18,7 +18,11 @@
 //     (math/axis.hpp:745-766, ascending axis).  Everything else -- a point on a
 //     node, a wrong guess, NaN, a coordinate outside the axis -- leaves the hot
 //     path: beyond the ends of a non-periodic axis the result is NaN, the rest is
-//     re-done by the generic code (slow_point, pyi_fast2d.cuh).
+//     queued (a device counter + index list per launch) and re-done by the generic
+//     code in tol2d_redo_kernel -- the hot loop has no call.  When more than 2^20
+//     points of a launch are queued (e.g. every query exactly on a node) the
+//     bit-identical kernel of pyi_fast2d.cuh, launched behind the queue, recomputes
+//     the whole launch; it returns at once otherwise.
 //   * "exact nodes" axes (DAxis::tol_ok == 2, e.g. every multiple-of-2^-k grid
 //     such as the 0.25 degree one): the host has checked that fma(k, step, start)
 //     IS the reference's node for every k and that every spacing, the periodic
@@ -229,12 +233,17 @@ bilinear2d_tol_kernel(const __grid_constant__ GeoParams p) {
       for (int i = 0; i < PTS; ++i) {
         if (safe[i]) continue;
         // a finite coordinate beyond the ends of an axis that does not wrap is
-        // NaN (see beyond_ends); with bounds_error the generic code reports it
+        // NaN (see beyond_ends); with bounds_error the generic code reports it.
+        // Everything else is queued for the redo kernel: no call in this loop.
         bool far = false;
         if (!p.bounds_error && sane(x[i]) && sane(y[i])) {
           far = beyond_ends(ay, y[i]) || (!PER && beyond_ends(ax, x[i]));
         }
-        o[i] = far ? RT<double>::nan() : slow_point<double>(p, x[i], y[i], static_cast<long long>(base) + i);
+        if (!far) {
+          const unsigned slot = atomicAdd(p.queue, 1u);
+          if (slot < p.queue_cap) p.queue[1 + slot] = static_cast<unsigned>(base + i);
+        }
+        o[i] = RT<double>::nan();
       }
     }
     VecIO<PTS>::store(out + base, o);
@@ -250,9 +259,23 @@ bilinear2d_tol_kernel(const __grid_constant__ GeoParams p) {
       VecIO<PTS>::load(p.y + static_cast<size_t>(g) * PTS, y);
     }
   }
-  // tail: n % PTS points
-  if (blockIdx.x == 0 && threadIdx.x < static_cast<unsigned>(p.n % PTS)) {
-    const long long k = static_cast<long long>(groups) * PTS + threadIdx.x;
+}
+
+// The points the hot kernel queued (on a node, NaN, far-away longitudes ...)
+// and the n % pts tail, through the generic code.  Nothing to do when the queue
+// overflowed: the exact kernel launched next recomputes every point.
+__global__ void __launch_bounds__(kFastThreads)
+tol2d_redo_kernel(const __grid_constant__ GeoParams p, int pts) {
+  const unsigned total = *p.queue;
+  if (total > p.queue_cap) return;
+  double* __restrict__ out = static_cast<double*>(p.out);
+  const unsigned stride = gridDim.x * blockDim.x;
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const long long k = p.queue[1 + i];
+    out[k] = slow_point<double>(p, __ldg(p.x + k), __ldg(p.y + k), k);
+  }
+  if (blockIdx.x == 0 && threadIdx.x < static_cast<unsigned>(p.n % pts)) {
+    const long long k = p.n - (p.n % pts) + threadIdx.x;
     out[k] = slow_point<double>(p, __ldg(p.x + k), __ldg(p.y + k), k);
   }
 }
@@ -267,9 +290,9 @@ static int bilinear_default_mode() {
 // Tuning variant: PYI_TOL_VARIANT = <points per thread: 2|4><min blocks per SM: 2..5>[n]
 // ("n": no register prefetch); read per launch so that one process can sweep them
 static void tol2d_variant(int& pts, int& minb, bool& prefetch) {
-  pts = 2;  // round-2 sweeps on B200 (profiles/r2_k1_sweep*.txt)
-  minb = 3;
-  prefetch = true;
+  pts = 2;  // round-2 sweeps on B200 (profiles/r2_k1_sweep*.txt): 2 points x 5 blocks, no prefetch
+  minb = 5;
+  prefetch = false;
   const char* e = std::getenv("PYI_TOL_VARIANT");
   if (e && (e[0] == '2' || e[0] == '4') && e[1] >= '2' && e[1] <= '5') {
     pts = e[0] - '0';
@@ -301,12 +324,12 @@ static void launch_tol2d_v(const GeoParams& p, cudaStream_t stream) {
   constexpr bool kSweep = PER && XM == 2 && YM != 1;
   if (!kSweep) {
     pts = 2;
-    minb = 3;
-    prefetch = true;
+    minb = 4;
+    prefetch = false;
   }
   const int blocks = grid_for((p.n + pts - 1) / pts, kFastThreads, minb);
   if constexpr (!kSweep) {
-    bilinear2d_tol_kernel<PER, XM, YM, 2, 3, true><<<blocks, kFastThreads, 0, stream>>>(p);
+    bilinear2d_tol_kernel<PER, XM, YM, 2, 4, false><<<blocks, kFastThreads, 0, stream>>>(p);
     return;
   } else {
 #define PYI_LAUNCH(P, B)                                                                        \
@@ -347,8 +370,13 @@ static void launch_tol2d_p(const GeoParams& p, cudaStream_t stream) {
   }
 }
 
+constexpr unsigned kTolQueue = 1u << 20;  // unsettled points kept per launch (4 MB)
+
 static cudaError_t launch_tol2d(const GeoParams& p, cudaStream_t stream) {
   const long long chunk = 1LL << 31;  // multiple of 4: keeps the 32-byte alignment of the slices
+  int pts, minb;
+  bool prefetch;
+  tol2d_variant(pts, minb, prefetch);
   for (long long begin = 0; begin < p.n; begin += chunk) {
     GeoParams q = p;
     q.n = p.n - begin < chunk ? p.n - begin : chunk;
@@ -356,11 +384,26 @@ static cudaError_t launch_tol2d(const GeoParams& p, cudaStream_t stream) {
     q.x = p.x + begin;
     q.y = p.y + begin;
     q.out = static_cast<char*>(p.out) + begin * 8;
-    if (p.ax[0].period != 0.0) launch_tol2d_p<true>(q, stream);
-    else launch_tol2d_p<false>(q, stream);
-    g_launches.fetch_add(1);
-    const cudaError_t e = cudaGetLastError();
+    // per-launch queue from the stream-ordered allocator (concurrent calls on
+    // other streams have their own)
+    cudaError_t e = cudaMallocAsync(reinterpret_cast<void**>(&q.queue), (kTolQueue + 1) * sizeof(unsigned), stream);
     if (e != cudaSuccess) return e;
+    q.queue_cap = kTolQueue;
+    e = cudaMemsetAsync(q.queue, 0, sizeof(unsigned), stream);
+    if (e == cudaSuccess) {
+      if (p.ax[0].period != 0.0) launch_tol2d_p<true>(q, stream);
+      else launch_tol2d_p<false>(q, stream);
+      // kernels compiled once use the default points per thread
+      const bool sweep = p.ax[0].period != 0.0 && p.ax[0].tol_ok == 2 && !(p.ax[1].kind == 0 && p.ax[1].tol_ok == 1);
+      tol2d_redo_kernel<<<sm_count(), kFastThreads, 0, stream>>>(q, sweep ? pts : 2);
+      g_launches.fetch_add(2);
+      e = cudaGetLastError();
+    }
+    // the bit-identical kernel behind the queue: returns at once unless it overflowed
+    if (e == cudaSuccess) e = launch_fast2d_r<double>(q, stream);
+    const cudaError_t e2 = cudaFreeAsync(q.queue, stream);
+    if (e != cudaSuccess) return e;
+    if (e2 != cudaSuccess) return e2;
   }
   return cudaSuccess;
 }

@@ -29,6 +29,11 @@ struct GeoParams {
   const double* u;
   void* out;      // double (f64/i64/u64 grids) or float
   unsigned long long* oob_key;
+  // tolerance-mode bilinear (pyi_fast2d_tol.cuh): queue[0] counts the points the
+  // hot kernel could not settle, queue[1 ..] holds the first queue_cap of them.
+  // The exact kernel launched behind it only runs when the queue overflowed.
+  unsigned* queue;
+  unsigned queue_cap;
 };
 
 struct WinParams {

@@ -50,7 +50,7 @@ for lat_name, lat in (("regular", syn.lat_axis_values()), ("irregular", syn.irre
     tol = pyi.geometric.Bivariate.bilinear().with_value_mode("tolerance")
     ms = run(grid, exact)
     print(f"{lat_name:9s} exact   default  {ms:8.3f} ms {n / ms / 1e6:8.1f} Gpts/s  frac {n * 24 / ms / 1e6 / peak:.4f}", flush=True)
-    variants = ["23", "23n", "22", "24", "25", "42", "43", "44", "43n"] if lat_name == "regular" else ["23", "23n", "24", "43"]
+    variants = ["23", "23n", "22n", "24", "24n", "25", "25n", "42n", "43n", "44n"] if lat_name == "regular" else ["23", "23n", "24n", "25n"]
     for v in variants:
         os.environ["PYI_TOL_VARIANT"] = v
         ms = run(grid, tol)
