@@ -294,11 +294,19 @@ class Env:
         self.dev = torch.device("cuda", self.local)
         if self.world > 1:
             # NCCL's banner / debug lines go to stderr: stdout carries the one JSON line
+            # (the banner is written to file descriptor 1 by the library itself)
             os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
-            dist.init_process_group("nccl", device_id=self.dev)
-            warm = torch.zeros(1, device=self.dev)  # communicator set-up is a one-off of the process group
-            dist.all_reduce(warm)
-            torch.cuda.synchronize()
+            sys.stdout.flush()
+            saved = os.dup(1)
+            os.dup2(2, 1)
+            try:
+                dist.init_process_group("nccl", device_id=self.dev)
+                warm = torch.zeros(1, device=self.dev)  # communicator set-up is a one-off of the process group
+                dist.all_reduce(warm)
+                torch.cuda.synchronize()
+            finally:
+                os.dup2(saved, 1)
+                os.close(saved)
 
     def barrier(self):
         if self.world > 1:

@@ -48,64 +48,6 @@
 
 namespace pyi {
 
-constexpr double kMagic = 6755399441055744.0;  // 1.5 * 2^52
-
-// rint(v) for |v| < 2^51 as a double, and its low 32 bits as an int
-__device__ __forceinline__ double rint_magic(double v, int& lo) {
-  const double m = __dadd_rn(v, kMagic);
-  lo = __double2loint(m);
-  return __dsub_rn(m, kMagic);
-}
-
-// |v| < 2^31 and finite, from the exponent field (integer pipe)
-__device__ __forceinline__ bool below_2p31(double v) {
-  return (static_cast<unsigned>(__double2hiint(v)) & 0x7ff00000u) < 0x41e00000u;
-}
-
-// One regular ascending axis.  MODE 1: general, 2: exact nodes.  WRAP: the
-// coordinate was normalised (x = c + jf * period; cell n-1 -> 0 exists when
-// a.periodic).  Returns the cell index and the weight t; `safe` is cleared
-// unless the bracket is verified.
-//
-// The numerator of t follows the reference's roundings: for y it is fl(y - y0);
-// for a periodic x the reference normalises the query against the cell's own
-// x0 (bivariate.hpp:83-88): px = fl(remainder(fl(x - x0), period) + x0), then
-// fl(px - x0).  remainder()'s quotient is jf for a point inside the cell, and
-// fma(-jf, period, d) is exact, so the same four roundings are made here.
-template <int MODE, bool WRAP>
-__device__ __forceinline__ void tol_regular(const DAxis& a, double c, double x, double jf, int& k,
-                                            double& t, bool& safe) {
-  const double q5 = fma(c, a.inv_step, a.tol_off);
-  const double kf = rint_magic(q5, k);
-  double c0, scale = a.inv_step;
-  if (MODE == 2) {
-    c0 = fma(kf, a.step, a.start);
-  } else {
-    c0 = __dadd_rn(a.start, __dmul_rn(kf, a.step));
-    double c1 = __dadd_rn(a.start, __dmul_rn(__dadd_rn(kf, 1.0), a.step));
-    if (WRAP) c1 = (k == a.n - 1) ? a.seam_c1 : c1;
-    // 1 / dx to first order in e = 1 - dx * inv_step (|e| < 2^-26, host gate)
-    const double e = fma(-__dsub_rn(c1, c0), a.inv_step, 1.0);
-    scale = fma(a.inv_step, e, a.inv_step);
-  }
-  double num;
-  if (WRAP) {
-    const double r = fma(-jf, a.period, __dsub_rn(x, c0));
-    num = __dsub_rn(__dadd_rn(r, c0), c0);
-  } else {
-    num = __dsub_rn(c, c0);
-  }
-  t = __dmul_rn(num, scale);
-  // t strictly inside (2^-21, 1 - 2^-21), tested on the high word (integer pipe;
-  // NaN and negative values fail).  The margin covers the roundings above and
-  // the distance between this kernel's normalised coordinate and the
-  // reference's (a few ulp of the coordinate, below 2^-24 of a step by the
-  // host's gate): the reference's bracket is (k, k + 1).
-  const int th = __double2hiint(t);
-  const unsigned cells = static_cast<unsigned>((WRAP && a.periodic) ? a.n : a.n - 1);
-  safe = safe && below_2p31(q5) && th > 0x3ea00000 && th < 0x3fefffff && static_cast<unsigned>(k) < cells;
-}
-
 // Irregular ascending y: the exact bracket of pyi_fast2d.cuh, weight through the
 // staged reciprocal spacings.
 __device__ __forceinline__ void tol_irregular(const DAxis& a, const double* __restrict__ sp,
@@ -370,8 +312,6 @@ static void launch_tol2d_p(const GeoParams& p, cudaStream_t stream) {
   }
 }
 
-constexpr unsigned kTolQueue = 1u << 20;  // unsettled points kept per launch (4 MB)
-
 static cudaError_t launch_tol2d(const GeoParams& p, cudaStream_t stream) {
   const long long chunk = 1LL << 31;  // multiple of 4: keeps the 32-byte alignment of the slices
   int pts, minb;
@@ -384,11 +324,16 @@ static cudaError_t launch_tol2d(const GeoParams& p, cudaStream_t stream) {
     q.x = p.x + begin;
     q.y = p.y + begin;
     q.out = static_cast<char*>(p.out) + begin * 8;
-    // per-launch queue from the stream-ordered allocator (concurrent calls on
-    // other streams have their own)
-    cudaError_t e = cudaMallocAsync(reinterpret_cast<void**>(&q.queue), (kTolQueue + 1) * sizeof(unsigned), stream);
-    if (e != cudaSuccess) return e;
-    q.queue_cap = kTolQueue;
+    // the queue: the caller's (host pipeline: one per stream slot), else a
+    // per-launch one from the stream-ordered allocator, so that concurrent
+    // calls on other streams never share it
+    const bool own = p.queue == nullptr;
+    cudaError_t e = cudaSuccess;
+    if (own) {
+      e = cudaMallocAsync(reinterpret_cast<void**>(&q.queue), (kTolQueue + 1) * sizeof(unsigned), stream);
+      if (e != cudaSuccess) return e;
+      q.queue_cap = kTolQueue;
+    }
     e = cudaMemsetAsync(q.queue, 0, sizeof(unsigned), stream);
     if (e == cudaSuccess) {
       if (p.ax[0].period != 0.0) launch_tol2d_p<true>(q, stream);
@@ -401,9 +346,11 @@ static cudaError_t launch_tol2d(const GeoParams& p, cudaStream_t stream) {
     }
     // the bit-identical kernel behind the queue: returns at once unless it overflowed
     if (e == cudaSuccess) e = launch_fast2d_r<double>(q, stream);
-    const cudaError_t e2 = cudaFreeAsync(q.queue, stream);
+    if (own) {
+      const cudaError_t e2 = cudaFreeAsync(q.queue, stream);
+      if (e == cudaSuccess) e = e2;
+    }
     if (e != cudaSuccess) return e;
-    if (e2 != cudaSuccess) return e2;
   }
   return cudaSuccess;
 }

@@ -300,7 +300,7 @@ void parallel_memcpy(void* dst, const void* src, size_t bytes) {
 // ---------------------------------------------------------------------------
 constexpr int kSlots = 3;
 constexpr long long kChunk = 1LL << 23;     // points per chunk, upper bound
-constexpr long long kChunkMin = 1LL << 20;  // lower bound (calls above it are cut in >= 8 chunks)
+constexpr long long kChunkMin = 1LL << 20;  // lower bound (calls above it are cut in up to 32 chunks)
 constexpr int kMaxWorkspacesPerDevice = 4;
 
 struct Slot {
@@ -308,6 +308,7 @@ struct Slot {
   cudaEvent_t done{nullptr};
   char* dev{nullptr};     // device chunk buffers
   char* pinned{nullptr};  // staging (allocated on first pageable use)
+  unsigned* queue{nullptr};  // the tolerance kernel's queue of unsettled points
   bool busy{false};
   long long begin{0}, count{0};
 };
@@ -331,6 +332,9 @@ struct Workspace {
     for (auto& s : slot) {
       if (!s.stream) PYI_CUDA(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
       if (!s.done) PYI_CUDA(cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
+      if (!s.queue) {
+        PYI_CUDA(cudaMalloc(reinterpret_cast<void**>(&s.queue), (pyi::kTolQueue + 1) * sizeof(unsigned)));
+      }
     }
     if (need_dev > dev_bytes) {
       for (auto& s : slot) {
@@ -450,12 +454,14 @@ struct Column {
 
 long long chunk_points(long long n) {
   if (n <= kChunkMin) return std::max<long long>(n, 1);
-  long long c = std::min(kChunk, std::max(kChunkMin, (n + 7) / 8));
+  // the first chunk's upload and the last chunk's download overlap nothing:
+  // 1/32 of the call keeps that below ~5 % of a copy-bound call
+  long long c = std::min(kChunk, std::max(kChunkMin, (n + 31) / 32));
   return (c + 63) & ~63LL;  // keeps every chunk start 512-byte aligned in the streams
 }
 
-// Runs `launch(slot_stream, begin, count, dev_buffer)` over all chunks of the n
-// points the columns describe.  With `reset_key` the workspace's bounds-error
+// Runs `launch(slot_stream, begin, count, dev_buffer, slot_queue)` over all
+// chunks of the n points the columns describe.  With `reset_key` the workspace's bounds-error
 // key is reset on the first slot's stream and every other slot waits for it.
 template <typename Launch>
 int run_pipeline(Workspace& ws, long long n, std::vector<Column>& cols, bool reset_key,
@@ -509,7 +515,7 @@ int run_pipeline(Workspace& ws, long long n, std::vector<Column>& cols, bool res
       }
       PYI_CUDA(cudaMemcpyAsync(s.dev + c.dev_off, src, bytes, cudaMemcpyHostToDevice, s.stream));
     }
-    cudaError_t e = launch(s.stream, begin, count, s.dev);
+    cudaError_t e = launch(s.stream, begin, count, s.dev, s.queue);
     if (e != cudaSuccess) return cuda_fail(e, "kernel launch");
     for (auto& c : cols) {
       if (!c.host_out) continue;
@@ -674,8 +680,8 @@ std::vector<int> shard_devices(const pyi_grid* grid, long long n) {
 // device, exactly as the reference's parallel_for splits them over threads
 // (parallel_for.hpp:46-53: n / G each, the first n % G shards take one more);
 // every shard runs its own chunk pipeline on its own workspace from its own
-// host thread.  `launch_on(view, oob_key, stream, global_begin, count, dev)`
-// enqueues the kernel of one chunk.  `key` receives the minimum bounds-error
+// host thread.  `launch_on(view, oob_key, stream, global_begin, count, dev,
+// columns, slot_queue)` enqueues the kernel of one chunk.  `key` receives the minimum bounds-error
 // key over all devices (indexes are global, so the lowest offending point wins
 // whatever the sharding).
 template <typename LaunchOn>
@@ -710,8 +716,8 @@ int run_host_call(const pyi_grid* grid, long long n, const std::vector<Column>& 
       Lease lease(devices[r]);
       Workspace& ws = *lease.ws;
       st = run_pipeline(ws, count, mine, true,
-                        [&](cudaStream_t s, long long b, long long c, char* dev) {
-                          return launch_on(view, ws.oob_key, s, begin + b, c, dev, mine);
+                        [&](cudaStream_t s, long long b, long long c, char* dev, unsigned* queue) {
+                          return launch_on(view, ws.oob_key, s, begin + b, c, dev, mine, queue);
                         });
       if (st != PYI_OK) return st;
       if (want_key) return read_key(ws, out.key);
@@ -734,6 +740,26 @@ int run_host_call(const pyi_grid* grid, long long n, const std::vector<Column>& 
     key = std::min(key, r.key);
   }
   return PYI_OK;
+}
+
+// The stream-ordered allocator serves the per-launch scratch of device-memory
+// calls (bounds-error key, queue of unsettled points).  By default a pool gives
+// its memory back to the driver at every synchronisation, which makes the next
+// allocation a (process-wide serialising) driver call: keep it cached instead.
+void keep_pool_cached(int device) {
+  static std::mutex mu;
+  static std::vector<char> done;
+  std::lock_guard<std::mutex> lock(mu);
+  if (device < 0) return;
+  if (static_cast<size_t>(device) >= done.size()) done.resize(device + 1, 0);
+  if (done[device]) return;
+  cudaMemPool_t pool = nullptr;
+  if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
+    unsigned long long threshold = ~0ULL;
+    cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &threshold);
+  }
+  cudaGetLastError();
+  done[device] = 1;
 }
 
 // Per-call bounds-error key of a device-memory call, from the stream-ordered
@@ -767,6 +793,7 @@ int require_grid_device(const pyi_grid* grid) {
     return fail(PYI_BAD_ARG, "device-memory call: the current device (" + std::to_string(dev) +
                                  ") is not the grid's device (" + std::to_string(grid->device) + ")");
   }
+  keep_pool_cached(dev);
   return PYI_OK;
 }
 
@@ -899,7 +926,7 @@ static int axis_lookup(const pyi_axis* axis_c, int64_t n, const void* coords, in
   int dev = 0;
   PYI_CUDA(cudaGetDevice(&dev));
   Lease lease(dev);
-  return run_pipeline(*lease.ws, n, cols, false, [&](cudaStream_t s, long long, long long count, char* d) {
+  return run_pipeline(*lease.ws, n, cols, false, [&](cudaStream_t s, long long, long long count, char* d, unsigned*) {
     pyi::FindParams q = p;
     q.n = count;
     q.coords = d + cols[0].dev_off;
@@ -1222,7 +1249,8 @@ int pyi_geometric(const pyi_grid* grid, const pyi_geometric_config* cfg, int64_t
   unsigned long long key = pyi::kNoOob;
   st = run_host_call(grid, n, cols, cfg->bounds_error != 0, key,
                      [&](const GridView& view, unsigned long long* oob_key, cudaStream_t s,
-                         long long begin, long long count, char* dev, const std::vector<Column>& c) {
+                         long long begin, long long count, char* dev, const std::vector<Column>& c,
+                         unsigned* queue) {
                        pyi::GeoParams q = p;
                        bind(q, view);
                        q.n = count;
@@ -1233,6 +1261,8 @@ int pyi_geometric(const pyi_grid* grid, const pyi_geometric_config* cfg, int64_t
                        q.out = dev + c[cout_].dev_off;
                        q.oob_key = oob_key;
                        q.index_base = begin;
+                       q.queue = queue;
+                       q.queue_cap = pyi::kTolQueue;
                        return pyi::launch_geometric(q, s);
                      });
   if (st != PYI_OK) return st;
@@ -1373,7 +1403,8 @@ int pyi_windowed(const pyi_grid* grid, const pyi_windowed_nd_config* cfg, int64_
   unsigned long long key = pyi::kNoOob;
   st = run_host_call(grid, n, cols, cfg->bounds_error != 0, key,
                      [&](const GridView& view, unsigned long long* oob_key, cudaStream_t s,
-                         long long begin, long long count, char* dev, const std::vector<Column>& c) {
+                         long long begin, long long count, char* dev, const std::vector<Column>& c,
+                         unsigned*) {
                        pyi::WinNdParams q = p;
                        bind(q, view);
                        q.n = count;
@@ -1440,7 +1471,7 @@ int pyi_datetime_convert(int src, int dst, int64_t n, const int64_t* in, int64_t
   PYI_CUDA(cudaGetDevice(&dev));
   Lease lease(dev);
   Workspace& ws = *lease.ws;
-  st = run_pipeline(ws, n, cols, true, [&](cudaStream_t s, long long begin, long long count, char* d) {
+  st = run_pipeline(ws, n, cols, true, [&](cudaStream_t s, long long begin, long long count, char* d, unsigned*) {
     return pyi::launch_datetime_convert(reinterpret_cast<const long long*>(d + cols[0].dev_off),
                                         reinterpret_cast<long long*>(d + cols[1].dev_off), count,
                                         begin, src, dst, ws.oob_key, s);

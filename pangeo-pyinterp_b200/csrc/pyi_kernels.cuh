@@ -96,6 +96,9 @@ struct FindParams {
   int32_t bounded;
 };
 
+// capacity of the tolerance kernel's queue of unsettled points (entries; the
+// buffer holds one counter more)
+constexpr unsigned kTolQueue = 1u << 20;
 cudaError_t launch_geometric(const GeoParams& p, cudaStream_t stream);
 cudaError_t launch_windowed2d(const WinParams& p, cudaStream_t stream);
 cudaError_t launch_windowed_nd(const WinNdParams& p, cudaStream_t stream);
