@@ -307,11 +307,18 @@ class Env:
             finally:
                 os.dup2(saved, 1)
                 os.close(saved)
+            # a CPU-side group: ranks that only wait must not park an NCCL kernel on their GPU
+            self.cpu_group = dist.new_group(backend="gloo")
 
     def barrier(self):
         if self.world > 1:
             self.dist.barrier()
         self.torch.cuda.synchronize()
+
+    def cpu_barrier(self):
+        """Barrier on the host only (gloo): a rank waiting here leaves its GPU idle."""
+        if self.world > 1:
+            self.dist.barrier(group=self.cpu_group)
 
     def max_over_ranks(self, v: float) -> float:
         if self.world == 1:
@@ -551,14 +558,18 @@ def main():
         if active:
             for _ in range(2):
                 r = api(grid, *host_arrays, method)
+        env.cpu_barrier()
         env.barrier()
         t0 = time.perf_counter()
         if active:
             for _ in range(steps):
                 r = api(grid, *host_arrays, method)
             torch.cuda.synchronize()
-        dt = env.max_over_ranks(time.perf_counter() - t0)
-        return dt, r
+        dt = time.perf_counter() - t0
+        # idle ranks wait on the host: an NCCL collective entered early would
+        # spin on THEIR device, which the active rank's call is also using
+        env.cpu_barrier()
+        return env.max_over_ranks(dt), r
 
     e2e_ranks = None
     if world > 1:

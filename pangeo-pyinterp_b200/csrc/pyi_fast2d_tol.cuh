@@ -345,7 +345,10 @@ static cudaError_t launch_tol2d(const GeoParams& p, cudaStream_t stream) {
       e = cudaGetLastError();
     }
     // the bit-identical kernel behind the queue: returns at once unless it overflowed
-    if (e == cudaSuccess) e = launch_fast2d_r<double>(q, stream);
+    if (e == cudaSuccess) {
+      q.run_if_overflow = q.queue;
+      e = launch_fast2d_r<double>(q, stream);
+    }
     if (own) {
       const cudaError_t e2 = cudaFreeAsync(q.queue, stream);
       if (e == cudaSuccess) e = e2;

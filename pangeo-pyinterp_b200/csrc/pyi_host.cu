@@ -265,10 +265,10 @@ bool host_pinned(const void* p) {
 }
 
 void parallel_memcpy(void* dst, const void* src, size_t bytes) {
-  const size_t kMin = 8u << 20;
+  const size_t kMin = 2u << 20;  // bytes per copying thread, at least
   unsigned hw = std::thread::hardware_concurrency();
   const unsigned nt = static_cast<unsigned>(
-      std::min<size_t>(std::max(1u, std::min(hw, 8u)), std::max<size_t>(1, bytes / kMin)));
+      std::min<size_t>(std::max(1u, std::min(hw, 16u)), std::max<size_t>(1, bytes / kMin)));
   if (nt <= 1) {
     std::memcpy(dst, src, bytes);
     return;
@@ -300,7 +300,7 @@ void parallel_memcpy(void* dst, const void* src, size_t bytes) {
 // ---------------------------------------------------------------------------
 constexpr int kSlots = 3;
 constexpr long long kChunk = 1LL << 23;     // points per chunk, upper bound
-constexpr long long kChunkMin = 1LL << 20;  // lower bound (calls above it are cut in up to 32 chunks)
+constexpr long long kChunkMin = 1LL << 20;  // lower bound (calls above it are cut in >= 8 chunks)
 constexpr int kMaxWorkspacesPerDevice = 4;
 
 struct Slot {
@@ -454,9 +454,9 @@ struct Column {
 
 long long chunk_points(long long n) {
   if (n <= kChunkMin) return std::max<long long>(n, 1);
-  // the first chunk's upload and the last chunk's download overlap nothing:
-  // 1/32 of the call keeps that below ~5 % of a copy-bound call
-  long long c = std::min(kChunk, std::max(kChunkMin, (n + 31) / 32));
+  // 1/8 of the call (measured, round 2: 1/32 chunks lost 20 % of a copy-bound
+  // call to per-chunk event waits on three slots)
+  long long c = std::min(kChunk, std::max(kChunkMin, (n + 7) / 8));
   return (c + 63) & ~63LL;  // keeps every chunk start 512-byte aligned in the streams
 }
 
@@ -594,9 +594,31 @@ struct pyi_grid {
   // node-derivative weights of the six-node spline on x / y (pyi_bicubicw.cuh)
   int w_ok{0};
   double w6[2][12]{};
+  // cubic coefficients of the separable bicubic stencil (pyi_bicubics.cuh)
+  int cw_ok{0};
+  double cw[2][8][4]{};
 };
 
 namespace {
+
+// Window weights of the separable bicubic stencil as cubics in the cell
+// coordinate t (pyi_bicubics.cuh): C_j(t) = [j==2] h00 + [j==3] h01 +
+// step (h10 W2[j] + h11 W3[j]) with the cubic Hermite basis h00 = 1 - 3t^2 +
+// 2t^3, h01 = 3t^2 - 2t^3, h10 = t - 2t^2 + t^3, h11 = t^3 - t^2, and W2 / W3
+// the spline derivative weights at the two centre nodes (w6).
+void stencil_cubics(const double* w6, double step, double (*cw)[4]) {
+  for (int e = 0; e < 8; ++e) {
+    for (int c = 0; c < 4; ++c) cw[e][c] = 0.0;
+  }
+  for (int j = 0; j < 6; ++j) {
+    const double a = step * w6[j], b = step * w6[6 + j];
+    const double d2 = j == 2 ? 1.0 : 0.0, d3 = j == 3 ? 1.0 : 0.0;
+    cw[j + 1][0] = d2;
+    cw[j + 1][1] = a;
+    cw[j + 1][2] = -3.0 * d2 + 3.0 * d3 - 2.0 * a - b;
+    cw[j + 1][3] = 2.0 * d2 - 2.0 * d3 + a + b;
+  }
+}
 
 // What a kernel launch on one device reads of a grid.
 struct GridView {
@@ -1054,6 +1076,10 @@ pyi_grid* pyi_grid_create(int ndim, const pyi_axis* const* axes, int dtype, cons
         ++have;
       }
       g->w_ok = have == 2;
+      if (g->w_ok && g->dax[0].step > 0.0 && g->dax[1].step > 0.0) {
+        for (int k = 0; k < 2; ++k) stencil_cubics(g->w6[k], g->dax[k].step, g->cw[k]);
+        g->cw_ok = 1;
+      }
       cudaFree(d_w);
     }
     cudaGetLastError();
@@ -1347,6 +1373,8 @@ int pyi_windowed(const pyi_grid* grid, const pyi_windowed_nd_config* cfg, int64_
   }
   p.w_ok = grid->w_ok;
   for (int a = 0; a < 2; ++a) std::memcpy(p.w6[a], grid->w6[a], sizeof(p.w6[a]));
+  p.cw_ok = grid->cw_ok;
+  std::memcpy(p.cw, grid->cw, sizeof(p.cw));
   p.cells = 1;
   for (int a = 0; a < nd; ++a) p.cells *= grid->shape[a];
   const size_t out_elem = result_is_f64(grid->dtype) ? 8 : 4;

@@ -34,6 +34,9 @@ struct GeoParams {
   // The exact kernel launched behind it only runs when the queue overflowed.
   unsigned* queue;
   unsigned queue_cap;
+  // set only on the bit-identical kernel launched BEHIND the tolerance kernel:
+  // it runs when *run_if_overflow > queue_cap and returns at once otherwise
+  const unsigned* run_if_overflow;
 };
 
 struct WinParams {
@@ -86,6 +89,11 @@ struct WinNdParams {
   int32_t w_ok;
   double w6[2][12];
   long long cells;  // elements of the whole grid (bounds the vector loads)
+  // separable bicubic stencil (pyi_bicubics.cuh): cubic coefficients of the six
+  // window weights C_j(t) of the x / y axis, entry j + 1 (entries 0 and 7 are
+  // zero), valid when cw_ok
+  int32_t cw_ok;
+  double cw[2][8][4];
 };
 
 struct FindParams {

@@ -23,6 +23,7 @@ static bool force_generic() {
 #include "pyi_fastwin.cuh"
 #include "pyi_fastwin_nd.cuh"
 #include "pyi_bicubicw.cuh"
+#include "pyi_bicubics.cuh"
 
 namespace pyi {
 // K6 (pyi_windowed_nd.cuh) is instantiated per window capacity in
@@ -39,7 +40,11 @@ cudaError_t launch_windowed_nd(const WinNdParams& p, cudaStream_t stream) {
   // generic kernel recomputes the points that pass tagged
   if (p.ndim >= 2 && p.method == PYI_S_BICUBIC && p.half_x == 3 && p.half_y == 3 && p.w_ok &&
       (p.ndim == 2 || p.planes) && !force_generic() && !exact_bicubic(p)) {
-    cudaError_t e = launch_bicubicw(p, stream);
+    // 2-D float64 grids with ascending axes: the separable stencil (K4s);
+    // PYINTERP_B200_BICUBIC=weights keeps K4w for comparison
+    const char* which = getenv("PYINTERP_B200_BICUBIC");
+    const bool separable = bicubics_eligible(p) && !(which != nullptr && which[0] == 'w');
+    cudaError_t e = separable ? launch_bicubics(p, stream) : launch_bicubicw(p, stream);
     if (e != cudaSuccess) return e;
     WinNdParams q = p;
     q.redo = 1;
