@@ -227,7 +227,14 @@ bicubic_sep_kernel(const __grid_constant__ WinNdParams p) {
       }
       mine = has_nan ? CUDART_NAN : RedoTag<double>::value();
     }
-    if (active) __stcs(out + k, mine);
+    if (active) {
+      __stcs(out + k, mine);
+      // tagged points are also listed, so that the redo pass need not scan the output
+      if (p.queue != nullptr && RedoTag<double>::is(mine)) {
+        const unsigned slot = atomicAdd(p.queue, 1u);
+        if (slot < p.queue_cap) p.queue[1 + slot] = static_cast<unsigned>(k);
+      }
+    }
   }
 }
 

@@ -1432,7 +1432,7 @@ int pyi_windowed(const pyi_grid* grid, const pyi_windowed_nd_config* cfg, int64_
   st = run_host_call(grid, n, cols, cfg->bounds_error != 0, key,
                      [&](const GridView& view, unsigned long long* oob_key, cudaStream_t s,
                          long long begin, long long count, char* dev, const std::vector<Column>& c,
-                         unsigned*) {
+                         unsigned* queue) {
                        pyi::WinNdParams q = p;
                        bind(q, view);
                        q.n = count;
@@ -1443,6 +1443,8 @@ int pyi_windowed(const pyi_grid* grid, const pyi_windowed_nd_config* cfg, int64_
                        q.out = dev + c[cout_].dev_off;
                        q.oob_key = oob_key;
                        q.index_base = begin;
+                       q.queue = queue;
+                       q.queue_cap = pyi::kTolQueue;
                        return pyi::launch_windowed_nd(q, s);
                      });
   if (st != PYI_OK) return st;

@@ -94,6 +94,11 @@ struct WinNdParams {
   // zero), valid when cw_ok
   int32_t cw_ok;
   double cw[2][8][4];
+  // separable pass: queue[0] counts the points it tagged for the redo pass,
+  // queue[1 ..] holds the first queue_cap of them; the redo pass scans the
+  // output for tags only when there is no queue or it overflowed
+  unsigned* queue;
+  unsigned queue_cap;
 };
 
 struct FindParams {

@@ -44,11 +44,32 @@ cudaError_t launch_windowed_nd(const WinNdParams& p, cudaStream_t stream) {
     // PYINTERP_B200_BICUBIC=weights keeps K4w for comparison
     const char* which = getenv("PYINTERP_B200_BICUBIC");
     const bool separable = bicubics_eligible(p) && !(which != nullptr && which[0] == 'w');
-    cudaError_t e = separable ? launch_bicubics(p, stream) : launch_bicubicw(p, stream);
-    if (e != cudaSuccess) return e;
     WinNdParams q = p;
-    q.redo = 1;
-    return launch_windowed_nd_w<6>(q, stream);
+    q.queue = nullptr;
+    bool own = false;
+    cudaError_t e = cudaSuccess;
+    if (separable && p.n < (1LL << 32)) {
+      // the list of tagged points: the caller's (host pipeline slots) or one
+      // from the stream-ordered allocator
+      q.queue = p.queue;
+      if (q.queue == nullptr) {
+        e = cudaMallocAsync(reinterpret_cast<void**>(&q.queue), (kTolQueue + 1) * sizeof(unsigned), stream);
+        if (e != cudaSuccess) return e;
+        own = true;
+      }
+      q.queue_cap = kTolQueue;
+      e = cudaMemsetAsync(q.queue, 0, sizeof(unsigned), stream);
+    }
+    if (e == cudaSuccess) e = separable ? launch_bicubics(q, stream) : launch_bicubicw(q, stream);
+    if (e == cudaSuccess) {
+      q.redo = 1;
+      e = launch_windowed_nd_w<6>(q, stream);
+    }
+    if (own) {
+      const cudaError_t e2 = cudaFreeAsync(q.queue, stream);
+      if (e == cudaSuccess) e = e2;
+    }
+    return e;
   }
   // 2-D bicubic / bilinear keep K4 and its fast path
   if (p.ndim == 2 && p.method <= PYI_S_BILINEAR) {
@@ -82,6 +103,7 @@ cudaError_t launch_windowed_nd(const WinNdParams& p, cudaStream_t stream) {
     if (e != cudaSuccess) return e;
     WinNdParams q = p;
     q.redo = 1;
+    q.queue = nullptr;  // this fast pass tags its points in the output only: the redo pass scans
     return launch_windowed_nd_w<6>(q, stream);
   }
   const int hy = p.ndim >= 2 ? p.half_y : 1;

@@ -279,6 +279,14 @@ windowed_nd_redo_kernel(const __grid_constant__ WinNdParams p) {
   R* __restrict__ out = static_cast<R*>(p.out);
   const ZT* __restrict__ zs = static_cast<const ZT*>(p.z);
   auto compute = [&](long long k) { redo_point<MAXW, ND, ZT, R>(p, k, key); };
+  // the fast pass listed what it tagged (pyi_bicubics.cuh): no scan
+  if (p.queue != nullptr && *p.queue <= p.queue_cap) {
+    const unsigned total = *p.queue;
+    const unsigned stride = gridDim.x * blockDim.x;
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) compute(p.queue[1 + i]);
+    if (p.bounds_error && key != kNoOob) atomicMin(p.oob_key, key);
+    return;
+  }
   // the scan reads kScan x 32 outputs per step so that the loads overlap
   constexpr int kScan = 8;
   const long long warps = static_cast<long long>(gridDim.x) * 4;
