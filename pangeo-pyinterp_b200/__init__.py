@@ -8,7 +8,7 @@ Everything is computed by hand-written CUDA kernels behind the C-ABI of
 fallback: importing works without a GPU (axes are host objects), every lookup
 or interpolation raises without one.
 """
-from . import _abi, config, core, dist, fill, synthetic
+from . import _abi, backends, config, core, dist, fill, synthetic
 from .config import geometric, windowed
 from .core import Axis, Grid, TemporalAxis
 from .regular_grid_interpolator import (bivariate, quadrivariate, trivariate, univariate,
@@ -17,7 +17,7 @@ from .regular_grid_interpolator import (bivariate, quadrivariate, trivariate, un
 Grid1D = Grid2D = Grid3D = Grid4D = Grid  # pyinterp/__init__.py:92-95
 
 __all__ = ["Axis", "TemporalAxis", "Grid", "Grid1D", "Grid2D", "Grid3D", "Grid4D", "bivariate", "trivariate",
-           "quadrivariate", "univariate", "univariate_derivative", "geometric", "windowed", "config", "core", "dist", "fill", "synthetic", "device_count",
+           "quadrivariate", "univariate", "univariate_derivative", "geometric", "windowed", "config", "core", "dist", "fill", "synthetic", "backends", "device_count",
            "launch_count"]
 
 

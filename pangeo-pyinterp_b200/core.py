@@ -329,7 +329,10 @@ class TemporalAxis(Axis):
         return convert_resolution(v, src, dst)
 
     def cast_to_temporal_axis(self, array):
-        return self.cast_to_int64(array).view(self._dtype)
+        v = self.cast_to_int64(array)
+        if _is_torch_cuda(v):  # device int64 values in the axis resolution stay where they are
+            return v
+        return v.view(self._dtype)
 
     def _coords(self, coordinates):
         return self.cast_to_int64(coordinates)
