@@ -346,6 +346,33 @@ int pyi_fill_multigrid(void *grid, int dtype, int64_t nx, int64_t ny,
                        uint64_t *iterations, double *max_residual,
                        void *stream);
 
+/* config::fill::Loess (config/fill.hpp:164-219) and LoessValueType (:26-30) */
+typedef enum pyi_loess_value_type {
+  PYI_LOESS_UNDEFINED = 0, /* fill only the undefined (NaN) cells */
+  PYI_LOESS_DEFINED = 1,   /* smooth only the defined cells */
+  PYI_LOESS_ALL = 2        /* smooth and fill every cell */
+} pyi_loess_value_type;
+
+typedef struct pyi_loess_config {
+  int32_t first_guess;     /* pyi_first_guess (iterative mode) */
+  int32_t is_periodic;     /* x axis periodic (longitude) */
+  uint32_t max_iterations; /* 1: single pass; 0: only the first guess */
+  uint32_t half_x;         /* config nx: half window size along x (rows), >= 1 */
+  uint32_t half_y;         /* config ny: half window size along y (columns), >= 1 */
+  int32_t value_type;      /* pyi_loess_value_type */
+  double epsilon;          /* iteration stops when max |change| < epsilon */
+} pyi_loess_config;
+
+/* fill::loess (fill/loess.hpp:207-253): `result` receives the row-major (nx, ny)
+ * grid `grid` (dtype PYI_F32 or PYI_F64, left untouched) with every processed
+ * cell replaced by the tri-cube weighted mean of the defined values in its
+ * (2 half_x + 1) x (2 half_y + 1) window; single pass, or iterated from the
+ * first guess until the largest change is below epsilon.  Bit-identical to the
+ * reference whatever its thread count. */
+int pyi_fill_loess(const void *grid, void *result, int dtype, int64_t nx,
+                   int64_t ny, const pyi_loess_config *cfg, int mem,
+                   void *stream);
+
 /* Reference text "{coord} is out of bounds for axis {x|y|z|u} [{min}, ...,
  * {max}]" (pybind/grid.hpp:367-370). `coord` points to a double or an int64
  * according to the axis. Returns the length written (excluding NUL). */

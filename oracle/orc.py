@@ -59,6 +59,8 @@ _SIG = {
     "orc_fill_multigrid": (C.c_int, [_P, C.c_int, C.c_int64, C.c_int64, C.c_int, C.c_int, C.c_uint64,
                                      C.c_double, C.c_uint32, C.c_uint32, C.c_int, C.POINTER(C.c_uint64),
                                      C.POINTER(C.c_double), C.c_char_p, C.c_size_t]),
+    "orc_fill_loess": (C.c_int, [_P, _P, C.c_int, C.c_int64, C.c_int64, C.c_uint32, C.c_uint32, C.c_int, C.c_int,
+                                 C.c_int, C.c_uint64, C.c_double, C.c_int, C.c_char_p, C.c_size_t]),
     "orc_eval2d_f64": (C.c_double, [C.c_int, C.c_int, C.c_int] + [C.c_double] * 10),
     "orc_eval2d_f32": (C.c_float, [C.c_int, C.c_int, C.c_int] + [C.c_float] * 10),
     "orc_axis_interp_f64": (C.c_double, [C.c_int] + [C.c_double] * 5),
@@ -254,6 +256,19 @@ class Oracle:
         if st == _abi.PYI_OVERFLOW:
             raise OverflowError(msg.value.decode())
         assert st == 0, (st, msg.value)
+        return out
+
+    def fill_loess(self, grid, nx=3, ny=3, value_type="undefined", first_guess="zonal_average", is_periodic=True,
+                   max_iterations=500, epsilon=1e-4, num_threads=1):
+        """fill::loess: returns the processed copy of `grid`."""
+        dt, rows, cols = self._fill_args(grid)
+        out = np.empty_like(grid)
+        msg = C.create_string_buffer(256)
+        st = self.lib.orc_fill_loess(_ptr(grid), _ptr(out), dt, rows, cols, nx, ny,
+                                     {"undefined": 0, "defined": 1, "all": 2}[value_type],
+                                     _abi.FIRST_GUESS[first_guess], int(is_periodic), max_iterations, epsilon,
+                                     num_threads, msg, 256)
+        assert st == 0, msg.value
         return out
 
     def temporal_repr(self, value: int, unit: str, timedelta: bool = False) -> str:

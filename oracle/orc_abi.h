@@ -111,6 +111,14 @@ double orc_univariate(int method, const double *xa, const double *ya, int n,
 int orc_datetime_convert(int src, int dst, int64_t n, const int64_t *in,
                          int64_t *out, char *msg, size_t msglen);
 
+/* fill::loess (fill/loess.hpp:207-253): `out` receives the processed copy of the
+ * row-major (nx, ny) grid `in`.  half_x / half_y: config nx / ny; value_type:
+ * LoessValueType (0 undefined, 1 defined, 2 all). */
+int orc_fill_loess(const void *in, void *out, int dtype, int64_t nx, int64_t ny,
+                   uint32_t half_x, uint32_t half_y, int value_type,
+                   int first_guess, int is_periodic, uint64_t max_iterations,
+                   double epsilon, int num_threads, char *msg, size_t msglen);
+
 /* TemporalAxis::coordinate_repr (math/temporal_axis.hpp:80-83,150-156;
  * dateutils::datetime64_to_string / timedelta64_to_string,
  * dateutils.hpp:729-812).  Returns the length written, -1 on a bad argument. */

@@ -1330,3 +1330,43 @@ extern "C" int orc_fill_multigrid(void* grid, int dtype, int64_t nx, int64_t ny,
     return PYI_BAD_ARG;
   }
 }
+
+// ---------------------------------------------------------------------------
+// fill::loess (fill/loess.hpp:207-253), the reference's own function: `in` is
+// a row-major (nx, ny) grid, `out` receives the processed copy.  half_x /
+// half_y are the half-window sizes (config nx / ny), value_type is
+// LoessValueType (0 undefined, 1 defined, 2 all).
+// ---------------------------------------------------------------------------
+#include "pyinterp/fill/loess.hpp"
+
+extern "C" int orc_fill_loess(const void* in, void* out, int dtype, int64_t nx, int64_t ny,
+                              uint32_t half_x, uint32_t half_y, int value_type, int first_guess,
+                              int is_periodic, uint64_t max_iterations, double epsilon,
+                              int num_threads, char* msg, size_t msglen) {
+  try {
+    ref::config::fill::Loess cfg;
+    fill_base(cfg, first_guess, is_periodic, max_iterations, epsilon, num_threads);
+    cfg.nx_ = half_x;
+    cfg.ny_ = half_y;
+    cfg.value_type_ = static_cast<ref::config::fill::LoessValueType>(value_type);
+    auto run = [&](auto tag) {
+      using T = decltype(tag);
+      Eigen::Map<const ref::RowMajorMatrix<T>> m(static_cast<const T*>(in), nx, ny);
+      const ref::RowMajorMatrix<T> res =
+          ref::fill::loess<T>(ref::EigenDRef<const ref::RowMajorMatrix<T>>(m), cfg);
+      std::copy(res.data(), res.data() + nx * ny, static_cast<T*>(out));
+    };
+    if (dtype == PYI_F32) {
+      run(float{});
+    } else if (dtype == PYI_F64) {
+      run(double{});
+    } else {
+      set_err(msg, msglen, "grid must be float32 or float64");
+      return PYI_BAD_ARG;
+    }
+    return PYI_OK;
+  } catch (const std::exception& e) {
+    set_err(msg, msglen, e.what());
+    return PYI_BAD_ARG;
+  }
+}

@@ -118,6 +118,18 @@ class FillConfig(C.Structure):
     ]
 
 
+class LoessConfig(C.Structure):
+    _fields_ = [
+        ("first_guess", C.c_int32),
+        ("is_periodic", C.c_int32),
+        ("max_iterations", C.c_uint32),
+        ("half_x", C.c_uint32),
+        ("half_y", C.c_uint32),
+        ("value_type", C.c_int32),
+        ("epsilon", C.c_double),
+    ]
+
+
 #: every symbol include/pyinterp_b200.h declares: name -> (restype, argtypes)
 _P = C.c_void_p
 _I64P = C.POINTER(C.c_int64)
@@ -152,6 +164,7 @@ SIGNATURES = {
                                         C.POINTER(C.c_uint64), C.POINTER(C.c_double), _P]),
     "pyi_fill_multigrid": (C.c_int, [_P, C.c_int, C.c_int64, C.c_int64, C.POINTER(FillConfig), C.c_int,
                                      C.POINTER(C.c_uint64), C.POINTER(C.c_double), _P]),
+    "pyi_fill_loess": (C.c_int, [_P, _P, C.c_int, C.c_int64, C.c_int64, C.POINTER(LoessConfig), C.c_int, _P]),
     "pyi_format_bounds_error": (C.c_int, [_P, C.c_int, _P, C.c_char_p, C.c_size_t]),
     "pyi_format_temporal": (C.c_int, [C.c_int, C.c_int, C.c_int64, C.c_char_p, C.c_size_t]),
     "pyi_launch_count": (C.c_int64, []),

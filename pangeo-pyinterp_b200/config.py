@@ -366,4 +366,44 @@ class Multigrid(_FillBase):
         return self._post_smooth
 
 
-fill = types.SimpleNamespace(FirstGuess=FirstGuess, GaussSeidel=GaussSeidel, Multigrid=Multigrid)
+class LoessValueType(enum.IntEnum):
+    """config::fill::LoessValueType (config/fill.hpp:26-30)."""
+    UNDEFINED = 0
+    DEFINED = 1
+    ALL = 2
+
+
+class Loess(_FillBase):
+    """config::fill::Loess (config/fill.hpp:164-219)."""
+
+    _value_type = LoessValueType.UNDEFINED
+    _nx = 3
+    _ny = 3
+
+    def _size(self, name, value):
+        value = int(value)
+        if not 0 <= value < 2 ** 32:  # uint32_t argument of the reference binding
+            raise TypeError(f"with{name}(): value must fit an uint32")
+        return self._with(name, value)
+
+    def with_value_type(self, value):
+        return self._with("_value_type", LoessValueType(value))
+
+    def with_nx(self, value: int):
+        return self._size("_nx", value)
+
+    def with_ny(self, value: int):
+        return self._size("_ny", value)
+
+    def value_type(self):
+        return self._value_type
+
+    def nx(self) -> int:
+        return self._nx
+
+    def ny(self) -> int:
+        return self._ny
+
+
+fill = types.SimpleNamespace(FirstGuess=FirstGuess, GaussSeidel=GaussSeidel, Multigrid=Multigrid, Loess=Loess,
+                             LoessValueType=LoessValueType)

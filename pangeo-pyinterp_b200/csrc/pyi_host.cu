@@ -1596,6 +1596,60 @@ int pyi_fill_multigrid(void* grid, int dtype, int64_t nx, int64_t ny, const pyi_
   return fill_entry(true, grid, dtype, nx, ny, cfg, mem, iterations, max_residual, stream);
 }
 
+// fill::loess (fill/loess.hpp:207-253).  Host grids are staged through two
+// device copies; everything else happens in pyi_loess.cu.
+int pyi_fill_loess(const void* grid, void* result, int dtype, int64_t nx, int64_t ny,
+                   const pyi_loess_config* cfg, int mem, void* stream) {
+  int st = require_device();
+  if (st != PYI_OK) return st;
+  if (!cfg) return fail(PYI_BAD_ARG, "pyi_fill_loess: missing argument");
+  if (dtype != PYI_F32 && dtype != PYI_F64) {
+    return fail(PYI_BAD_ARG, "pyi_fill_loess: grid must be float32 or float64");
+  }
+  if (nx < 0 || ny < 0 || (nx > 0 && ny > int64_t{0x7fffffff} / nx)) {
+    return fail(PYI_BAD_SHAPE, "pyi_fill_loess: invalid grid shape (at most 2^31 - 1 cells)");
+  }
+  if (cfg->half_x < 1 || cfg->half_y < 1) {
+    return fail(PYI_BAD_ARG, "nx and ny must be at least 1");  // fill/helpers.hpp:117-124
+  }
+  if (cfg->first_guess != PYI_FIRST_GUESS_ZERO && cfg->first_guess != PYI_FIRST_GUESS_ZONAL_AVERAGE) {
+    return fail(PYI_BAD_ARG, "Unsupported first guess method: " + std::to_string(cfg->first_guess));
+  }
+  if (cfg->value_type < PYI_LOESS_UNDEFINED || cfg->value_type > PYI_LOESS_ALL) {
+    return fail(PYI_BAD_ARG, "pyi_fill_loess: unknown value type");
+  }
+  if (nx == 0 || ny == 0) return PYI_OK;
+  if (!grid || !result) return fail(PYI_BAD_SHAPE, "pyi_fill_loess: missing grid");
+  auto run = [&](const void* in, void* out, cudaStream_t s) {
+    return pyi::fill_loess(in, out, dtype, nx, ny, cfg->half_x, cfg->half_y, cfg->value_type,
+                           cfg->first_guess, cfg->is_periodic != 0, cfg->max_iterations, cfg->epsilon, s);
+  };
+  int dev = 0;
+  PYI_CUDA(cudaGetDevice(&dev));
+  keep_pool_cached(dev);
+  if (mem == PYI_MEM_DEVICE) {
+    cudaError_t e = run(grid, result, static_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) return cuda_fail(e, "loess kernels");
+    return PYI_OK;
+  }
+  const size_t bytes = static_cast<size_t>(nx) * static_cast<size_t>(ny) * dtype_size(dtype);
+  Lease lease(dev);
+  Workspace& ws = *lease.ws;
+  st = ws.ensure(2 * ((bytes + 255) & ~static_cast<size_t>(255)), 0);
+  if (st != PYI_OK) return st;
+  Slot& slot = ws.slot[0];
+  slot.busy = true;
+  char* d_in = slot.dev;
+  char* d_out = slot.dev + ((bytes + 255) & ~static_cast<size_t>(255));
+  PYI_CUDA(cudaMemcpyAsync(d_in, grid, bytes, cudaMemcpyHostToDevice, slot.stream));
+  cudaError_t e = run(d_in, d_out, slot.stream);
+  if (e != cudaSuccess) return cuda_fail(e, "loess kernels");
+  PYI_CUDA(cudaMemcpyAsync(result, d_out, bytes, cudaMemcpyDeviceToHost, slot.stream));
+  PYI_CUDA(cudaStreamSynchronize(slot.stream));
+  slot.busy = false;
+  return PYI_OK;
+}
+
 // TemporalAxis::coordinate_repr (math/temporal_axis.hpp:80-83,150-156) =
 // dateutils::datetime64_to_string / timedelta64_to_string
 // (dateutils.hpp:729-812): ISO-8601 text of an int64 in a numpy resolution.

@@ -132,6 +132,11 @@ cudaError_t fill_multigrid(void* grid, int dtype, long long nx, long long ny, in
                            int periodic, unsigned long long max_iterations, double epsilon,
                            unsigned pre_smooth, unsigned post_smooth,
                            unsigned long long* iterations, double* residual, cudaStream_t stream);
+// fill::loess on a device-resident row-major (nx, ny) grid (pyi_loess.cu): `result`
+// receives the processed copy, `in` is left untouched; dtype PYI_F32 / PYI_F64
+cudaError_t fill_loess(const void* in, void* result, int dtype, long long nx, long long ny,
+                       unsigned half_x, unsigned half_y, int value_type, int first_guess, int periodic,
+                       unsigned max_iterations, double epsilon, cudaStream_t stream);
 // six-node spline derivative weights of an axis (pyi_bicubicw.cuh)
 cudaError_t launch_spline6_weights(double step, double* out12, cudaStream_t stream);
 // plane-major copy of a 3-D / 4-D grid: [x][y][z][u] -> [z][u][x][y]

@@ -4,7 +4,9 @@
 * :func:`gauss_seidel` -- ``core.fill.gauss_seidel``
   (cxx/include/pyinterp/fill/gauss_seidel.hpp:166-211);
 * :func:`multigrid` -- ``core.fill.multigrid``
-  (cxx/include/pyinterp/fill/multi_grid.hpp:276-334).
+  (cxx/include/pyinterp/fill/multi_grid.hpp:276-334);
+* :func:`loess` -- ``core.fill.loess``
+  (cxx/include/pyinterp/fill/loess.hpp:207-253), which returns a new array.
 
 Grids are filled IN PLACE like the reference: numpy arrays are staged through
 the device, CUDA tensors (torch, or anything exposing
@@ -23,12 +25,20 @@ from . import _abi
 from .config import fill as _cfg
 from .core import _device_view, _is_torch_cuda, _lib, _np_ptr
 
-__all__ = ["gauss_seidel", "multigrid"]
+__all__ = ["gauss_seidel", "multigrid", "loess"]
 
 #: pyinterp/fill.py:47-50
 _FIRST_GUESS_MAP = {
     "zero": _cfg.FirstGuess.ZERO,
     "zonal_average": _cfg.FirstGuess.ZONAL_AVERAGE,
+}
+
+
+#: pyinterp/fill.py:53-57
+_LOESS_VALUE_TYPE_MAP = {
+    "all": _cfg.LoessValueType.ALL,
+    "defined": _cfg.LoessValueType.DEFINED,
+    "undefined": _cfg.LoessValueType.UNDEFINED,
 }
 
 
@@ -123,3 +133,51 @@ def multigrid(grid, config=None, *, max_iterations: int | None = None, epsilon: 
     pod = _abi.FillConfig(int(config.first_guess()), int(config.is_periodic()), config.max_iterations(),
                           config.epsilon(), 1.0, config.pre_smooth(), config.post_smooth())
     return _run("pyi_fill_multigrid", "multigrid", grid, pod)
+
+
+def loess(data, config=None, *, nx: int | None = None, ny: int | None = None, max_iterations: int | None = None,
+          epsilon: float | None = None, value_type: str | None = None, first_guess: str | None = None,
+          is_periodic: bool | None = None, num_threads: int | None = None):
+    """``pyinterp.fill.loess`` (pyinterp/fill.py:240-305): a NEW array in which
+    every processed cell (``value_type``: the undefined ones, the defined ones,
+    or all) is the tri-cube weighted mean of the defined values in its
+    ``(2 nx + 1) x (2 ny + 1)`` window; ``max_iterations == 1`` is the single
+    pass, larger values iterate from the first guess until the largest change is
+    below ``epsilon``.  numpy in, numpy out; a CUDA tensor gives a CUDA tensor."""
+    if config is None:
+        config = _build_config(
+            _cfg.Loess,
+            {"nx": ("with_nx", None), "ny": ("with_ny", None), "max_iterations": ("with_max_iterations", None),
+             "epsilon": ("with_epsilon", None), "value_type": ("with_value_type", _LOESS_VALUE_TYPE_MAP),
+             "first_guess": ("with_first_guess", _FIRST_GUESS_MAP), "is_periodic": ("with_is_periodic", None),
+             "num_threads": ("with_num_threads", None)},
+            nx=nx, ny=ny, max_iterations=max_iterations, epsilon=epsilon, value_type=value_type,
+            first_guess=first_guess, is_periodic=is_periodic, num_threads=num_threads)
+    elif not isinstance(config, _cfg.Loess):
+        raise TypeError("config must be a config.fill.Loess")
+    if config.max_iterations() >= 2 ** 32:
+        raise TypeError("max_iterations must fit an uint32")
+    pod = _abi.LoessConfig(int(config.first_guess()), int(config.is_periodic()), int(config.max_iterations()),
+                           config.nx(), config.ny(), int(config.value_type()), config.epsilon())
+    data = _device_view(data)
+    lib = _lib()
+    if _is_torch_cuda(data):
+        import torch
+        if data.dim() != 2 or data.dtype not in (torch.float32, torch.float64):
+            raise TypeError("data must be a 2-D float32 or float64 array")
+        src = data.contiguous()
+        out = torch.empty_like(src)
+        dt = _abi.DTYPES["float64" if src.dtype == torch.float64 else "float32"]
+        with torch.cuda.device(src.device):
+            st = lib.pyi_fill_loess(src.data_ptr(), out.data_ptr(), dt, src.shape[0], src.shape[1], C.byref(pod),
+                                    _abi.PYI_MEM_DEVICE, torch.cuda.current_stream(src.device).cuda_stream)
+        _abi.check(st, "loess")
+        return out
+    if not isinstance(data, np.ndarray) or data.ndim != 2 or data.dtype not in (np.float32, np.float64):
+        raise TypeError("data must be a 2-D float32 or float64 array")
+    src = np.ascontiguousarray(data)
+    out = np.empty_like(src)
+    st = lib.pyi_fill_loess(_np_ptr(src), _np_ptr(out), _abi.DTYPES[src.dtype.name], src.shape[0], src.shape[1],
+                            C.byref(pod), _abi.PYI_MEM_HOST, None)
+    _abi.check(st, "loess")
+    return out

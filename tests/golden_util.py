@@ -180,6 +180,19 @@ CASES["fill_mg_f32_zero_reflect"] = dict(kind="fill", algo="multigrid", shape=(4
 CASES["fill_mg_f64_odd_sizes"] = dict(kind="fill", algo="multigrid", shape=(77, 41), dtype="float64", seed=66,
                                       first_guess="zonal_average", is_periodic=True, max_iterations=6,
                                       epsilon=0.0, pre_smooth=2, post_smooth=1)
+# fill::loess: the whole processed grid of the reference build is the fixture
+CASES["fill_loess_f64_single_pass"] = dict(kind="fill", algo="loess", shape=(72, 36), dtype="float64", seed=67,
+                                           first_guess="zonal_average", is_periodic=True, max_iterations=1,
+                                           epsilon=1e-4, nx=3, ny=3, value_type="undefined")
+CASES["fill_loess_f32_iterative_reflect"] = dict(kind="fill", algo="loess", shape=(45, 31), dtype="float32", seed=68,
+                                                 first_guess="zonal_average", is_periodic=False, max_iterations=25,
+                                                 epsilon=1e-3, nx=2, ny=4, value_type="undefined")
+CASES["fill_loess_f64_all_iterative"] = dict(kind="fill", algo="loess", shape=(37, 23), dtype="float64", seed=69,
+                                             first_guess="zero", is_periodic=True, max_iterations=6,
+                                             epsilon=0.0, nx=5, ny=2, value_type="all")
+CASES["fill_loess_f64_defined"] = dict(kind="fill", algo="loess", shape=(40, 30), dtype="float64", seed=70,
+                                       first_guess="zonal_average", is_periodic=True, max_iterations=1,
+                                       epsilon=1e-4, nx=4, ny=4, value_type="defined")
 VECTOR_CASES = sorted(CASES)
 PORT_CASES = [k for k in VECTOR_CASES if not CASES[k].get("ref_only")]
 
@@ -269,6 +282,9 @@ def run_case_on_oracle(o, name, d):
     c = CASES[name]
     if c["kind"] == "fill":
         g = d["grid"].copy()
+        if c["algo"] == "loess":
+            return {"out": o.fill_loess(g, c["nx"], c["ny"], c["value_type"], c["first_guess"], c["is_periodic"],
+                                        c["max_iterations"], c["epsilon"])}
         if c["algo"] == "gauss_seidel":
             its, res = o.fill_gauss_seidel(g, c["first_guess"], c["is_periodic"], c["max_iterations"],
                                            c["epsilon"], c["relaxation"])
@@ -316,6 +332,8 @@ def run_case_on_gpu(pyi, name, d):
         g = d["grid"].copy()
         kw = dict(first_guess=c["first_guess"], is_periodic=c["is_periodic"],
                   max_iterations=c["max_iterations"], epsilon=c["epsilon"])
+        if c["algo"] == "loess":
+            return {"out": pyi.fill.loess(g, nx=c["nx"], ny=c["ny"], value_type=c["value_type"], **kw)}
         if c["algo"] == "gauss_seidel":
             its, res = pyi.fill.gauss_seidel(g, relaxation=c["relaxation"], **kw)
         else:

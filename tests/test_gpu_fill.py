@@ -137,3 +137,40 @@ def test_multigrid_config_device_tensor_and_errors(pyi, orc_best):
     assert its == 0 and res == float(np.finfo(np.float32).max)  # multi_grid.hpp:311
     with pytest.raises(TypeError):
         pyi.fill.multigrid(np.zeros((3, 3)), pyi.config.fill.GaussSeidel())
+
+
+@pytest.mark.parametrize("dtype", ["float64", "float32"])
+def test_loess_bit_identical(pyi, dtype):
+    """fill::loess on the device against the CPU oracle: single pass and
+    iterated, the three value types, periodic or mirrored x, both first guesses,
+    host arrays and device tensors, at toy sizes and on the 0.25 degree grid."""
+    import orc
+    import torch
+    import golden_util as gu
+    o = orc.Oracle("reference") if orc.available("reference") else orc.Oracle("port")
+    for k, shape in enumerate([(40, 30), (37, 23), (1, 9), (9, 1), (2, 2), (64, 5), (1, 1), (130, 67)]):
+        g0 = gu.fill_field(shape, dtype, 700 + k, blobs=2)
+        for vt in ("undefined", "defined", "all"):
+            for fg, per, its, eps, hx, hy in (("zonal_average", True, 1, 1e-4, 3, 3), ("zero", False, 4, 0.0, 2, 5),
+                                              ("zonal_average", False, 30, 1e-3, 4, 1), ("zonal_average", True, 0, 1e-4, 3, 3)):
+                want = o.fill_loess(g0, hx, hy, vt, fg, per, its, eps)
+                kw = dict(nx=hx, ny=hy, value_type=vt, first_guess=fg, is_periodic=per, max_iterations=its, epsilon=eps)
+                keep = g0.copy()
+                got = pyi.fill.loess(g0, **kw)
+                assert np.array_equal(g0, keep, equal_nan=True)  # the input is left untouched
+                assert got.dtype == g0.dtype and np.array_equal(got, want, equal_nan=True), (shape, vt, fg, per, its)
+        dev = pyi.fill.loess(torch.from_numpy(g0).cuda(), nx=3, ny=3, max_iterations=5)
+        assert dev.is_cuda and np.array_equal(dev.cpu().numpy(), o.fill_loess(g0, 3, 3, max_iterations=5), equal_nan=True)
+    s = pyi.synthetic
+    g = s.field(s.lon_axis_values(), s.lat_axis_values()).astype(dtype)
+    rng = np.random.default_rng(4)
+    g[rng.random(g.shape) < 0.2] = np.nan
+    g[200:260, 300:380] = np.nan
+    for its in (1, 4):
+        want = o.fill_loess(g, 5, 5, "undefined", "zonal_average", True, its, 1e-6, num_threads=0)
+        got = pyi.fill.loess(g, nx=5, ny=5, max_iterations=its, epsilon=1e-6)
+        assert np.array_equal(got, want, equal_nan=True)
+    with pytest.raises(ValueError, match="at least 1"):
+        pyi.fill.loess(g, nx=0)
+    with pytest.raises(TypeError):
+        pyi.fill.loess(g.astype(np.int32))

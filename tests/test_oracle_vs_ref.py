@@ -375,3 +375,24 @@ def test_fill_multigrid_port_vs_ref(port, ref, dtype):
     for o in (port, ref):
         g = np.arange(12, dtype=dtype).reshape(3, 4)
         assert o.fill_multigrid(g.copy()) == (0, 0.0)
+
+
+@pytest.mark.parametrize("dtype", ["float64", "float32"])
+def test_fill_loess_port_vs_ref(port, ref, dtype):
+    """fill::loess (fill/loess.hpp:207-253): the C restatement's processed grid
+    equals the reference build's bit for bit -- single pass and iterated, the
+    three value types, periodic or mirrored x, both first guesses (the zonal
+    average is a SEQUENTIAL sum in storage order in the reference build),
+    windows larger than the grid, threaded or not."""
+    for k, shape in enumerate([(40, 30), (37, 23), (1, 9), (9, 1), (2, 2), (5, 64), (64, 5), (1, 1), (130, 67)]):
+        g0 = gu.fill_field(shape, dtype, 500 + k, blobs=2)
+        for vt in ("undefined", "defined", "all"):
+            for fg, per, its, eps, hx, hy in (("zonal_average", True, 1, 1e-4, 3, 3), ("zero", False, 4, 0.0, 2, 5),
+                                              ("zonal_average", False, 30, 1e-3, 4, 1), ("zonal_average", True, 0, 1e-4, 3, 3)):
+                a = ref.fill_loess(g0, hx, hy, vt, fg, per, its, eps, num_threads=3)
+                b = port.fill_loess(g0, hx, hy, vt, fg, per, its, eps)
+                assert np.array_equal(a, b, equal_nan=True), (shape, vt, fg, per, its)
+    for o in (port, ref):
+        g = np.full((6, 5), np.nan, dtype=dtype)
+        assert np.isnan(o.fill_loess(g, max_iterations=1)).all()      # nothing to average: cells keep their value
+        assert not o.fill_loess(g, max_iterations=3).any()            # iterative: the first guess (0) is kept
