@@ -195,11 +195,12 @@ cudaError_t loess_typed(const T* in, T* result, long long nx, long long ny, unsi
   if (max_iterations == 1) return pass(in, in);  // single pass (loess.hpp:213-216)
   // iterative filling (loess.hpp:218-250)
   char* scratch = nullptr;
-  e = cudaMallocAsync(reinterpret_cast<void**>(&scratch), bytes + 64, stream);
+  const size_t padded = (bytes + 15) & ~static_cast<size_t>(15);  // the two scalars behind the copy stay aligned
+  e = cudaMallocAsync(reinterpret_cast<void**>(&scratch), padded + 64, stream);
   if (e != cudaSuccess) return e;
   T* previous = reinterpret_cast<T*>(scratch);
-  T* fill_value = reinterpret_cast<T*>(scratch + bytes);
-  unsigned long long* max_bits = reinterpret_cast<unsigned long long*>(scratch + bytes + 16);
+  T* fill_value = reinterpret_cast<T*>(scratch + padded);
+  unsigned long long* max_bits = reinterpret_cast<unsigned long long*>(scratch + padded + 16);
   auto finish = [&](cudaError_t status) {
     const cudaError_t freed = cudaFreeAsync(scratch, stream);
     return status != cudaSuccess ? status : freed;
