@@ -111,7 +111,8 @@ typedef enum pyi_first_guess {
  * weights (bilinear), precomputed spline-derivative weights (bicubic 6 x 6):
  * values within 1e-12 (float64) / 1e-5 (float32) relative of the reference,
  * NaN positions identical.  PYI_VALUES_DEFAULT: tolerance where a tolerance
- * kernel exists and the axes are well conditioned for it, else exact; the
+ * kernel exists, the axes are well conditioned for it and the launch is large
+ * enough to pay for its extra launches (bilinear: 2^22 points), else exact; the
  * environment variables PYINTERP_B200_BILINEAR / PYINTERP_B200_BICUBIC
  * (= "exact" | "tolerance") change what DEFAULT means for the process. */
 typedef enum pyi_value_mode {

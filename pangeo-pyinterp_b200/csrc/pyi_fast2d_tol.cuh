@@ -48,17 +48,45 @@
 
 namespace pyi {
 
-// Irregular ascending y: the exact bracket of pyi_fast2d.cuh, weight through the
-// staged reciprocal spacings.
-__device__ __forceinline__ void tol_irregular(const DAxis& a, const double* __restrict__ sp,
-                                              const double* __restrict__ sinv,
-                                              const int* __restrict__ slut, double c, int& k,
-                                              double& t, bool& safe) {
-  bool ok = sane(c);
-  const RegBracket b = bracket_irregular(a, sp, slut, ok ? c : a.min, ok);
-  k = b.k;
-  t = __dmul_rn(b.dl, sinv[k]);
-  safe = safe && ok;
+// Irregular ascending y without period.  Shared-memory lookups share the L1TEX
+// data pipe with the cell gather (ncu, round 2: the first version of this path
+// kept that pipe 87 % busy with a 4-byte bin table, a scan over the points, the
+// node pair and the reciprocal spacing: seven loads per point), so the tables
+// are packed for two 16-byte loads and one 8-byte load per point:
+//   bin table  {first node of the bin (or +inf), its index j, nodes in the bin}
+//   cell table {node(k), node(k+1)}, and 1 / (node(k+1) - node(k))
+// The bins are the host's uniform-bin table (pyi_axis_host.hpp: build_lut, whose
+// bin() is monotone in c), merged 2^shift at a time so that the tables fit.
+// k = (number of nodes <= c) - 1: with at most one node in the bin that is
+// j or j - 1 by one comparison; fuller bins are scanned.  The bracket is then
+// verified against the nodes themselves, as everywhere else.
+struct TolBin {
+  double node;
+  int j, count;
+};
+constexpr int kTolMaxBins = 1500;
+
+__device__ __forceinline__ void tol_irregular(const DAxis& a, const TolBin* __restrict__ sbin,
+                                              const double2* __restrict__ scell,
+                                              const double* __restrict__ sinv, int shift, double c,
+                                              int& k, double& t, bool& safe) {
+  const double f = __dmul_rn(__dsub_rn(c, a.lut_min), a.lut_inv);
+  int bin = __double2int_rd(f);  // saturating; NaN -> 0 and fails the checks below
+  const bool in_table = sane(c) && static_cast<unsigned>(bin) < static_cast<unsigned>(a.lut_bins);
+  bin = in_table ? bin : 0;
+  const TolBin e = sbin[bin >> shift];
+  int kk = c >= e.node ? e.j : e.j - 1;
+  if (e.count > 1) {  // several nodes in the (merged) bin: last one that is <= c
+    kk = e.j - 1;
+    for (int j = e.j; j < e.j + e.count && scell[j].x <= c; ++j) kk = j;
+  }
+  const bool ok = in_table && static_cast<unsigned>(kk) < static_cast<unsigned>(a.n - 1);
+  kk = ok ? kk : 0;
+  const double2 nodes = scell[kk];
+  const double dl = __dsub_rn(c, nodes.x);
+  k = kk;
+  t = __dmul_rn(dl, sinv[kk]);
+  safe = safe && ok && !negative(dl) && c < nodes.y;
 }
 
 template <int PTS>
@@ -93,19 +121,37 @@ struct VecIO<4> {
 template <bool PER, int XM, int YM, int PTS, int MINB, bool PREFETCH>
 __global__ void __launch_bounds__(kFastThreads, MINB)
 bilinear2d_tol_kernel(const __grid_constant__ GeoParams p) {
-  __shared__ double s_points[YM == 0 ? kFastMaxIrregular : 1];
-  __shared__ double s_inv[YM == 0 ? kFastMaxIrregular : 1];
-  __shared__ int s_lut[YM == 0 ? kFastMaxLut : 1];
+  // irregular y: packed tables in dynamic shared memory (sized by the launcher)
+  extern __shared__ __align__(16) unsigned char s_raw[];
+  const int ny_ = p.ax[1].n;
+  int shift = 0;
+  TolBin* s_bin = reinterpret_cast<TolBin*>(s_raw);
+  double2* s_cell = nullptr;
+  double* s_inv = nullptr;
   if (YM == 0) {
+    while (((p.ax[1].lut_bins - 1) >> shift) + 1 > kTolMaxBins) ++shift;
+    const int nb = ((p.ax[1].lut_bins - 1) >> shift) + 1;
+    s_cell = reinterpret_cast<double2*>(s_raw + static_cast<size_t>(nb) * sizeof(TolBin));
+    s_inv = reinterpret_cast<double*>(s_cell + ny_);
     const double* gp = static_cast<const double*>(p.ax[1].points);
-    const int ny = p.ax[1].n;
-    for (int i = threadIdx.x; i < ny; i += blockDim.x) {
+    const int* lut = p.ax[1].lut;
+    for (int i = threadIdx.x; i < ny_; i += blockDim.x) {
       const double a = __ldg(gp + i);
-      s_points[i] = a;
+      const double b = i + 1 < ny_ ? __ldg(gp + i + 1) : a;
+      s_cell[i] = make_double2(a, b);
       // reciprocal spacing of cell i (the last entry is never addressed)
-      s_inv[i] = i + 1 < ny ? __ddiv_rn(1.0, __dsub_rn(__ldg(gp + i + 1), a)) : 0.0;
+      s_inv[i] = i + 1 < ny_ ? __ddiv_rn(1.0, __dsub_rn(b, a)) : 0.0;
     }
-    for (int i = threadIdx.x; i <= p.ax[1].lut_bins; i += blockDim.x) s_lut[i] = __ldg(p.ax[1].lut + i);
+    for (int i = threadIdx.x; i < nb; i += blockDim.x) {
+      const int lo = __ldg(lut + (i << shift));
+      const int last = min((i + 1) << shift, p.ax[1].lut_bins);
+      const int hi = __ldg(lut + last);
+      TolBin e;
+      e.j = lo;
+      e.count = hi - lo;
+      e.node = (hi > lo && lo < ny_) ? __ldg(gp + lo) : CUDART_INF;
+      s_bin[i] = e;
+    }
     __syncthreads();
   }
   const DAxis& ax = p.ax[0];
@@ -151,7 +197,7 @@ bilinear2d_tol_kernel(const __grid_constant__ GeoParams p) {
       int kx, ky;
       tol_regular<XM, PER>(ax, c, x[i], jf, kx, t[i], s);
       if (YM == 0) {
-        tol_irregular(ay, s_points, s_inv, s_lut, y[i], ky, u[i], s);
+        tol_irregular(ay, s_bin, s_cell, s_inv, shift, y[i], ky, u[i], s);
       } else {
         tol_regular<YM, false>(ay, y[i], y[i], 0.0, ky, u[i], s);
       }
@@ -232,9 +278,12 @@ static int bilinear_default_mode() {
 // Tuning variant: PYI_TOL_VARIANT = <points per thread: 2|4><min blocks per SM: 2..5>[n]
 // ("n": no register prefetch); read per launch so that one process can sweep them
 static void tol2d_variant(int& pts, int& minb, bool& prefetch) {
-  pts = 2;  // round-2 sweeps on B200 (profiles/r2_k1_sweep*.txt): 2 points x 5 blocks, no prefetch
-  minb = 5;
-  prefetch = false;
+  // round-2 sweeps on three B200 boxes (profiles/r2_k1_sweep*.txt): the variants
+  // within 5 % of the best change from box to box (25n: 188 / 165 Gpts/s, 24: 146 /
+  // 184); 2 points x 3 blocks with register prefetch gave 181 / 181
+  pts = 2;
+  minb = 3;
+  prefetch = true;
   const char* e = std::getenv("PYI_TOL_VARIANT");
   if (e && (e[0] == '2' || e[0] == '4') && e[1] >= '2' && e[1] <= '5') {
     pts = e[0] - '0';
@@ -246,6 +295,13 @@ static void tol2d_variant(int& pts, int& minb, bool& prefetch) {
 static bool tol2d_eligible(const GeoParams& p) {
   const int mode = p.value_mode == PYI_VALUES_DEFAULT ? bilinear_default_mode() : p.value_mode;
   if (mode != PYI_VALUES_TOLERANCE) return false;
+  // small launches are launch bound (three launches and a memset here, one for
+  // the bit-identical kernel): below 2^22 points DEFAULT means exact
+  // (PYINTERP_B200_BILINEAR=tolerance forces the tolerance kernel at any size)
+  const char* forced = std::getenv("PYINTERP_B200_BILINEAR");
+  if (p.value_mode == PYI_VALUES_DEFAULT && p.n < (1LL << 22) && !(forced != nullptr && forced[0] == 't')) {
+    return false;
+  }
   if (p.dtype != PYI_F64 && p.dtype != PYI_I64 && p.dtype != PYI_U64) return false;  // float64 results
   if (!fast2d_eligible(p)) return false;
   if (!p.ax[0].tol_ok) return false;
@@ -270,14 +326,22 @@ static void launch_tol2d_v(const GeoParams& p, cudaStream_t stream) {
     prefetch = false;
   }
   const int blocks = grid_for((p.n + pts - 1) / pts, kFastThreads, minb);
+  // irregular y: bin table + node pairs + reciprocal spacings (at most 47.5 KB)
+  size_t smem = 0;
+  if (YM == 0) {
+    int shift = 0;
+    while (((p.ax[1].lut_bins - 1) >> shift) + 1 > kTolMaxBins) ++shift;
+    smem = static_cast<size_t>(((p.ax[1].lut_bins - 1) >> shift) + 1) * sizeof(TolBin) +
+           static_cast<size_t>(p.ax[1].n) * 24;
+  }
   if constexpr (!kSweep) {
-    bilinear2d_tol_kernel<PER, XM, YM, 2, 4, false><<<blocks, kFastThreads, 0, stream>>>(p);
+    bilinear2d_tol_kernel<PER, XM, YM, 2, 4, false><<<blocks, kFastThreads, smem, stream>>>(p);
     return;
   } else {
 #define PYI_LAUNCH(P, B)                                                                        \
   do {                                                                                          \
-    if (prefetch) bilinear2d_tol_kernel<PER, XM, YM, P, B, true><<<blocks, kFastThreads, 0, stream>>>(p); \
-    else bilinear2d_tol_kernel<PER, XM, YM, P, B, false><<<blocks, kFastThreads, 0, stream>>>(p);         \
+    if (prefetch) bilinear2d_tol_kernel<PER, XM, YM, P, B, true><<<blocks, kFastThreads, smem, stream>>>(p); \
+    else bilinear2d_tol_kernel<PER, XM, YM, P, B, false><<<blocks, kFastThreads, smem, stream>>>(p);         \
   } while (0)
   if (pts == 2) {
     switch (minb) {

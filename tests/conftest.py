@@ -58,8 +58,7 @@ def bilinear_mode(request, monkeypatch):
     reciprocal weights, values within the north-star 1e-12) and the
     bit-identical one (PYINTERP_B200_BILINEAR=exact, pyi_fast2d.cuh).  Every
     other kernel is bit-identical in both modes."""
-    if request.param == "exact":
-        monkeypatch.setenv("PYINTERP_B200_BILINEAR", "exact")
-    else:
-        monkeypatch.delenv("PYINTERP_B200_BILINEAR", raising=False)
+    # "tolerance" in the environment also lifts the size threshold below which
+    # the default mode picks the (launch-cheaper) bit-identical kernel
+    monkeypatch.setenv("PYINTERP_B200_BILINEAR", request.param)
     return request.param
