@@ -40,10 +40,15 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 BYTES_PER_POINT = {"bilinear": 24, "bilinear_irrlat": 24, "bicubic": 24, "trivariate": 60, "quadrivariate": 100,
+                   # the other half of the geometric matrix: idw on the 2-D grid, bilinear on a float64 3-D grid
+                   # (x, y, z 24 + out 8 + 8 corners x 8 = 96)
+                   "idw": 24, "trivariate_f64": 96,
                    # K6: streams only; the windows are compute / L2 work
                    "c_spline2d": 24, "bicubic3d": 28}
 # windowed workloads: fitting model of the public API
 WINDOWED = {"bicubic": "bicubic", "c_spline2d": "c_spline", "bicubic3d": "bicubic"}
+# geometric workloads: spatial method of the public API (default bilinear)
+GEOMETRIC = {"idw": "idw"}
 METRIC = "Mpoints/s"
 
 
@@ -64,7 +69,8 @@ def parse():
 
 
 def default_points(workload: str) -> int:
-    return {"bilinear": 1_000_000_000, "bilinear_irrlat": 1_000_000_000, "bicubic": 100_000_000, "trivariate": 100_000_000,
+    return {"bilinear": 1_000_000_000, "bilinear_irrlat": 1_000_000_000, "idw": 100_000_000,
+            "trivariate_f64": 100_000_000, "bicubic": 100_000_000, "trivariate": 100_000_000,
             "quadrivariate": 100_000_000, "c_spline2d": 20_000_000, "bicubic3d": 20_000_000}[workload]
 
 
@@ -99,8 +105,12 @@ def build_host_case(workload: str):
     lon, lat = syn.lon_axis_values(), syn.lat_axis_values()
     if workload == "bilinear_irrlat":  # BASELINE configs[4]: irregular latitude axis
         lat = syn.irregular_lat_values()
-    if workload in ("bilinear", "bilinear_irrlat", "bicubic", "c_spline2d"):
+    if workload in ("bilinear", "bilinear_irrlat", "bicubic", "c_spline2d", "idw"):
         return dict(nd=2, lon=lon, lat=lat, grid=syn.field(lon, lat), dtype="f64")
+    if workload == "trivariate_f64":
+        t = syn.time_axis_values(120)
+        return dict(nd=3, lon=lon, lat=lat, time=t, grid=syn.field(lon, lat, nz=120, dtype="float64", noise=0.0),
+                    dtype="f64")
     if workload in ("trivariate", "bicubic3d"):
         t = syn.time_axis_values(365)
         return dict(nd=3, lon=lon, lat=lat, time=t, grid=syn.field(lon, lat, nz=365, dtype="float32", noise=0.0),
@@ -119,6 +129,8 @@ def host_queries(case, n, seed):
 def workload_name(workload, n):
     shape = {"bilinear": "bivariate bilinear f64 Grid2D 1440x720 circular lon",
              "bilinear_irrlat": "bivariate bilinear f64 Grid2D 1440x720 circular lon, irregular (Gaussian-like) latitude",
+             "idw": "bivariate inverse distance weighting (exp 2) f64 Grid2D 1440x720 circular lon",
+             "trivariate_f64": "trivariate bilinear f64 Grid3D 1440x720x120 int64 TemporalAxis",
              "bicubic": "bivariate bicubic (6x6 window) f64 Grid2D 1440x720 circular lon",
              "trivariate": "trivariate bilinear f32 Grid3D 1440x720x365 int64 TemporalAxis",
              "c_spline2d": "bivariate windowed c_spline (6x6 window) f64 Grid2D 1440x720 circular lon",
@@ -149,7 +161,7 @@ def cpu_run(case, workload, q, threads=0):
             out, _ = o.windowed_nd(axes, case["grid"], *qq, method=WINDOWED[workload], num_threads=threads,
                                    stateless=kind != "reference")  # the C port has the stateless form only
         else:
-            out, _ = o.geometric(axes, case["grid"], *qq, num_threads=threads)
+            out, _ = o.geometric(axes, case["grid"], *qq, method={"idw": 1}.get(workload, 0), num_threads=threads)
         return out, time.perf_counter() - t0
 
     return kind, run
@@ -356,7 +368,12 @@ def oracle_guard(env, pyi, case, grid, workload):
     """Parity guard, on EVERY rank: a fixed 1e6-point sub-chunk of the workload
     (seed 1001 + rank) against the CPU oracle before any number is recorded."""
     nd = case["nd"]
-    q = host_queries(case, 1_000_000, 1001 + env.rank)
+    # 2-D bilinear: from 2^22 points per launch the default value mode runs the tolerance kernel -- the
+    # kernel the timed region runs -- so the guard is that large and goes through the device entry
+    # (one launch; the host path would cut it into chunks below the threshold)
+    big = workload in ("bilinear", "bilinear_irrlat")
+    n_guard = 4_200_000 if big else 1_000_000
+    q = host_queries(case, n_guard, 1001 + env.rank)
     kind, run = cpu_run(case, workload, None)
     if workload in WINDOWED:
         sys.path.insert(0, os.path.join(ROOT, "oracle"))
@@ -376,8 +393,15 @@ def oracle_guard(env, pyi, case, grid, workload):
     if nd >= 3:
         qq[2] = qq[2].view("datetime64[ns]")
     api = {2: pyi.bivariate, 3: pyi.trivariate, 4: pyi.quadrivariate}[nd]
-    got = api(grid, *qq, WINDOWED.get(workload, "bilinear"))
+    if big:
+        dq = [env.torch.from_numpy(np.ascontiguousarray(a)).to(env.dev) for a in q]
+        got = api(grid, *dq, "bilinear").cpu().numpy()
+    else:
+        got = api(grid, *qq, WINDOWED.get(workload, GEOMETRIC.get(workload, "bilinear")))
     tol = 1e-12 if got.dtype == np.float64 else 1e-5
+    if workload in GEOMETRIC:
+        # idw goes through sin / cos / pow, correctly rounded on neither side: the slack of tests/test_gpu_parity.py
+        tol *= 20
     nan_ok = np.array_equal(np.isnan(got), np.isnan(want))
     m = ~np.isnan(want)
     err = np.abs(got[m].astype(np.float64) - want[m].astype(np.float64))
@@ -385,7 +409,7 @@ def oracle_guard(env, pyi, case, grid, workload):
     if env.min_over_ranks(1.0 if ok else 0.0) < 1.0:
         raise SystemExit(f"bench.py: parity check of '{workload}' against the CPU oracle FAILED on a rank; "
                          "no number recorded")
-    return {"checked": "ok", "points": 1_000_000, "ranks": env.world, "oracle": kind,
+    return {"checked": "ok", "points": n_guard, "ranks": env.world, "oracle": kind,
             "bit_identical_fraction": float((err == 0).mean()) if err.size else 1.0,
             "max_abs_err": float(err.max()) if err.size else 0.0}
 
@@ -413,7 +437,8 @@ def make_config(pyi, case, workload):
     nd = case["nd"]
     if workload in WINDOWED:
         return getattr({2: pyi.windowed.Bivariate, 3: pyi.windowed.Trivariate}[nd], WINDOWED[workload])()
-    return {2: pyi.geometric.Bivariate, 3: pyi.geometric.Trivariate, 4: pyi.geometric.Quadrivariate}[nd].bilinear()
+    cls = {2: pyi.geometric.Bivariate, 3: pyi.geometric.Trivariate, 4: pyi.geometric.Quadrivariate}[nd]
+    return getattr(cls, GEOMETRIC.get(workload, "bilinear"))()
 
 
 def time_device(env, pyi, grid, coords, cfg, steps, warmup, sampler=None):
@@ -537,7 +562,7 @@ def main():
     # points; the other ranks idle at the barrier.  `ranks` is the other way to
     # feed N GPUs: every torchrun rank calling with its own ne points.
     api = {2: pyi.bivariate, 3: pyi.trivariate, 4: pyi.quadrivariate}[nd]
-    method = WINDOWED.get(args.workload, "bilinear")
+    method = WINDOWED.get(args.workload, GEOMETRIC.get(args.workload, "bilinear"))
     grid._resident = True
     ne = int(min(args.e2e_points if world == 1 else args.e2e_points / 2, n))
     e2e_steps = max(3, min(args.steps, 10))
@@ -605,6 +630,7 @@ def main():
         del grid
         torch.cuda.empty_cache()
         sub = [("bicubic", 100_000_000, ()), ("trivariate", 100_000_000, ()), ("quadrivariate", 100_000_000, ()),
+               ("idw", 100_000_000, ()), ("trivariate_f64", 100_000_000, ()),
                ("bilinear_irrlat", 1_000_000_000, (1_000_000, 10_000_000, 100_000_000, 1_000_000_000))]
         for name, m, sweep in sub:
             m = int(min(m, args.points)) if args.points else m

@@ -303,7 +303,7 @@ static bool tol2d_eligible(const GeoParams& p) {
     return false;
   }
   if (p.dtype != PYI_F64 && p.dtype != PYI_I64 && p.dtype != PYI_U64) return false;  // float64 results
-  if (!fast2d_eligible(p)) return false;
+  if (p.method != PYI_BILINEAR || !fast2d_eligible(p)) return false;
   if (!p.ax[0].tol_ok) return false;
   if (p.ax[1].kind == 0 && !p.ax[1].tol_ok) return false;
   const uintptr_t align = reinterpret_cast<uintptr_t>(p.x) | reinterpret_cast<uintptr_t>(p.y) |

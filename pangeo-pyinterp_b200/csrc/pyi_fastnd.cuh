@@ -1,7 +1,7 @@
 // pyi_fastnd.cuh -- K2 / K3 fast path: trivariate / quadrivariate with the
-// bilinear spatial evaluator and linear or nearest z / u interpolation, float
-// results (every grid dtype except f64 / i64 / u64), ascending axes, reading
-// the cell-packed copy.  Included by pyi_kernels.cu after pyi_fast2d.cuh.
+// bilinear / idw / nearest spatial evaluator and linear or nearest z / u
+// interpolation, float or double results (every grid dtype), ascending axes,
+// reading the cell-packed copy.  Included by pyi_kernels.cu after pyi_fast2d.cuh.
 //
 // What is computed is trivariate_single / quadrivariate_single
 // (pybind/geometric/trivariate.hpp:47-123, quadrivariate.hpp:50-148) with
@@ -63,40 +63,47 @@ __device__ __forceinline__ RegBracket bracket_f64(const DAxis& a, const double* 
   return bracket_regular<false>(a, c, 0.0, ok);
 }
 
-// linear<Z, float> / nearest<Z, float> on a verified bracket z0 <= z < z1.
-// f64 axis: dl = fl(z - z0), c1 = z1.
-__device__ __forceinline__ float axis_mix_f64(int method, double z, const RegBracket& b, float y0,
-                                              float y1) {
+// linear<Z, R> / nearest<Z, R> (interpolate/linear.hpp:22-33, nearest.hpp:21-32)
+// on a verified bracket z0 <= z < z1.  f64 axis: dl = fl(z - z0), c1 = z1.
+template <typename R>
+__device__ __forceinline__ R div_ieee_r(R a, R b);
+template <>
+__device__ __forceinline__ float div_ieee_r<float>(float a, float b) { return __fdiv_rn(a, b); }
+template <>
+__device__ __forceinline__ double div_ieee_r<double>(double a, double b) { return __ddiv_rn(a, b); }
+
+template <typename R>
+__device__ __forceinline__ R axis_mix_f64(int method, double z, const RegBracket& b, R y0, R y1) {
   if (method == PYI_AXIS_NEAREST) {
     // |z0 - z| < |z1 - z| ? y0 : y1 ; |z0 - z| == dl exactly
     return b.dl < __dsub_rn(b.c1, z) ? y0 : y1;
   }
-  const float dx = static_cast<float>(__dsub_rn(b.c1, b.c0));
-  const float t = __fdiv_rn(static_cast<float>(b.dl), dx);
+  const R dx = static_cast<R>(__dsub_rn(b.c1, b.c0));
+  const R t = div_ieee_r<R>(static_cast<R>(b.dl), dx);
   return y0 + t * (y1 - y0);
 }
 // i64 axis: d0 = z - z0 and step = z1 - z0, exact
-__device__ __forceinline__ float axis_mix_i64(int method, long long d0, long long step, float y0,
-                                              float y1) {
+template <typename R>
+__device__ __forceinline__ R axis_mix_i64(int method, long long d0, long long step, R y0, R y1) {
   if (method == PYI_AXIS_NEAREST) {
     return d0 < step - d0 ? y0 : y1;
   }
-  const float dx = static_cast<float>(step);
-  const float t = __fdiv_rn(static_cast<float>(d0), dx);
+  const R dx = static_cast<R>(step);
+  const R t = div_ieee_r<R>(static_cast<R>(d0), dx);
   return y0 + t * (y1 - y0);
 }
 
 // The generic code, out of line (reads the packed copy with its own loads).
-template <int ND, bool ZI64>
-__device__ __noinline__ float slow_point_nd(const GeoParams& p, double x, double y,
-                                            typename ZOf<ZI64>::type z, double u, long long index) {
-  float res;
-  const int bad = geometric_eval<ND, -1, float, ZI64, true>(p, x, y, z, u, res);
+template <int ND, bool ZI64, typename R>
+__device__ __noinline__ R slow_point_nd(const GeoParams& p, double x, double y,
+                                        typename ZOf<ZI64>::type z, double u, long long index) {
+  R res;
+  const int bad = geometric_eval<ND, -1, R, ZI64, true>(p, x, y, z, u, res);
   if (bad < 0) return res;
   if (p.bounds_error) {
     atomicMin(p.oob_key, (static_cast<unsigned long long>(p.index_base + index) << 2) | bad);
   }
-  return CUDART_NAN_F;
+  return RT<R>::nan();
 }
 
 __device__ __forceinline__ void stage_axis(const DAxis& a, double* sp, int* slut) {
@@ -108,8 +115,8 @@ __device__ __forceinline__ void stage_axis(const DAxis& a, double* sp, int* slut
 
 // One point per thread and iteration; whole warps iterate together so that
 // lane pairs can share the line requests of 64-byte cells (4-D).
-template <int ND, bool ZI64>
-__global__ void __launch_bounds__(kFastThreads, 3)
+template <int ND, bool ZI64, typename R, bool BIL>
+__global__ void __launch_bounds__(kFastThreads, (sizeof(R) == 4 && BIL) ? 3 : 2)
 bilinear_nd_fast_kernel(const __grid_constant__ GeoParams p) {
   using Z = typename ZOf<ZI64>::type;
   __shared__ double s_y[kFastMaxIrregular];
@@ -129,7 +136,8 @@ bilinear_nd_fast_kernel(const __grid_constant__ GeoParams p) {
   const bool per = ax.period != 0.0;
   const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
   const unsigned lane = threadIdx.x & 31u;
-  float* __restrict__ out = static_cast<float*>(p.out);
+  R* __restrict__ out = static_cast<R*>(p.out);
+  constexpr bool bilinear = BIL;  // idw / nearest (trigonometry) are compiled apart
   const Z* __restrict__ zs = static_cast<const Z*>(p.z);
 
   long long k = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -160,7 +168,7 @@ bilinear_nd_fast_kernel(const __grid_constant__ GeoParams p) {
       const double cn = norm_fast(x, ax.min, ax.period, ax.inv_period);
       c = outside_period(ax, x) ? cn : x;
     }
-    const RegBracket bx = per ? bracket_regular<true>(ax, c, ax.seam_c1_f32, ok)
+    const RegBracket bx = per ? bracket_regular<true>(ax, c, sizeof(R) == 8 ? ax.seam_c1 : ax.seam_c1_f32, ok)
                               : bracket_regular<false>(ax, c, 0.0, ok);
     const RegBracket by = bracket_f64(ay, s_y, s_ylut, y, ok);
     RegBracket bz;
@@ -178,10 +186,9 @@ bilinear_nd_fast_kernel(const __grid_constant__ GeoParams p) {
       ok = ok && sane(u);
       bu = bracket_f64(p.ax[3], s_u, s_ulut, u, ok);
     }
-    // float results: x1 is normalised against the float-rounded x0
-    // (bivariate.hpp:78-89); the seam constant already is, any other cell
-    // needing it leaves the hot path
-    const float x0 = static_cast<float>(bx.c0);
+    // x1 is normalised against the R-rounded x0 (bivariate.hpp:78-89); the
+    // seam constant already is, any other cell needing it leaves the hot path
+    const R x0 = static_cast<R>(bx.c0);
     const double x0d = static_cast<double>(x0);
     const double hi0 = per ? __dadd_rn(x0d, ax.period) : 0.0;
     if (per) ok = ok && (bx.k == ax.n - 1 || !(bx.c1 >= hi0 || bx.c1 < x0d));
@@ -191,11 +198,11 @@ bilinear_nd_fast_kernel(const __grid_constant__ GeoParams p) {
     r.cell = (static_cast<long long>(bx.k) * ay.n + by.k) * az.n + kz;
     if (ND >= 4) r.cell = r.cell * p.ax[3].n + bu.k;
     if (!ok) r.cell = 0;  // always a legal address
-    Corners<ND, float> q;
-    if constexpr (ND >= 4) {
-      geo_gather_group<ND, float>(p, r, q);
+    Corners<ND, R> q;
+    if constexpr (Corners<ND, R>::BYTES >= 64) {  // 64- / 128-byte cells: one request per lane group
+      geo_gather_group<ND, R>(p, r, q);
     } else {
-      geo_gather_packed<ND, float>(p, r, q);
+      geo_gather_packed<ND, R>(p, r, q);
     }
     // ---- weights (Bilinear::evaluate, geometric/bivariate.hpp:110-132) -------
     double px = x;
@@ -204,31 +211,46 @@ bilinear_nd_fast_kernel(const __grid_constant__ GeoParams p) {
       const double pn = norm_fast(x, x0d, ax.period, ax.inv_period);
       px = out2 ? pn : x;
     }
-    const float y0 = static_cast<float>(by.c0);
-    const float dx = static_cast<float>(bx.c1) - x0;
-    const float dy = static_cast<float>(by.c1) - y0;
-    const float t = __fdiv_rn(static_cast<float>(px) - x0, dx);
-    const float w = __fdiv_rn(static_cast<float>(y) - y0, dy);
-    const float omt = 1.0f - t;
-    const float omw = 1.0f - w;
-    constexpr int NU = Corners<ND, float>::NU;
-    float sp[2][NU];
+    const R y0 = static_cast<R>(by.c0);
+    const R x1 = static_cast<R>(bx.c1);
+    const R y1 = static_cast<R>(by.c1);
+    const R pxr = static_cast<R>(px);
+    const R pyr = static_cast<R>(y);
+    constexpr int NU = Corners<ND, R>::NU;
+    R sp[2][NU];
+    if (bilinear) {
+      const R dx = x1 - x0;
+      const R dy = y1 - y0;
+      const R t = div_ieee_r<R>(pxr - x0, dx);
+      const R w = div_ieee_r<R>(pyr - y0, dy);
+      const R omt = R(1) - t;
+      const R omw = R(1) - w;
 #pragma unroll
-    for (int cz = 0; cz < 2; ++cz) {
+      for (int cz = 0; cz < 2; ++cz) {
 #pragma unroll
-      for (int d = 0; d < NU; ++d) {
-        sp[cz][d] = omt * (omw * q.q[cz][d][0][0] + w * q.q[cz][d][0][1]) +
-                    t * (omw * q.q[cz][d][1][0] + w * q.q[cz][d][1][1]);
+        for (int d = 0; d < NU; ++d) {
+          sp[cz][d] = omt * (omw * q.q[cz][d][0][0] + w * q.q[cz][d][0][1]) +
+                      t * (omw * q.q[cz][d][1][0] + w * q.q[cz][d][1][1]);
+        }
+      }
+    } else {  // idw / nearest on the same verified corners (geometric/bivariate.hpp:189-302)
+#pragma unroll
+      for (int cz = 0; cz < 2; ++cz) {
+#pragma unroll
+        for (int d = 0; d < NU; ++d) {
+          sp[cz][d] = eval_spatial<R>(p.method, p.idw_exp, pxr, pyr, x0, y0, x1, y1, q.q[cz][d][0][0],
+                                      q.q[cz][d][0][1], q.q[cz][d][1][0], q.q[cz][d][1][1]);
+        }
       }
     }
-    float along[NU];
+    R along[NU];
 #pragma unroll
     for (int d = 0; d < NU; ++d) {
-      along[d] = ZI64 ? axis_mix_i64(p.z_method, dz, az.istep, sp[0][d], sp[1][d])
-                      : axis_mix_f64(p.z_method, static_cast<double>(z), bz, sp[0][d], sp[1][d]);
+      along[d] = ZI64 ? axis_mix_i64<R>(p.z_method, dz, az.istep, sp[0][d], sp[1][d])
+                      : axis_mix_f64<R>(p.z_method, static_cast<double>(z), bz, sp[0][d], sp[1][d]);
     }
-    float res = along[0];
-    if (ND >= 4) res = axis_mix_f64(p.u_method, u, bu, along[0], along[NU - 1]);
+    R res = along[0];
+    if (ND >= 4) res = axis_mix_f64<R>(p.u_method, u, bu, along[0], along[NU - 1]);
     if (!ok && active) {
       // a finite coordinate beyond the ends of an axis that does not wrap (or
       // a NaT / out-of-range time) cannot be bracketed: NaN; with bounds_error,
@@ -242,7 +264,7 @@ bilinear_nd_fast_kernel(const __grid_constant__ GeoParams p) {
         far = far || (sane(static_cast<double>(z)) && beyond_ends(az, static_cast<double>(z)));
       }
       if (ND >= 4) far = far || (sane(u) && beyond_ends(p.ax[3], u));
-      res = (far && !p.bounds_error) ? CUDART_NAN_F : slow_point_nd<ND, ZI64>(p, x, y, z, u, k);
+      res = (far && !p.bounds_error) ? RT<R>::nan() : slow_point_nd<ND, ZI64, R>(p, x, y, z, u, k);
     }
     if (active) __stcs(out + k, res);
     k = kn;
@@ -263,8 +285,7 @@ static bool axis_f64_fast(const DAxis& a, int max_irregular) {
 }
 
 static bool fastnd_eligible(const GeoParams& p) {
-  if (p.ndim < 3 || p.method != PYI_BILINEAR || p.packed == nullptr) return false;
-  if (p.dtype == PYI_F64 || p.dtype == PYI_I64 || p.dtype == PYI_U64) return false;  // float results
+  if (p.ndim < 3 || p.packed == nullptr) return false;
   const DAxis& ax = p.ax[0];
   if (!ax.fast_ok || ax.coord_i64 || ax.kind != 0 || ax.n < 2) return false;
   if (ax.period != 0.0 && !(ax.period > 0.0 && ax.step < ax.period)) return false;
@@ -279,15 +300,28 @@ static bool fastnd_eligible(const GeoParams& p) {
   return true;
 }
 
-static cudaError_t launch_fastnd(const GeoParams& p, cudaStream_t stream) {
-  const int blocks = grid_for(p.n, kFastThreads, 3);
+template <typename R, bool BIL>
+static void launch_fastnd_r(const GeoParams& p, cudaStream_t stream) {
+  const int blocks = grid_for(p.n, kFastThreads, (sizeof(R) == 4 && BIL) ? 3 : 2);
   const bool zi64 = p.ax[2].coord_i64 != 0;
   if (p.ndim == 3) {
-    if (zi64) bilinear_nd_fast_kernel<3, true><<<blocks, kFastThreads, 0, stream>>>(p);
-    else bilinear_nd_fast_kernel<3, false><<<blocks, kFastThreads, 0, stream>>>(p);
+    if (zi64) bilinear_nd_fast_kernel<3, true, R, BIL><<<blocks, kFastThreads, 0, stream>>>(p);
+    else bilinear_nd_fast_kernel<3, false, R, BIL><<<blocks, kFastThreads, 0, stream>>>(p);
   } else {
-    if (zi64) bilinear_nd_fast_kernel<4, true><<<blocks, kFastThreads, 0, stream>>>(p);
-    else bilinear_nd_fast_kernel<4, false><<<blocks, kFastThreads, 0, stream>>>(p);
+    if (zi64) bilinear_nd_fast_kernel<4, true, R, BIL><<<blocks, kFastThreads, 0, stream>>>(p);
+    else bilinear_nd_fast_kernel<4, false, R, BIL><<<blocks, kFastThreads, 0, stream>>>(p);
+  }
+}
+
+static cudaError_t launch_fastnd(const GeoParams& p, cudaStream_t stream) {
+  const bool r64 = p.dtype == PYI_F64 || p.dtype == PYI_I64 || p.dtype == PYI_U64;
+  const bool bil = p.method == PYI_BILINEAR;
+  if (r64) {
+    if (bil) launch_fastnd_r<double, true>(p, stream);
+    else launch_fastnd_r<double, false>(p, stream);
+  } else {
+    if (bil) launch_fastnd_r<float, true>(p, stream);
+    else launch_fastnd_r<float, false>(p, stream);
   }
   g_launches.fetch_add(1);
   return cudaGetLastError();
