@@ -49,44 +49,53 @@
 namespace pyi {
 
 // Irregular ascending y without period.  Shared-memory lookups share the L1TEX
-// data pipe with the cell gather (ncu, round 2: the first version of this path
-// kept that pipe 87 % busy with a 4-byte bin table, a scan over the points, the
-// node pair and the reciprocal spacing: seven loads per point), so the tables
-// are packed for two 16-byte loads and one 8-byte load per point:
-//   bin table  {first node of the bin (or +inf), its index j, nodes in the bin}
-//   cell table {node(k), node(k+1)}, and 1 / (node(k+1) - node(k))
-// The bins are the host's uniform-bin table (pyi_axis_host.hpp: build_lut, whose
-// bin() is monotone in c), merged 2^shift at a time so that the tables fit.
-// k = (number of nodes <= c) - 1: with at most one node in the bin that is
-// j or j - 1 by one comparison; fuller bins are scanned.  The bracket is then
-// verified against the nodes themselves, as everywhere else.
-struct TolBin {
-  double node;
-  int j, count;
-};
-constexpr int kTolMaxBins = 1500;
+// data pipe with the cell gather, and random 16-byte reads conflict on banks
+// (ncu, round 2: 33 shared wavefronts per warp of points for three loads, 23 of
+// them bank conflicts; the pipe 98 % busy), so a point reads as little as it can:
+//   bin table   2 bytes: j = nodes below the bin, flags "a node inside" /
+//               "several nodes inside" (bins: the host's uniform-bin table,
+//               pyi_axis_host.hpp: build_lut, whose bin() is monotone in c,
+//               merged 2^shift at a time when the axis has more than 1500 bins)
+//   cell table  16 bytes: node(k) and 1 / (node(k+1) - node(k))
+// k = (number of nodes <= c) - 1.  A bin without a node gives k = j - 1 at once;
+// with one node inside, cell j is read first and cell j - 1 only by the lanes
+// whose c lies below node(j); fuller bins are scanned.  Every decision is an
+// exact comparison with a node value and bin() is the host's own expression, so
+// the bracket is the reference's (container.hpp:382-404 + axis.hpp:745-766 on an
+// ascending axis); c >= node(k) is still verified from the cell that was read.
+constexpr int kTolMaxBins = 6000;
+constexpr unsigned short kTolOne = 0x8000, kTolMany = 0x4000;
 
-__device__ __forceinline__ void tol_irregular(const DAxis& a, const TolBin* __restrict__ sbin,
-                                              const double2* __restrict__ scell,
-                                              const double* __restrict__ sinv, int shift, double c,
+__device__ __forceinline__ void tol_irregular(const DAxis& a, const unsigned short* __restrict__ sbin,
+                                              const double2* __restrict__ scell, int shift, double c,
                                               int& k, double& t, bool& safe) {
   const double f = __dmul_rn(__dsub_rn(c, a.lut_min), a.lut_inv);
   int bin = __double2int_rd(f);  // saturating; NaN -> 0 and fails the checks below
   const bool in_table = sane(c) && static_cast<unsigned>(bin) < static_cast<unsigned>(a.lut_bins);
   bin = in_table ? bin : 0;
-  const TolBin e = sbin[bin >> shift];
-  int kk = c >= e.node ? e.j : e.j - 1;
-  if (e.count > 1) {  // several nodes in the (merged) bin: last one that is <= c
-    kk = e.j - 1;
-    for (int j = e.j; j < e.j + e.count && scell[j].x <= c; ++j) kk = j;
+  const unsigned e = sbin[bin >> shift];
+  const int j = static_cast<int>(e & 0x3fffu);
+  const bool inside = (e & kTolOne) != 0;
+  int kk = inside ? j : j - 1;
+  kk = min(max(kk, 0), a.n - 1);
+  double2 cell = scell[kk];  // {node(kk), 1 / spacing}
+  bool below = inside && c < cell.x;  // the node of the bin is above c: cell j - 1
+  if (e & kTolMany) {  // several nodes in the bin: the last one that is <= c
+    below = false;
+    kk = j - 1;
+    for (int m = j; m < a.n && scell[m].x <= c; ++m) kk = m;
+    kk = min(max(kk, 0), a.n - 1);
+    cell = scell[kk];  // (c >= lut_min = node(0) inside the table: kk >= 0 here)
+  }
+  if (below) {
+    kk = j - 1;
+    cell = scell[max(kk, 0)];
   }
   const bool ok = in_table && static_cast<unsigned>(kk) < static_cast<unsigned>(a.n - 1);
-  kk = ok ? kk : 0;
-  const double2 nodes = scell[kk];
-  const double dl = __dsub_rn(c, nodes.x);
-  k = kk;
-  t = __dmul_rn(dl, sinv[kk]);
-  safe = safe && ok && !negative(dl) && c < nodes.y;
+  const double dl = __dsub_rn(c, cell.x);
+  k = ok ? kk : 0;
+  t = __dmul_rn(dl, cell.y);
+  safe = safe && ok && !negative(dl);
 }
 
 template <int PTS>
@@ -125,32 +134,25 @@ bilinear2d_tol_kernel(const __grid_constant__ GeoParams p) {
   extern __shared__ __align__(16) unsigned char s_raw[];
   const int ny_ = p.ax[1].n;
   int shift = 0;
-  TolBin* s_bin = reinterpret_cast<TolBin*>(s_raw);
-  double2* s_cell = nullptr;
-  double* s_inv = nullptr;
+  double2* s_cell = reinterpret_cast<double2*>(s_raw);
+  unsigned short* s_bin = nullptr;
   if (YM == 0) {
     while (((p.ax[1].lut_bins - 1) >> shift) + 1 > kTolMaxBins) ++shift;
     const int nb = ((p.ax[1].lut_bins - 1) >> shift) + 1;
-    s_cell = reinterpret_cast<double2*>(s_raw + static_cast<size_t>(nb) * sizeof(TolBin));
-    s_inv = reinterpret_cast<double*>(s_cell + ny_);
+    s_bin = reinterpret_cast<unsigned short*>(s_cell + ny_);
     const double* gp = static_cast<const double*>(p.ax[1].points);
     const int* lut = p.ax[1].lut;
     for (int i = threadIdx.x; i < ny_; i += blockDim.x) {
       const double a = __ldg(gp + i);
-      const double b = i + 1 < ny_ ? __ldg(gp + i + 1) : a;
-      s_cell[i] = make_double2(a, b);
-      // reciprocal spacing of cell i (the last entry is never addressed)
-      s_inv[i] = i + 1 < ny_ ? __ddiv_rn(1.0, __dsub_rn(b, a)) : 0.0;
+      // reciprocal spacing of cell i (the last entry is never used: cell n - 1 is not a bracket)
+      const double inv = i + 1 < ny_ ? __ddiv_rn(1.0, __dsub_rn(__ldg(gp + i + 1), a)) : 0.0;
+      s_cell[i] = make_double2(a, inv);
     }
     for (int i = threadIdx.x; i < nb; i += blockDim.x) {
       const int lo = __ldg(lut + (i << shift));
       const int last = min((i + 1) << shift, p.ax[1].lut_bins);
-      const int hi = __ldg(lut + last);
-      TolBin e;
-      e.j = lo;
-      e.count = hi - lo;
-      e.node = (hi > lo && lo < ny_) ? __ldg(gp + lo) : CUDART_INF;
-      s_bin[i] = e;
+      const int count = __ldg(lut + last) - lo;
+      s_bin[i] = static_cast<unsigned short>(lo | (count == 1 ? kTolOne : 0) | (count > 1 ? kTolMany : 0));
     }
     __syncthreads();
   }
@@ -197,7 +199,7 @@ bilinear2d_tol_kernel(const __grid_constant__ GeoParams p) {
       int kx, ky;
       tol_regular<XM, PER>(ax, c, x[i], jf, kx, t[i], s);
       if (YM == 0) {
-        tol_irregular(ay, s_bin, s_cell, s_inv, shift, y[i], ky, u[i], s);
+        tol_irregular(ay, s_bin, s_cell, shift, y[i], ky, u[i], s);
       } else {
         tol_regular<YM, false>(ay, y[i], y[i], 0.0, ky, u[i], s);
       }
@@ -326,13 +328,13 @@ static void launch_tol2d_v(const GeoParams& p, cudaStream_t stream) {
     prefetch = false;
   }
   const int blocks = grid_for((p.n + pts - 1) / pts, kFastThreads, minb);
-  // irregular y: bin table + node pairs + reciprocal spacings (at most 47.5 KB)
+  // irregular y: cell table (16 bytes per node) + bin table (2 bytes per bin): at most 28 KB
   size_t smem = 0;
   if (YM == 0) {
     int shift = 0;
     while (((p.ax[1].lut_bins - 1) >> shift) + 1 > kTolMaxBins) ++shift;
-    smem = static_cast<size_t>(((p.ax[1].lut_bins - 1) >> shift) + 1) * sizeof(TolBin) +
-           static_cast<size_t>(p.ax[1].n) * 24;
+    smem = static_cast<size_t>(p.ax[1].n) * 16 +
+           static_cast<size_t>(((p.ax[1].lut_bins - 1) >> shift) + 1) * sizeof(unsigned short);
   }
   if constexpr (!kSweep) {
     bilinear2d_tol_kernel<PER, XM, YM, 2, 4, false><<<blocks, kFastThreads, smem, stream>>>(p);
