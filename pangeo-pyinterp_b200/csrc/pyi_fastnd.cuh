@@ -115,8 +115,8 @@ __device__ __forceinline__ void stage_axis(const DAxis& a, double* sp, int* slut
 
 // One point per thread and iteration; whole warps iterate together so that
 // lane pairs can share the line requests of 64-byte cells (4-D).
-template <int ND, bool ZI64, typename R, bool BIL>
-__global__ void __launch_bounds__(kFastThreads, (sizeof(R) == 4 && BIL) ? 3 : 2)
+template <int ND, bool ZI64, typename R, bool BIL, int MINB = 2>
+__global__ void __launch_bounds__(kFastThreads, MINB)
 bilinear_nd_fast_kernel(const __grid_constant__ GeoParams p) {
   using Z = typename ZOf<ZI64>::type;
   __shared__ double s_y[kFastMaxIrregular];
@@ -302,8 +302,28 @@ static bool fastnd_eligible(const GeoParams& p) {
 
 template <typename R, bool BIL>
 static void launch_fastnd_r(const GeoParams& p, cudaStream_t stream) {
-  const int blocks = grid_for(p.n, kFastThreads, (sizeof(R) == 4 && BIL) ? 3 : 2);
   const bool zi64 = p.ax[2].coord_i64 != 0;
+  if constexpr (sizeof(R) == 4 && BIL) {
+    // tuning knob for the benchmark configurations (float results, int64 time): PYI_ND_MINB = 2 .. 5
+    const char* e = std::getenv("PYI_ND_MINB");
+    // (round-2 sweep, 1e8 points: trivariate 32.9 / 32.1 / 31.4 / 30.9 and quadrivariate 29.4 / 26.9 /
+    // 27.7 / 27.4 Gpts/s at 2 / 3 / 4 / 5 blocks: the DRAM request rate is the limit, not occupancy)
+    if (e && zi64 && e[0] >= '3' && e[0] <= '5') {
+      const int b = e[0] - '0';
+      const int nb = grid_for(p.n, kFastThreads, b);
+      if (p.ndim == 3) {
+        if (b == 3) bilinear_nd_fast_kernel<3, true, R, BIL, 3><<<nb, kFastThreads, 0, stream>>>(p);
+        else if (b == 4) bilinear_nd_fast_kernel<3, true, R, BIL, 4><<<nb, kFastThreads, 0, stream>>>(p);
+        else bilinear_nd_fast_kernel<3, true, R, BIL, 5><<<nb, kFastThreads, 0, stream>>>(p);
+      } else {
+        if (b == 3) bilinear_nd_fast_kernel<4, true, R, BIL, 3><<<nb, kFastThreads, 0, stream>>>(p);
+        else if (b == 4) bilinear_nd_fast_kernel<4, true, R, BIL, 4><<<nb, kFastThreads, 0, stream>>>(p);
+        else bilinear_nd_fast_kernel<4, true, R, BIL, 5><<<nb, kFastThreads, 0, stream>>>(p);
+      }
+      return;
+    }
+  }
+  const int blocks = grid_for(p.n, kFastThreads, 2);
   if (p.ndim == 3) {
     if (zi64) bilinear_nd_fast_kernel<3, true, R, BIL><<<blocks, kFastThreads, 0, stream>>>(p);
     else bilinear_nd_fast_kernel<3, false, R, BIL><<<blocks, kFastThreads, 0, stream>>>(p);
