@@ -632,6 +632,10 @@ def main():
         sub = [("bicubic", 100_000_000, ()), ("trivariate", 100_000_000, ()), ("quadrivariate", 100_000_000, ()),
                ("idw", 100_000_000, ()), ("trivariate_f64", 100_000_000, ()),
                ("bilinear_irrlat", 1_000_000_000, (1_000_000, 10_000_000, 100_000_000, 1_000_000_000))]
+        if world >= 8 and not args.points:
+            # configs[4] sweeps to 1e10 points in total: 1.25e9 per GPU on eight of them (30 GB of streams each)
+            top = -(-10_000_000_000 // world)
+            sub[-1] = ("bilinear_irrlat", top, (1_000_000, 10_000_000, 100_000_000, 1_000_000_000, top))
         for name, m, sweep in sub:
             m = int(min(m, args.points)) if args.points else m
             try:
