@@ -59,7 +59,9 @@ def _host_result(n: int, dtype) -> np.ndarray:
     (through torch's caching host allocator) so that the device-to-host copy is
     a direct DMA instead of a staged one; the numpy array keeps the allocation
     alive."""
-    if n >= (1 << 20):
+    # (from 2^17 elements: a fresh pageable array of 1 MB or more costs more in first-touch
+    # page faults than the whole device round trip; torch caches page-locked blocks by size class)
+    if n >= (1 << 17):
         try:
             import torch
             t = torch.empty(n, dtype=torch.float64 if np.dtype(dtype) == np.float64 else torch.float32,
