@@ -154,3 +154,40 @@ def test_bilinear_at_baseline_size(pyi, synthetic, orc_best, lat_kind, bilinear_
         assert np.all(err <= 1e-12 * np.maximum(np.abs(want[m]), 1.0)), err.max()
         # the tolerance kernel differs by rounding only: a few ulp of the cell values
         assert err.max() < 1e-14
+
+
+def test_every_query_on_a_node_overflows_the_queues(pyi, synthetic, orc_best, monkeypatch):
+    """Regridding onto the grid's own lattice: EVERY query sits exactly on a node,
+    which the tolerance kernels hand to their redo queues.  4.5e6 points overflow
+    the 2^20-entry queues: bilinear must then be recomputed by the bit-identical
+    kernel launched behind the queue (device entry, one launch), bicubic by the
+    scanning redo pass -- both bit-identical to the oracle."""
+    import torch
+    monkeypatch.setenv("PYINTERP_B200_BILINEAR", "tolerance")
+    lon, lat = synthetic.lon_axis_values(), synthetic.lat_axis_values()
+    g = synthetic.field(lon, lat)
+    g[::37, ::11] = np.nan
+    rng = np.random.default_rng(41)
+    n = 4_500_000
+    x = lon[rng.integers(0, lon.size, n)] + 360.0 * rng.integers(-1, 2, n)
+    y = lat[rng.integers(0, lat.size, n)]
+    oaxes = [orc_best.axis(lon, period=360.0), orc_best.axis(lat)]
+    grid = pyi.Grid(pyi.Axis(lon, period=360.0), pyi.Axis(lat), g, resident=True)
+    xd, yd = torch.from_numpy(x).cuda(), torch.from_numpy(y).cuda()
+    want, _ = orc_best.geometric(oaxes, g, x, y, method=0, num_threads=0)
+    got = pyi.bivariate(grid, xd, yd).cpu().numpy()
+    assert np.array_equal(got, want, equal_nan=True)
+    # a mix: half of the points on nodes (overflow), half random (the exact kernel recomputes them all)
+    x[::2] = rng.uniform(-180.0, 540.0, x[::2].size)
+    y[::2] = rng.uniform(-90.0, 90.0, y[::2].size)
+    want, _ = orc_best.geometric(oaxes, g, x, y, method=0, num_threads=0)
+    got = pyi.bivariate(grid, torch.from_numpy(x).cuda(), torch.from_numpy(y).cuda()).cpu().numpy()
+    assert np.array_equal(got, want, equal_nan=True)
+    # bicubic: every point tagged -> the redo pass scans
+    m = 1_500_000
+    xb = lon[rng.integers(0, lon.size, m)]
+    yb = lat[rng.integers(3, lat.size - 3, m)]
+    want, _ = orc_best.windowed2d(oaxes, g, xb, yb, num_threads=0, stateless=True)
+    got = pyi.bivariate(grid, torch.from_numpy(xb).cuda(), torch.from_numpy(yb).cuda(), "bicubic").cpu().numpy()
+    assert np.array_equal(got, want, equal_nan=True)
+    assert np.isfinite(want).mean() > 0.5
