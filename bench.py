@@ -480,6 +480,45 @@ def time_device(env, pyi, grid, coords, cfg, steps, warmup, sampler=None):
     return total_ms, kernel_ms, int(launches), finite
 
 
+def live_copy_probe(torch, n_gpus, in_bytes_per_point, out_bytes_per_point, points):
+    """Copy-only ceiling of the host-fed path ON THIS BOX, measured in this run: the bytes one step of the
+    end-to-end call moves (inputs up, results down), `points` split over the first n_gpus devices, 8M-point
+    chunks on three streams per device, page-locked buffers, no kernel.  Returns GB/s (best of 3)."""
+    per = -(-points // n_gpus)
+    chunk = 1 << 23
+    state = []
+    for d in range(n_gpus):
+        with torch.cuda.device(d):
+            hin = torch.empty(per * in_bytes_per_point, dtype=torch.uint8, pin_memory=True)
+            hout = torch.empty(per * out_bytes_per_point, dtype=torch.uint8, pin_memory=True)
+            streams = [torch.cuda.Stream(device=d) for _ in range(3)]
+            dev = [torch.empty(chunk * (in_bytes_per_point + out_bytes_per_point), dtype=torch.uint8,
+                               device=f"cuda:{d}") for _ in range(3)]
+            state.append((hin, hout, streams, dev))
+    best = float("inf")
+    for _ in range(4):
+        for d in range(n_gpus):
+            torch.cuda.synchronize(d)
+        t0 = time.perf_counter()
+        for d, (hin, hout, streams, dev) in enumerate(state):
+            k = 0
+            for b in range(0, per, chunk):
+                c = min(chunk, per - b)
+                s = streams[k % 3]
+                with torch.cuda.stream(s):
+                    dev[k % 3][: c * in_bytes_per_point].copy_(hin[b * in_bytes_per_point:(b + c) * in_bytes_per_point],
+                                                               non_blocking=True)
+                    o0 = chunk * in_bytes_per_point
+                    hout[b * out_bytes_per_point:(b + c) * out_bytes_per_point].copy_(
+                        dev[k % 3][o0:o0 + c * out_bytes_per_point], non_blocking=True)
+                k += 1
+        for d in range(n_gpus):
+            torch.cuda.synchronize(d)
+        best = min(best, time.perf_counter() - t0)
+    del state
+    return per * n_gpus * (in_bytes_per_point + out_bytes_per_point) / best / 1e9
+
+
 def e2e_bound(n_gpus, gbs):
     """Names the limiter of the host-fed path from the committed copy-only probe
     (tools/pcie_probe.cu -> profiles/r2_pcie_probe.json: the best aggregate
@@ -620,8 +659,14 @@ def main():
     pageable = [np.array(h, copy=True) for h in hq] if lead else None
     dt, _ = time_calls(pageable, e2e_steps, active=lead)
     e2e_pageable = total * e2e_steps / dt / 1e6
+    live_probe = None
     if lead:
         pyi.dist.init(1)
+        try:
+            live_probe = live_copy_probe(torch, world, h2d // total, d2h // total, total)
+        except Exception as e:  # the probe is evidence, not the measurement
+            live_probe = f"{type(e).__name__}: {e}"
+    env.cpu_barrier()
     del pageable, hq, r, coords
     torch.cuda.empty_cache()
 
@@ -661,6 +706,8 @@ def main():
                     "how": f"one process, one API call per step, sharded over {world} device(s) inside the C-ABI "
                            "(pyi_dist_init)",
                     "host_link_gbs": e2e_gbs, **e2e_bound(world, e2e_gbs),
+                    "live_probe_gbs": live_probe,
+                    "frac_of_live_probe": (e2e_gbs / live_probe) if isinstance(live_probe, float) else None,
                     "pageable": {"value": e2e_pageable, "unit": METRIC,
                                  "input": "plain numpy arrays, staged through the library's pinned slots"},
                     "ranks": e2e_ranks},

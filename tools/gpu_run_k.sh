@@ -11,7 +11,7 @@ lines=[l for l in open('gpurun_out/k_bench_$N.json')]
 print('stdout lines:', len(lines), 'non-json:', [l[:60] for l in lines if not l.startswith('{')])
 d=json.loads([l for l in lines if l.startswith('{')][-1])
 print('value',d['value'],'frac',d['roofline']['frac'],'parity',d['config']['parity'])
-e=d['e2e']; print('e2e',e['value'],e['host_link_gbs'],e['frac_of_probe'],'pageable',e['pageable']['value'],'ranks',e['ranks'])
+e=d['e2e']; print('e2e',e['value'],e['host_link_gbs'],e['frac_of_probe'],'live',e.get('live_probe_gbs'),e.get('frac_of_live_probe'),'pageable',e['pageable']['value'],'ranks',e['ranks'])
 for k,v in d['secondary'].items():
     if 'error' in v: print(k, v['error']); continue
     print(k, round(v['value']), round(v['roofline']['frac'],4), v['parity']['bit_identical_fraction'], v['parity']['max_abs_err'], v['roofline']['traffic'] is not None)
