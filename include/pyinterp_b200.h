@@ -374,6 +374,24 @@ int pyi_fill_loess(const void *grid, void *result, int dtype, int64_t nx,
                    int64_t ny, const pyi_loess_config *cfg, int mem,
                    void *stream);
 
+/* pyi_fill_loess for callers that may not allocate device memory (code under
+ * CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+ * No counterpart in the reference.
+ * Same arguments, kernels and results (bit for bit) as pyi_fill_loess with
+ * PYI_MEM_DEVICE -- `grid` and `result` are device pointers on the current
+ * device -- but the scratch of the iterative filling (the previous iterate and
+ * two scalars) lives in a static device array of PYI_LOESS_STATIC_MAX_BYTES
+ * (+ 256) bytes that every GPU loading the library holds until exit, and the
+ * call makes no cudaMalloc / cudaFree / cudaMallocAsync nor any allocating
+ * library call.  Grids of more than PYI_LOESS_STATIC_MAX_BYTES bytes
+ * (1 048 576 float64 or 2 097 152 float32 cells) are rejected with
+ * PYI_BAD_SHAPE.  All calls share the array: calls that overlap on one GPU
+ * (two streams, two threads) race and must be serialised by the caller. */
+#define PYI_LOESS_STATIC_MAX_BYTES (8u << 20)
+int pyi_fill_loess_static(const void *grid, void *result, int dtype,
+                          int64_t nx, int64_t ny, const pyi_loess_config *cfg,
+                          void *stream);
+
 /* Reference text "{coord} is out of bounds for axis {x|y|z|u} [{min}, ...,
  * {max}]" (pybind/grid.hpp:367-370). `coord` points to a double or an int64
  * according to the axis. Returns the length written (excluding NUL). */

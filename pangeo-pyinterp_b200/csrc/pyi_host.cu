@@ -1650,6 +1650,45 @@ int pyi_fill_loess(const void* grid, void* result, int dtype, int64_t nx, int64_
   return PYI_OK;
 }
 
+// pyi_fill_loess on device pointers with the scratch in a static device array
+// (pyi_loess.cu): no allocation of any kind on this path -- no workspace, no
+// memory pool, no cudaMallocAsync.  No counterpart in the reference.
+int pyi_fill_loess_static(const void* grid, void* result, int dtype, int64_t nx, int64_t ny,
+                          const pyi_loess_config* cfg, void* stream) {
+  int st = require_device();
+  if (st != PYI_OK) return st;
+  if (!cfg) return fail(PYI_BAD_ARG, "pyi_fill_loess_static: missing argument");
+  if (dtype != PYI_F32 && dtype != PYI_F64) {
+    return fail(PYI_BAD_ARG, "pyi_fill_loess_static: grid must be float32 or float64");
+  }
+  if (nx < 0 || ny < 0 || (nx > 0 && ny > int64_t{0x7fffffff} / nx)) {
+    return fail(PYI_BAD_SHAPE, "pyi_fill_loess_static: invalid grid shape (at most 2^31 - 1 cells)");
+  }
+  const size_t bytes = static_cast<size_t>(nx) * static_cast<size_t>(ny) * dtype_size(dtype);
+  if (bytes > PYI_LOESS_STATIC_MAX_BYTES) {
+    return fail(PYI_BAD_SHAPE, "pyi_fill_loess_static: grid of " + std::to_string(bytes) +
+                                   " bytes exceeds the static scratch of " +
+                                   std::to_string(PYI_LOESS_STATIC_MAX_BYTES) +
+                                   " bytes (use pyi_fill_loess)");
+  }
+  if (cfg->half_x < 1 || cfg->half_y < 1) {
+    return fail(PYI_BAD_ARG, "nx and ny must be at least 1");  // fill/helpers.hpp:117-124
+  }
+  if (cfg->first_guess != PYI_FIRST_GUESS_ZERO && cfg->first_guess != PYI_FIRST_GUESS_ZONAL_AVERAGE) {
+    return fail(PYI_BAD_ARG, "Unsupported first guess method: " + std::to_string(cfg->first_guess));
+  }
+  if (cfg->value_type < PYI_LOESS_UNDEFINED || cfg->value_type > PYI_LOESS_ALL) {
+    return fail(PYI_BAD_ARG, "pyi_fill_loess_static: unknown value type");
+  }
+  if (nx == 0 || ny == 0) return PYI_OK;
+  if (!grid || !result) return fail(PYI_BAD_SHAPE, "pyi_fill_loess_static: missing grid");
+  cudaError_t e = pyi::fill_loess_static(grid, result, dtype, nx, ny, cfg->half_x, cfg->half_y,
+                                         cfg->value_type, cfg->first_guess, cfg->is_periodic != 0,
+                                         cfg->max_iterations, cfg->epsilon, static_cast<cudaStream_t>(stream));
+  if (e != cudaSuccess) return cuda_fail(e, "loess kernels (static scratch)");
+  return PYI_OK;
+}
+
 // TemporalAxis::coordinate_repr (math/temporal_axis.hpp:80-83,150-156) =
 // dateutils::datetime64_to_string / timedelta64_to_string
 // (dateutils.hpp:729-812): ISO-8601 text of an int64 in a numpy resolution.

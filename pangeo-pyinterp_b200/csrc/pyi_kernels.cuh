@@ -137,6 +137,11 @@ cudaError_t fill_multigrid(void* grid, int dtype, long long nx, long long ny, in
 cudaError_t fill_loess(const void* in, void* result, int dtype, long long nx, long long ny,
                        unsigned half_x, unsigned half_y, int value_type, int first_guess, int periodic,
                        unsigned max_iterations, double epsilon, cudaStream_t stream);
+// the same with its scratch in a file-scope device array (pyi_loess.cu): allocates nothing,
+// at most PYI_LOESS_STATIC_MAX_BYTES of grid
+cudaError_t fill_loess_static(const void* in, void* result, int dtype, long long nx, long long ny,
+                              unsigned half_x, unsigned half_y, int value_type, int first_guess, int periodic,
+                              unsigned max_iterations, double epsilon, cudaStream_t stream);
 // six-node spline derivative weights of an axis (pyi_bicubicw.cuh)
 cudaError_t launch_spline6_weights(double step, double* out12, cudaStream_t stream);
 // plane-major copy of a 3-D / 4-D grid: [x][y][z][u] -> [z][u][x][y]

@@ -23,6 +23,7 @@
 // compute_max_difference (:161-172) is a maximum, order independent.
 #include <algorithm>
 #include <cstring>
+#include <mutex>
 #include <vector>
 
 #include "pyi_common.cuh"
@@ -234,6 +235,93 @@ cudaError_t loess_typed(const T* in, T* result, long long nx, long long ny, unsi
   return finish(cudaSuccess);
 }
 
+// ---- the allocation-free variant (pyi_fill_loess_static) -----------------------
+// The iterative filling needs a copy of the previous iterate and two scalars;
+// fill_loess takes them from cudaMallocAsync.  Callers that may not allocate
+// get the same kernels over a file-scope array instead: kLoessStaticBytes for
+// the copy plus 256 bytes for the scalars, resident on every GPU that loads the
+// library until the process exits.  All calls share it.
+constexpr size_t kLoessStaticBytes = PYI_LOESS_STATIC_MAX_BYTES;
+static __device__ __align__(256) unsigned char g_loess_static[kLoessStaticBytes + 256];
+
+constexpr int kLoessStaticDevices = 64;
+std::mutex g_loess_static_mutex;
+unsigned char* g_loess_static_ptr[kLoessStaticDevices] = {};
+
+// The device address of g_loess_static on the CURRENT device (in host code the
+// array's name is only a handle for the runtime): looked up once per device.
+cudaError_t loess_static_address(unsigned char** ptr) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= kLoessStaticDevices) return cudaErrorInvalidDevice;
+  std::lock_guard<std::mutex> lock(g_loess_static_mutex);
+  if (g_loess_static_ptr[dev] == nullptr) {
+    void* address = nullptr;
+    e = cudaGetSymbolAddress(&address, g_loess_static);
+    if (e != cudaSuccess) return e;
+    g_loess_static_ptr[dev] = static_cast<unsigned char*>(address);
+  }
+  *ptr = g_loess_static_ptr[dev];
+  return cudaSuccess;
+}
+
+// loess_typed with its scratch in g_loess_static: same kernels, same order of
+// launches, hence the same bits.  Nothing in the array has to survive between
+// calls and nothing is read before it is written: `previous` is overwritten by
+// the copy that opens every iteration, the fill value by loess_mean_kernel, and
+// the running maximum is cleared at the start of every iteration.
+template <typename T>
+cudaError_t loess_static_typed(const T* in, T* result, long long nx, long long ny, unsigned hx, unsigned hy,
+                               int value_type, int first_guess, int periodic, unsigned max_iterations,
+                               double epsilon, cudaStream_t stream) {
+  const long long cells = nx * ny;
+  const size_t bytes = static_cast<size_t>(cells) * sizeof(T);
+  if (bytes > kLoessStaticBytes) return cudaErrorInvalidValue;  // checked by the caller as well
+  unsigned char* scratch = nullptr;
+  cudaError_t e = loess_static_address(&scratch);
+  if (e != cudaSuccess) return e;
+  T* previous = reinterpret_cast<T*>(scratch);
+  T* fill_value = reinterpret_cast<T*>(scratch + kLoessStaticBytes);
+  unsigned long long* max_bits = reinterpret_cast<unsigned long long*>(scratch + kLoessStaticBytes + 16);
+  const int blocks = grid_for(cells, kThreads, 8);
+  e = cudaMemcpyAsync(result, in, bytes, cudaMemcpyDeviceToDevice, stream);
+  if (e != cudaSuccess) return e;
+  auto pass = [&](const T* values, const T* validity) {
+    loess_pass_kernel<T><<<blocks, kThreads, 0, stream>>>(values, validity, result, nx, ny, hx, hy, periodic,
+                                                          value_type);
+    g_launches.fetch_add(1);
+    return cudaGetLastError();
+  };
+  if (max_iterations == 1) return pass(in, in);
+  if (first_guess == PYI_FIRST_GUESS_ZONAL_AVERAGE) {
+    loess_mean_kernel<T><<<1, kThreads, 0, stream>>>(result, cells, fill_value);
+    loess_guess_kernel<T><<<blocks, kThreads, 0, stream>>>(result, cells, fill_value);
+    g_launches.fetch_add(2);
+  } else {
+    loess_guess_kernel<T><<<blocks, kThreads, 0, stream>>>(result, cells, nullptr);
+    g_launches.fetch_add(1);
+  }
+  e = cudaGetLastError();
+  if (e != cudaSuccess) return e;
+  for (unsigned iter = 0; iter < max_iterations; ++iter) {
+    e = cudaMemcpyAsync(previous, result, bytes, cudaMemcpyDeviceToDevice, stream);
+    if (e == cudaSuccess) e = cudaMemsetAsync(max_bits, 0, sizeof(unsigned long long), stream);
+    if (e == cudaSuccess) e = pass(previous, in);
+    if (e != cudaSuccess) return e;
+    loess_maxdiff_kernel<T><<<blocks, kThreads, 0, stream>>>(result, previous, cells, max_bits);
+    g_launches.fetch_add(1);
+    unsigned long long bits = 0;
+    e = cudaMemcpyAsync(&bits, max_bits, sizeof(bits), cudaMemcpyDeviceToHost, stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
+    if (e != cudaSuccess) return e;
+    double diff;
+    std::memcpy(&diff, &bits, sizeof(diff));
+    if (static_cast<T>(diff) < static_cast<T>(epsilon)) break;
+  }
+  return cudaSuccess;
+}
+
 }  // namespace
 
 cudaError_t fill_loess(const void* in, void* result, int dtype, long long nx, long long ny, unsigned half_x,
@@ -245,6 +333,19 @@ cudaError_t fill_loess(const void* in, void* result, int dtype, long long nx, lo
   }
   return loess_typed<double>(static_cast<const double*>(in), static_cast<double*>(result), nx, ny, half_x,
                              half_y, value_type, first_guess, periodic, max_iterations, epsilon, stream);
+}
+
+cudaError_t fill_loess_static(const void* in, void* result, int dtype, long long nx, long long ny,
+                              unsigned half_x, unsigned half_y, int value_type, int first_guess, int periodic,
+                              unsigned max_iterations, double epsilon, cudaStream_t stream) {
+  if (dtype == PYI_F32) {
+    return loess_static_typed<float>(static_cast<const float*>(in), static_cast<float*>(result), nx, ny,
+                                     half_x, half_y, value_type, first_guess, periodic, max_iterations,
+                                     epsilon, stream);
+  }
+  return loess_static_typed<double>(static_cast<const double*>(in), static_cast<double*>(result), nx, ny,
+                                    half_x, half_y, value_type, first_guess, periodic, max_iterations,
+                                    epsilon, stream);
 }
 
 }  // namespace pyi
