@@ -106,7 +106,7 @@ bicubic_sep_kernel(const __grid_constant__ WinNdParams p) {
     int kx, ky;
     double tx, ty;
     tol_regular<XM, PER>(ax, c, x, jf, kx, tx, safe);
-    tol_regular<YM, false>(ay, y, y, 0.0, ky, ty, safe);
+    tol_regular<YM, false, false>(ay, y, y, 0.0, ky, ty, safe);
     int wx0 = kx - 2;
     const int wy0 = ky - 2;
     bool inside = ky >= 2 && ky + 3 < ny;

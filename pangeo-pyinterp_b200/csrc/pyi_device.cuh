@@ -51,6 +51,12 @@ struct DAxis {
   int32_t tol_xhi;         // periodic axes: exponent field (high word) bound of |x|, 2^28 steps
   double tol_off;          // -(start * inv_step) - 0.5: rint(c * inv_step + tol_off) = floor guess
   double tol_poff;         // -(min * inv_period) - 0.5, periodic axes
+  // A DESCENDING regular f64 axis without period (e.g. latitude 90 -> -90) that
+  // passed the same checks as fast_ok: the kernels that know about it bracket
+  // node(k) > c > node(k+1) by index and swap the two corners (the reference's
+  // pair is (k+1, k): lower node first, math/axis.hpp:759-766).  fast_ok stays 0,
+  // so every kernel that does not test desc_ok keeps rejecting such an axis.
+  int32_t desc_ok;
 };
 
 // ---------------------------------------------------------------------------

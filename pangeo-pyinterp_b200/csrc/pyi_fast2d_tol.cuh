@@ -214,8 +214,14 @@ bilinear2d_tol_kernel(const __grid_constant__ GeoParams p) {
     for (int i = 0; i < PTS; ++i) {
       const double omt = __dsub_rn(1.0, t[i]);
       const double omu = __dsub_rn(1.0, u[i]);
-      const double a = fma(u[i], q[i].v01, __dmul_rn(omu, q[i].v00));
-      const double b = fma(u[i], q[i].v11, __dmul_rn(omu, q[i].v10));
+      double a, b;
+      if (YM != 0 && ay.desc_ok) {  // uniform: descending y, u is measured from node k + 1
+        a = fma(u[i], q[i].v00, __dmul_rn(omu, q[i].v01));
+        b = fma(u[i], q[i].v10, __dmul_rn(omu, q[i].v11));
+      } else {
+        a = fma(u[i], q[i].v01, __dmul_rn(omu, q[i].v00));
+        b = fma(u[i], q[i].v11, __dmul_rn(omu, q[i].v10));
+      }
       o[i] = fma(t[i], b, __dmul_rn(omt, a));
     }
     if (!all_safe) {  // rare: on a node, outside an axis, NaN

@@ -56,7 +56,7 @@ __device__ __forceinline__ void bracket_regular_i64(const DAxis& a, long long z,
   d0 = d;
 }
 
-// regular or irregular ascending f64 axis without period (uniform branch)
+// regular (ascending or descending) or irregular ascending f64 axis without period (uniform branch)
 __device__ __forceinline__ RegBracket bracket_f64(const DAxis& a, const double* sp, const int* slut,
                                                   double c, bool& ok) {
   if (a.kind != 0) return bracket_irregular(a, sp, slut, c, ok);
@@ -198,6 +198,10 @@ bilinear_nd_fast_kernel(const __grid_constant__ GeoParams p) {
     r.cell = (static_cast<long long>(bx.k) * ay.n + by.k) * az.n + kz;
     if (ND >= 4) r.cell = r.cell * p.ax[3].n + bu.k;
     if (!ok) r.cell = 0;  // always a legal address
+    // descending regular f64 axes (y, z, u): corner order of the reference's pair (k + 1, k)
+    r.sy = by.swap;
+    if (!ZI64) r.sz = bz.swap;
+    if (ND >= 4) r.su = bu.swap;
     Corners<ND, R> q;
     if constexpr (Corners<ND, R>::BYTES >= 64) {  // 64- / 128-byte cells: one request per lane group
       geo_gather_group<ND, R>(p, r, q);
@@ -277,7 +281,7 @@ bilinear_nd_fast_kernel(const __grid_constant__ GeoParams p) {
 
 // Eligibility of the N-D fast path (everything else runs the generic kernels).
 static bool axis_f64_fast(const DAxis& a, int max_irregular) {
-  if (!a.fast_ok || a.coord_i64 || a.n < 2 || a.period != 0.0) return false;
+  if (!(a.fast_ok || a.desc_ok) || a.coord_i64 || a.n < 2 || a.period != 0.0) return false;
   if (a.kind != 0 && (a.n > max_irregular || a.lut_bins <= 0 || a.lut_bins + 1 > 4 * max_irregular + 1)) {
     return false;
   }

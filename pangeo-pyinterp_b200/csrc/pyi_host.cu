@@ -95,15 +95,17 @@ bool exact_difference(double a, double b, double& diff) {
 }
 
 // Constants of the tolerance-mode bilinear kernel (pyi_fast2d_tol.cuh) for a
-// regular ascending float64 axis that already passed the fast-path checks.
+// regular float64 axis that already passed the fast-path checks (ascending, or
+// descending without period: step < 0, every expression below holds as it is).
 void tol_constants(const pyi_axis_desc& d, pyi::DAxis& out) {
   out.tol_ok = 0;
   const double step = d.step.f, start = d.start.f;
+  const double astep = std::fabs(step);  // negative on a descending axis (no period then)
   const double maxabs = std::max({std::fabs(d.min_value.f), std::fabs(d.max_value.f),
                                   std::fabs(d.min_value.f + d.period.f)});
   // |1 - dx / step| < 2^-26 for every spacing dx (the kernel's first-order
   // reciprocal), and cell numbers far below 2^31
-  if (!(maxabs / step < 67108864.0) || d.size >= (1LL << 30)) return;
+  if (!(maxabs / astep < 67108864.0) || d.size >= (1LL << 30)) return;
   if (d.period.f != 0.0 && !(d.period.f >= 9.765625e-4)) return;  // |x| < 2^40 => |x / period| < 2^50
   const double last = start + static_cast<double>(d.size - 1) * step;
   const bool wraps = d.is_periodic != 0;
@@ -113,7 +115,7 @@ void tol_constants(const pyi_axis_desc& d, pyi::DAxis& out) {
   }
   {
     int ex = 0;
-    std::frexp(step, &ex);                    // step = m * 2^ex, m in [0.5, 1)
+    std::frexp(astep, &ex);                   // |step| = m * 2^ex, m in [0.5, 1)
     const int bound = std::min(40, ex - 1 + 28);  // |x| < 2^bound <= 2^28 * step
     out.tol_xhi = (1023 + bound) << 20;
   }
@@ -148,6 +150,7 @@ void fast_constants(const pyi_axis* a, pyi::DAxis& out) {
   out.tol_xhi = 0;
   out.tol_off = out.tol_poff = 0.0;
   out.ispan = 0;
+  out.desc_ok = 0;
   if (d.coord_type == PYI_COORD_I64) {
     // regular ascending int64 (temporal) axis without period: pyi_fastnd.cuh
     const long long lim = 1LL << 61;
@@ -159,10 +162,25 @@ void fast_constants(const pyi_axis* a, pyi::DAxis& out) {
     out.fast_ok = 1;
     return;
   }
-  if (d.coord_type != PYI_COORD_F64 || !d.is_ascending || d.size < 2) return;
+  if (d.coord_type != PYI_COORD_F64 || d.size < 2) return;
   const double lim = 1099511627776.0;  // 2^40, the kernel's sane() bound
   auto moderate = [&](double v) { return std::fabs(v) < lim; };
   auto spacing_ok = [](double h) { return h > 1e-30 && h < 1e30; };
+  if (!d.is_ascending) {
+    // descending regular axis without period: the same checks mirrored (min is
+    // the last node, max the first); the kernels that test desc_ok serve it
+    if (d.kind != PYI_AXIS_REGULAR || d.is_periodic || d.period.f != 0.0) return;
+    const volatile double last = d.start.f + static_cast<double>(d.size - 1) * d.step.f;
+    const volatile double q_last = (last - d.start.f) * d.inv_step;
+    const bool ok = moderate(d.min_value.f) && moderate(d.max_value.f) && spacing_ok(-d.step.f) &&
+                    d.max_value.f == d.start.f && d.min_value.f == last &&
+                    std::round(q_last) == static_cast<double>(d.size - 1);
+    if (!ok) return;
+    out.hi = d.min_value.f;
+    out.desc_ok = 1;
+    tol_constants(d, out);
+    return;
+  }
   bool ok = moderate(d.min_value.f) && moderate(d.max_value.f) && moderate(d.period.f);
   if (d.kind == PYI_AXIS_REGULAR) {
     ok = ok && spacing_ok(d.step.f);

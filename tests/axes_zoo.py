@@ -19,6 +19,8 @@ def f64_axes():
         "lon_0p1": (np.arange(3600) * 0.1, dict(period=360.0), False),
         "lat": (lat, {}, False),
         "lat_desc": (lat, {}, True),
+        "lat_desc_inexact": (-89.8 + np.arange(600) * 0.3, {}, True),   # nodes are not fma(k, step, start)
+        "levels_desc": (np.arange(20) * 250.0, {}, True),                # regular descending z / u
         "lat_irregular": (np.degrees(np.arcsin(np.linspace(-0.99999, 0.99999, 720))), {}, False),
         "lat_irregular_desc": (np.degrees(np.arcsin(np.linspace(-0.99999, 0.99999, 720))), {}, True),
         "small_irregular": (np.array([0.0, 1.0, 4.0, 8.0, 20.0, 50.0]), {}, False),

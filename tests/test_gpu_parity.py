@@ -78,7 +78,7 @@ def test_axis_lookup_device_tensor(pyi, orc_best):
 
 
 def _grid_pair(pyi, o, nd, dtype, x_kind="lon_periodic", y_kind="lat", z_kind="monthly30", flip_z=False, nan=0.02,
-               small=True, pack_cells=True):
+               small=True, pack_cells=True, u_kind=None):
     fz, iz = axes_zoo.f64_axes(), axes_zoo.i64_axes()
     if small:
         specs = [(np.arange(72) * 5.0, dict(period=360.0), False) if x_kind == "lon_periodic" else fz[x_kind],
@@ -87,8 +87,10 @@ def _grid_pair(pyi, o, nd, dtype, x_kind="lon_periodic", y_kind="lat", z_kind="m
         specs = [fz[x_kind], fz[y_kind]]
     if nd >= 3:
         zs = iz[z_kind] if z_kind in iz else fz[z_kind]
-        specs.append((zs[0], zs[1], flip_z))
-    if nd >= 4:
+        specs.append((zs[0], zs[1], flip_z or zs[2]))
+    if nd >= 4 and u_kind is not None:
+        specs.append(fz[u_kind])
+    elif nd >= 4:
         specs.append((np.round(5500.0 * (np.arange(9) / 8) ** 2.2, 1), {}, False))
     pairs = [_mk_axis(pyi, o, s) for s in specs]
     shape = [len(p[0]) for p in pairs]
@@ -157,12 +159,13 @@ def test_geometric_bilinear(pyi, orc_best, nd, dtype, bilinear_mode):
 @pytest.mark.parametrize("nd", [2, 3, 4])
 @pytest.mark.parametrize("dtype", ["float64", "float32"])
 @pytest.mark.parametrize("method", [1, 2])
-def test_geometric_idw_nearest(pyi, orc_best, nd, dtype, method):
+@pytest.mark.parametrize("y_kind", ["lat", "lat_desc"])
+def test_geometric_idw_nearest(pyi, orc_best, nd, dtype, method, y_kind):
     """idw / nearest go through sin / cos / pow, which are not correctly
     rounded on either side: tolerance for idw; for nearest a differing corner
     is accepted only where the two candidate distances tie to rounding."""
     n = 30_000
-    grid, caxes, g = _grid_pair(pyi, orc_best, nd, dtype, nan=0.0)
+    grid, caxes, g = _grid_pair(pyi, orc_best, nd, dtype, nan=0.0, y_kind=y_kind)
     q = _queries(nd, n, 300 + nd)
     got = _call(pyi, grid, q, _geo_cfg(pyi, nd, method))
     want, _ = orc_best.geometric(caxes, g, *q, method=method, z_method=method == 2, u_method=method == 2,
@@ -217,6 +220,11 @@ def test_plain_layout_matches_packed_and_oracle(pyi, orc_best, nd, dtype, case, 
     dict(x_kind="lon_periodic", y_kind="lat", z_kind="irregular_time"),
     dict(x_kind="lon_periodic", y_kind="lat", z_kind="daily_ns_desc"),
     dict(x_kind="lon_periodic", y_kind="lat", z_kind="depth"),
+    # descending regular axes through the fast kernels (corner swap): y, then y + z + u
+    dict(x_kind="lon_periodic", y_kind="lat_desc"),
+    dict(x_kind="lon_180", y_kind="lat_desc_inexact", small=False),
+    dict(x_kind="lon_periodic", y_kind="lat_desc", z_kind="levels_desc", u_kind="levels_desc"),
+    dict(x_kind="lon_periodic", y_kind="lat_desc_inexact", z_kind="depth", u_kind="levels_desc"),
 ])
 @pytest.mark.parametrize("dtype", ["float64", "float32"])
 def test_geometric_axis_kinds(pyi, orc_best, case, dtype, bilinear_mode):
@@ -245,7 +253,7 @@ def test_geometric_axis_kinds(pyi, orc_best, case, dtype, bilinear_mode):
         assert np.isfinite(got).sum() > n // 100
 
 
-@pytest.mark.parametrize("lat_kind", ["regular", "irregular"])
+@pytest.mark.parametrize("lat_kind", ["regular", "irregular", "descending", "descending_inexact"])
 @pytest.mark.parametrize("dtype", ["float64", "float32", "int16"])
 def test_bilinear2d_fast_path_full_grid(pyi, orc_best, lat_kind, dtype, bilinear_mode):
     """BASELINE configs 1 / 5: the 0.25 degree global grid (regular or
@@ -256,7 +264,11 @@ def test_bilinear2d_fast_path_full_grid(pyi, orc_best, lat_kind, dtype, bilinear
     import torch
     s = pyi.synthetic
     lon = s.lon_axis_values()
-    lat = s.lat_axis_values() if lat_kind == "regular" else s.irregular_lat_values()
+    lat = s.lat_axis_values() if lat_kind != "irregular" else s.irregular_lat_values()
+    if lat_kind == "descending":  # 89.875 -> -89.875 (ERA5-like): the fast kernels swap the corners
+        lat = lat[::-1].copy()
+    elif lat_kind == "descending_inexact":  # nodes that are not fma(k, step, start): general mode
+        lat = 89.9 - np.arange(600) * 0.3
     g = s.field(lon, lat)
     if dtype == "int16":
         g = np.round(g * 1000).astype(np.int16)
@@ -265,11 +277,12 @@ def test_bilinear2d_fast_path_full_grid(pyi, orc_best, lat_kind, dtype, bilinear
         g[::37, ::11] = np.nan
     grid = pyi.Grid(pyi.Axis(lon, period=360.0), pyi.Axis(lat), g)
     cax = [orc_best.axis(lon, period=360.0), orc_best.axis(lat)]
-    assert cax[1].describe()["kind"] == (0 if lat_kind == "regular" else 1)
+    assert cax[1].describe()["kind"] == (1 if lat_kind == "irregular" else 0)
+    assert cax[1].describe()["is_ascending"] == (0 if lat_kind.startswith("descending") else 1)
     n = 400_001
     rng = np.random.default_rng(11)
     x = rng.uniform(-720.0, 1080.0, n)
-    y = rng.uniform(lat[0] - 0.5, lat[-1] + 0.5, n)
+    y = rng.uniform(lat.min() - 0.5, lat.max() + 0.5, n)
     x[0::53] = lon[rng.integers(0, lon.size, x[0::53].size)]              # exact nodes
     x[1::53] = lon[rng.integers(0, lon.size, x[1::53].size)] - 360.0
     x[2::53] = rng.uniform(359.75, 360.0, x[2::53].size)                  # seam cell
