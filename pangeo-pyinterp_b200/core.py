@@ -96,8 +96,9 @@ class Axis:
 
     def __del__(self):
         h = getattr(self, "_h", None)
-        if h and _abi._lib is not None:
-            _abi._lib.pyi_axis_destroy(h)
+        lib = getattr(_abi, "_lib", None)  # module globals are None while the interpreter shuts down
+        if h and lib is not None:
+            lib.pyi_axis_destroy(h)
             self._h = None
 
     # -- descriptor ----------------------------------------------------------
@@ -445,8 +446,9 @@ class Grid:
 
     def __del__(self):
         h = getattr(self, "_h", None)
-        if h and _abi._lib is not None:
-            _abi._lib.pyi_grid_destroy(h)
+        lib = getattr(_abi, "_lib", None)  # module globals are None while the interpreter shuts down
+        if h and lib is not None:
+            lib.pyi_grid_destroy(h)
             self._h = None
 
     # -- reference surface -----------------------------------------------------

@@ -1,5 +1,5 @@
-// pyi_bicubics.cuh -- K4s: bicubic on a 6 x 6 window of a 2-D float64 grid with
-// regular axes, in TOLERANCE value mode, as ONE separable 6 x 6 stencil whose
+// pyi_bicubics.cuh -- K4s: bicubic on a 6 x 6 window of a 2-D float64 or float32
+// grid with regular axes, in TOLERANCE value mode, as ONE separable 6 x 6 stencil whose
 // rows are loaded by lane quads.  Included by pyi_windowed.cu after
 // pyi_bicubicw.cuh (whose redo pass and tags it shares).
 //
@@ -59,11 +59,23 @@ __device__ __forceinline__ double cubic4(double c0, double c1, double c2, double
   return fma(fma(fma(c3, t, c2), t, c1), t, c0);
 }
 
+// Two adjacent grid values, loaded as one aligned piece (16 bytes of float64,
+// 8 bytes of float32); the arithmetic is float64 for both (the reference's
+// window holds doubles, cache.hpp:46-60, and only the result is cast).
+template <typename T>
+struct BcsPair;
+template <>
+struct BcsPair<double> { using type = double2; };
+template <>
+struct BcsPair<float> { using type = float2; };
+
+// T: grid (and result) type, double or float.
 // XM / YM: tol_ok of the axes (1 general, 2 exact nodes); PER: x has a period;
 // EVEN: ny is even, so every row of a window starts on the parity of wy0.
-template <bool PER, int XM, int YM, bool EVEN, int MINB>
+template <typename T, bool PER, int XM, int YM, bool EVEN, int MINB>
 __global__ void __launch_bounds__(kBcsThreads, MINB)
 bicubic_sep_kernel(const __grid_constant__ WinNdParams p) {
+  using V2 = typename BcsPair<T>::type;
   const DAxis& ax = p.ax[0];
   const DAxis& ay = p.ax[1];
   const int nx = ax.n, ny = ay.n;
@@ -72,8 +84,8 @@ bicubic_sep_kernel(const __grid_constant__ WinNdParams p) {
   const bool quiet_nan = p.boundary == PYI_BOUNDARY_UNDEF && !p.bounds_error;
   const unsigned lane = threadIdx.x & 31u;
   const int piece = static_cast<int>(lane & 3u);
-  const double* __restrict__ data = static_cast<const double*>(p.data);
-  double* __restrict__ out = static_cast<double*>(p.out);
+  const T* __restrict__ data = static_cast<const T*>(p.data);
+  T* __restrict__ out = static_cast<T*>(p.out);
   // This lane always holds columns 2 piece - par and 2 piece + 1 - par of a row
   // (par = parity of the row's first element): the cubics of the three column
   // weights it can need, j = 2 piece - 1, 2 piece, 2 piece + 1 (table entry
@@ -163,15 +175,19 @@ bicubic_sep_kernel(const __grid_constant__ WinNdParams p) {
         for (int i = 0; i < 6; ++i) {
           const double cx = cubic4(p.cw[0][i + 1][0], p.cw[0][i + 1][1], p.cw[0][i + 1][2], p.cw[0][i + 1][3], gtx);
           if (EVEN || (i & 1) == 0) {
-            const double2 v = __ldg(reinterpret_cast<const double2*>(data + idx));
-            a0 = fma(cx, v.x, a0);
-            a1 = fma(cx, v.y, a1);
+            const V2 v = __ldg(reinterpret_cast<const V2*>(data + idx));
+            a0 = fma(cx, static_cast<double>(v.x), a0);
+            a1 = fma(cx, static_cast<double>(v.y), a1);
           } else {
             // odd ny: rows 1, 3, 5 start on the other parity (a wrap keeps the
             // alternation: cells = nx ny has the parity of nx ... handled below)
-            const double2 v = __ldg(reinterpret_cast<const double2*>(data + idx + (par0 ? 1 : -1)));
-            b0 = fma(cx, v.x, b0);
-            b1 = fma(cx, v.y, b1);
+            // (the shifted piece of a row that restarts at element 0 of the array, wy0 = 0
+            // on a wrapped row, lies one past the unwrapped index: wrap the piece itself)
+            int shifted = idx + (par0 ? 1 : -1);
+            if (PER) shifted = shifted >= cells ? shifted - cells : shifted;
+            const V2 v = __ldg(reinterpret_cast<const V2*>(data + shifted));
+            b0 = fma(cx, static_cast<double>(v.x), b0);
+            b1 = fma(cx, static_cast<double>(v.y), b1);
           }
           // next row; past the last row a periodic x continues at row 0
           idx += ny;
@@ -210,9 +226,10 @@ bicubic_sep_kernel(const __grid_constant__ WinNdParams p) {
     const double r2 = shfl_xor_f64(odd2 ? half0 : half1, 2);
     const double total = __dadd_rn(odd2 ? half1 : half0, r2);  // group `piece`, point 8 piece + quad
     // lane L owns point L = 8 s + q: its value sits in lane 4 q + s
-    double mine = __shfl_sync(0xffffffffu, total, 4 * static_cast<int>(lane & 7u) + static_cast<int>(lane >> 3));
+    const double mine = __shfl_sync(0xffffffffu, total, 4 * static_cast<int>(lane & 7u) + static_cast<int>(lane >> 3));
+    T res = static_cast<T>(mine);  // ResultType of the grid (grid_dispatch.hpp:25-30)
     if (status != BCS_COMPUTE) {
-      mine = status == BCS_NAN ? CUDART_NAN : RedoTag<double>::value();
+      res = status == BCS_NAN ? RT<T>::nan() : RedoTag<T>::value();
     } else if (!isfinite(mine)) {
       // rare: a window with a NaN (-> NaN, cache.hpp:165-171) or an infinity /
       // an overflow (-> the generic code decides)
@@ -220,17 +237,17 @@ bicubic_sep_kernel(const __grid_constant__ WinNdParams p) {
       int row = wx0;
 #pragma unroll 1
       for (int i = 0; i < 6; ++i) {
-        const double* q = data + static_cast<long long>(row) * ny + wy0;
+        const T* q = data + static_cast<long long>(row) * ny + wy0;
 #pragma unroll 1
         for (int j = 0; j < 6; ++j) has_nan = has_nan || isnan(__ldg(q + j));
         row = (PER && row + 1 == nx) ? 0 : row + 1;
       }
-      mine = has_nan ? CUDART_NAN : RedoTag<double>::value();
+      res = has_nan ? RT<T>::nan() : RedoTag<T>::value();
     }
     if (active) {
-      __stcs(out + k, mine);
+      __stcs(out + k, res);
       // tagged points are also listed, so that the redo pass need not scan the output
-      if (p.queue != nullptr && RedoTag<double>::is(mine)) {
+      if (p.queue != nullptr && RedoTag<T>::is(res)) {
         const unsigned slot = atomicAdd(p.queue, 1u);
         if (slot < p.queue_cap) p.queue[1 + slot] = static_cast<unsigned>(k);
       }
@@ -239,7 +256,7 @@ bicubic_sep_kernel(const __grid_constant__ WinNdParams p) {
 }
 
 static bool bicubics_eligible(const WinNdParams& p) {
-  if (p.ndim != 2 || p.dtype != PYI_F64 || !p.w_ok || !p.cw_ok) return false;
+  if (p.ndim != 2 || (p.dtype != PYI_F64 && p.dtype != PYI_F32) || !p.w_ok || !p.cw_ok) return false;
   const DAxis& ax = p.ax[0];
   const DAxis& ay = p.ax[1];
   if (!ax.fast_ok || !ay.fast_ok || !ax.tol_ok || !ay.tol_ok) return false;  // ascending regular f64
@@ -249,11 +266,17 @@ static bool bicubics_eligible(const WinNdParams& p) {
   // odd ny: the rows of a window alternate parity; a periodic wrap keeps the
   // alternation only when nx is even
   if ((ay.n & 1) != 0 && ax.period != 0.0 && (ax.n & 1) != 0) return false;
-  return (reinterpret_cast<uintptr_t>(p.data) & 15) == 0;
+  // aligned pieces of two elements
+  return (reinterpret_cast<uintptr_t>(p.data) & (p.dtype == PYI_F64 ? 15 : 7)) == 0;
 }
 
 template <bool PER, int XM, int YM, bool EVEN>
 static void launch_bicubics_e(const WinNdParams& p, cudaStream_t stream) {
+  if (p.dtype == PYI_F32) {  // float32 grids: the default variant only
+    const int blocks32 = grid_for((p.n + 31) / 32, kBcsThreads / 32, 6);
+    bicubic_sep_kernel<float, PER, XM, YM, EVEN, 6><<<blocks32, kBcsThreads, 0, stream>>>(p);
+    return;
+  }
   // resident blocks per SM (round-2 sweep on B200: 22.7 / 25.1 / 23.4 Gpts/s at 4 / 6 / 8);
   // PYINTERP_B200_S_MINB = 4 | 6 | 8 for experiments
   int minb = 6;
@@ -261,9 +284,9 @@ static void launch_bicubics_e(const WinNdParams& p, cudaStream_t stream) {
   if (e && e[0] >= '4' && e[0] <= '8') minb = e[0] - '0';
   const int blocks = grid_for((p.n + 31) / 32, kBcsThreads / 32, minb);
   switch (minb) {
-    case 4: bicubic_sep_kernel<PER, XM, YM, EVEN, 4><<<blocks, kBcsThreads, 0, stream>>>(p); break;
-    case 6: bicubic_sep_kernel<PER, XM, YM, EVEN, 6><<<blocks, kBcsThreads, 0, stream>>>(p); break;
-    default: bicubic_sep_kernel<PER, XM, YM, EVEN, 8><<<blocks, kBcsThreads, 0, stream>>>(p); break;
+    case 4: bicubic_sep_kernel<double, PER, XM, YM, EVEN, 4><<<blocks, kBcsThreads, 0, stream>>>(p); break;
+    case 6: bicubic_sep_kernel<double, PER, XM, YM, EVEN, 6><<<blocks, kBcsThreads, 0, stream>>>(p); break;
+    default: bicubic_sep_kernel<double, PER, XM, YM, EVEN, 8><<<blocks, kBcsThreads, 0, stream>>>(p); break;
   }
 }
 

@@ -40,7 +40,7 @@ cudaError_t launch_windowed_nd(const WinNdParams& p, cudaStream_t stream) {
   // generic kernel recomputes the points that pass tagged
   if (p.ndim >= 2 && p.method == PYI_S_BICUBIC && p.half_x == 3 && p.half_y == 3 && p.w_ok &&
       (p.ndim == 2 || p.planes) && !force_generic() && !exact_bicubic(p)) {
-    // 2-D float64 grids with ascending axes: the separable stencil (K4s);
+    // 2-D float64 / float32 grids with ascending axes: the separable stencil (K4s);
     // PYINTERP_B200_BICUBIC=weights keeps K4w for comparison
     const char* which = getenv("PYINTERP_B200_BICUBIC");
     const bool separable = bicubics_eligible(p) && !(which != nullptr && which[0] == 'w');

@@ -129,6 +129,41 @@ def test_bicubic_at_baseline_size(pyi, synthetic, orc_best, bicubic_mode):
         assert np.all(err <= 1e-12 * np.maximum(np.abs(want[m]), 1.0)), err.max()
 
 
+@pytest.mark.parametrize("dtype,ny", [("float32", 720), ("float32", 719), ("float64", 719)])
+def test_bicubic_separable_dtypes_and_odd_ny(pyi, synthetic, orc_best, bicubic_mode, dtype, ny):
+    """The separable stencil on a FLOAT32 0.25 degree grid (8-byte pieces of two
+    values) and on grids with an ODD ny (the rows of a window alternate parity;
+    a window that wraps onto row 0 at wy0 = 0 once read past the array): results
+    within 1e-5 / 1e-12 of the oracle, NaN positions identical (the land mask has
+    a NaN at element 0); device and host entry."""
+    import torch
+    lon = synthetic.lon_axis_values()
+    lat = synthetic.lat_axis_values()[:ny]
+    g = synthetic.field(lon, lat).astype(dtype)
+    g[::37, ::11] = np.nan
+    n = 2_000_003
+    rng = np.random.default_rng(43)
+    q = _adversarial(synthetic.queries(n, 1002), dict(lon=lon, lat=lat), rng)
+    oaxes = [orc_best.axis(lon, period=360.0), orc_best.axis(lat)]
+    want, _ = orc_best.windowed2d(oaxes, g, q[0], q[1], num_threads=0, stateless=True)
+    assert want.dtype == np.dtype(dtype)
+    grid = pyi.Grid(pyi.Axis(lon, period=360.0), pyi.Axis(lat), g, resident=True)
+    got = pyi.bivariate(grid, q[0], q[1], "bicubic")
+    dev = pyi.bivariate(grid, torch.from_numpy(q[0]).cuda(), torch.from_numpy(q[1]).cuda(), "bicubic").cpu().numpy()
+    assert got.dtype == np.dtype(dtype) and np.array_equal(got, dev, equal_nan=True)
+    assert np.array_equal(np.isnan(got), np.isnan(want))
+    m = ~np.isnan(want)
+    assert m.mean() > 0.8
+    err = np.abs(got[m].astype(np.float64) - want[m].astype(np.float64))
+    if bicubic_mode == "exact":
+        assert err.max() == 0.0
+    else:
+        tol = 1e-5 if dtype == "float32" else 1e-12
+        assert np.all(err <= tol * np.maximum(np.abs(want[m]), 1.0)), err.max()
+        if dtype == "float32":
+            assert np.mean(got[m] == want[m]) > 0.99  # float64 arithmetic, one final rounding to float32
+
+
 @pytest.mark.parametrize("lat_kind", ["regular", "irregular"])
 def test_bilinear_at_baseline_size(pyi, synthetic, orc_best, lat_kind, bilinear_mode):
     """BASELINE configs 1 / 5 at 1e7 points (the CPU oracle's budget), both
