@@ -172,7 +172,9 @@ SIGNATURES = {
 }
 
 ABI_VERSION = 2
-LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc", "libpyinterp_b200.so")
+# PYINTERP_B200_LIB: another build of the same library (csrc/Makefile `check`: bounds-checked gathers)
+LIB_PATH = os.environ.get("PYINTERP_B200_LIB") or os.path.join(
+    os.path.dirname(os.path.abspath(__file__)), "csrc", "libpyinterp_b200.so")
 _lib = None
 
 

@@ -175,6 +175,7 @@ bicubic_sep_kernel(const __grid_constant__ WinNdParams p) {
         for (int i = 0; i < 6; ++i) {
           const double cx = cubic4(p.cw[0][i + 1][0], p.cw[0][i + 1][1], p.cw[0][i + 1][2], p.cw[0][i + 1][3], gtx);
           if (EVEN || (i & 1) == 0) {
+            PYI_CHECK_RANGE(idx, 2, cells, "K4s row piece");
             const V2 v = __ldg(reinterpret_cast<const V2*>(data + idx));
             a0 = fma(cx, static_cast<double>(v.x), a0);
             a1 = fma(cx, static_cast<double>(v.y), a1);
@@ -185,6 +186,7 @@ bicubic_sep_kernel(const __grid_constant__ WinNdParams p) {
             // on a wrapped row, lies one past the unwrapped index: wrap the piece itself)
             int shifted = idx + (par0 ? 1 : -1);
             if (PER) shifted = shifted >= cells ? shifted - cells : shifted;
+            PYI_CHECK_RANGE(shifted, 2, cells, "K4s shifted row piece");
             const V2 v = __ldg(reinterpret_cast<const V2*>(data + shifted));
             b0 = fma(cx, static_cast<double>(v.x), b0);
             b1 = fma(cx, static_cast<double>(v.y), b1);
@@ -239,6 +241,7 @@ bicubic_sep_kernel(const __grid_constant__ WinNdParams p) {
       for (int i = 0; i < 6; ++i) {
         const T* q = data + static_cast<long long>(row) * ny + wy0;
 #pragma unroll 1
+        PYI_CHECK_RANGE(q - data, 6, cells, "K4s NaN rescan");
         for (int j = 0; j < 6; ++j) has_nan = has_nan || isnan(__ldg(q + j));
         row = (PER && row + 1 == nx) ? 0 : row + 1;
       }

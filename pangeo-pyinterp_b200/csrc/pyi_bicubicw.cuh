@@ -86,6 +86,7 @@ __device__ __forceinline__ double dot6(const double* w, const double (&v)[6]) {
 template <int DT>
 __device__ __forceinline__ void load_row6(const void* data, int dtype, long long base,
                                           long long cells, bool ok, double (&v)[6]) {
+  if (ok) PYI_CHECK_RANGE(base, 6, cells, "K4w window row");
   if (DT == PYI_F64) {
     const long long b0 = base & ~1LL;
     const bool odd = (base & 1LL) != 0;

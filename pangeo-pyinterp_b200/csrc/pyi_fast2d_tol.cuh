@@ -73,11 +73,13 @@ __device__ __forceinline__ void tol_irregular(const DAxis& a, const unsigned sho
   int bin = __double2int_rd(f);  // saturating; NaN -> 0 and fails the checks below
   const bool in_table = sane(c) && static_cast<unsigned>(bin) < static_cast<unsigned>(a.lut_bins);
   bin = in_table ? bin : 0;
+  PYI_CHECK_RANGE(bin >> shift, 1, ((a.lut_bins - 1) >> shift) + 1, "K1t bin table");
   const unsigned e = sbin[bin >> shift];
   const int j = static_cast<int>(e & 0x3fffu);
   const bool inside = (e & kTolOne) != 0;
   int kk = inside ? j : j - 1;
   kk = min(max(kk, 0), a.n - 1);
+  PYI_CHECK_RANGE(kk, 1, a.n, "K1t cell table");
   double2 cell = scell[kk];  // {node(kk), 1 / spacing}
   bool below = inside && c < cell.x;  // the node of the bin is above c: cell j - 1
   if (e & kTolMany) {  // several nodes in the bin: the last one that is <= c
@@ -209,7 +211,10 @@ bilinear2d_tol_kernel(const __grid_constant__ GeoParams p) {
     }
     Cell<double> q[PTS];
 #pragma unroll
-    for (int i = 0; i < PTS; ++i) q[i].load(p.packed, cell[i]);
+    for (int i = 0; i < PTS; ++i) {
+      PYI_CHECK_RANGE(cell[i], 1, static_cast<long long>(ax.n) * ay.n, "K1t packed cell");
+      q[i].load(p.packed, cell[i]);
+    }
 #pragma unroll
     for (int i = 0; i < PTS; ++i) {
       const double omt = __dsub_rn(1.0, t[i]);

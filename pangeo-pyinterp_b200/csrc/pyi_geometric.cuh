@@ -113,6 +113,16 @@ __device__ __forceinline__ void load_256(const void* src, unsigned long long* w)
                : "l"(src));
 }
 
+// number of cells of the packed copy: one per grid node (the last one along an
+// axis is the seam cell of a periodic axis, unused otherwise)
+template <int ND>
+__device__ __forceinline__ long long geo_total_cells(const GeoParams& p) {
+  long long t = static_cast<long long>(p.ax[0].n) * p.ax[1].n;
+  if (ND >= 3) t *= p.ax[2].n;
+  if (ND >= 4) t *= p.ax[3].n;
+  return t;
+}
+
 // Packed value block -> q, exchanging corners of reversed pairs.
 template <int ND, typename R>
 __device__ __forceinline__ void unpack_cell(const R* v, const CellRef& r, Corners<ND, R>& k) {
@@ -189,6 +199,7 @@ __device__ __forceinline__ void geo_gather_packed(const GeoParams& p, const Cell
     unsigned long long w[BYTES / 8];
     R v[NV];
   } buf;
+  PYI_CHECK_RANGE(r.cell, 1, geo_total_cells<ND>(p), "packed cell (one thread)");
   const char* src = reinterpret_cast<const char*>(static_cast<const R*>(p.packed) + r.cell * NV);
   if (BYTES >= 32) {
 #pragma unroll
@@ -223,6 +234,7 @@ __device__ __forceinline__ void geo_gather_group(const GeoParams& p, const CellR
 #pragma unroll
   for (int g = 0; g < G; ++g) {
     const long long c = __shfl_sync(0xffffffffu, r.cell, base + g);
+    PYI_CHECK_RANGE(c, 1, geo_total_cells<ND>(p), "packed cell (lane group)");
     load_256(reinterpret_cast<const char*>(p.packed) + c * BYTES + m * 32, tmp[g]);
   }
   union {
