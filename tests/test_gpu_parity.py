@@ -715,3 +715,48 @@ def test_bicubic_reference_order_vs_stateless_near_the_seam(pyi, orc_best):
         gap = np.nanmax(np.abs(stateful - stateless))
         print(f"max |reference-order - stateless| near the seam: {gap:.3e}")
         assert gap <= 1e-12
+
+
+def test_divisors_with_all_ones_significand(pyi, orc_best, monkeypatch):
+    """Cell spacings one ulp below a power of two (significand all ones): the
+    Newton reciprocal behind the kernels' own IEEE division ends on an exact tie
+    for such a divisor unless it is seeded as nvcc seeds it (low word 1,
+    pyi_common.cuh rcp_seed).  Irregular axes whose EVERY spacing is
+    2^k (1 - 2^-53): bilinear and bicubic must stay bit-identical in exact mode
+    (found as 1-ulp differences on a 360 / 21 degree periodic axis, where the
+    spline's 1 / 63.99999999999999 came out as 2^-6)."""
+    one = 1.0 - 2.0 ** -53
+    nodes = np.r_[0.0, one * 2.0 ** np.arange(0, 10)]
+    h = np.diff(nodes)
+    assert np.all((h.view(np.uint64) & np.uint64(0xFFFFFFFFFFFFF)) == np.uint64(0xFFFFFFFFFFFFF))
+    rng = np.random.default_rng(77)
+    g = rng.normal(size=(nodes.size, nodes.size)) * 10.0
+    n = 200_000
+    x = rng.uniform(0.0, nodes[-1], n)
+    y = rng.uniform(0.0, nodes[-1], n)
+    # more points in the small cells
+    x[::2] = rng.uniform(0.0, 8.0, x[::2].size)
+    y[::3] = rng.uniform(0.0, 8.0, y[::3].size)
+    oaxes = [orc_best.axis(nodes), orc_best.axis(nodes)]
+    assert oaxes[0].describe()["kind"] == 1
+    grid = pyi.Grid(pyi.Axis(nodes), pyi.Axis(nodes), g)
+    monkeypatch.setenv("PYINTERP_B200_BILINEAR", "exact")
+    monkeypatch.setenv("PYINTERP_B200_BICUBIC", "exact")
+    want, _ = orc_best.geometric(oaxes, g, x, y, method=0, num_threads=0)
+    assert np.array_equal(pyi.bivariate(grid, x, y), want, equal_nan=True)
+    want, _ = orc_best.windowed2d(oaxes, g, x, y, num_threads=0, stateless=True)
+    got = pyi.bivariate(grid, x, y, "bicubic")
+    assert np.isfinite(want).mean() > 0.2
+    assert np.array_equal(got, want, equal_nan=True)
+    # regular periodic longitude with the same kind of divisor inside the spline solve
+    lon = 10.0 + np.arange(21) * (360.0 / 21)
+    lat = np.arange(24) * 0.5
+    g2 = rng.normal(size=(21, 24)) * 10.0
+    x2 = rng.uniform(-400.0, 800.0, n)
+    y2 = rng.uniform(1.2, 10.2, n)
+    o2 = [orc_best.axis(lon, period=360.0), orc_best.axis(lat)]
+    grid2 = pyi.Grid(pyi.Axis(lon, period=360.0), pyi.Axis(lat), g2)
+    want, _ = orc_best.windowed2d(o2, g2, x2, y2, num_threads=0, stateless=True)
+    assert np.array_equal(pyi.bivariate(grid2, x2, y2, "bicubic"), want, equal_nan=True)
+    want, _ = orc_best.geometric(o2, g2, x2, y2, method=0, num_threads=0)
+    assert np.array_equal(pyi.bivariate(grid2, x2, y2), want, equal_nan=True)
