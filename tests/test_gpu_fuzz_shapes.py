@@ -66,7 +66,7 @@ def _case(seed):
     return dict(lon=lon, lat=lat, periodic=periodic, g=g, x=x, y=y, dtype=dtype)
 
 
-@pytest.mark.parametrize("seed", range(24))
+@pytest.mark.parametrize("seed", range(60))
 def test_random_2d_shapes(pyi, orc_best, seed, monkeypatch):
     c = _case(seed)
     kw = dict(period=360.0) if c["periodic"] else {}
@@ -94,7 +94,7 @@ def test_random_2d_shapes(pyi, orc_best, seed, monkeypatch):
                 assert same == 1.0, f"{what} bicubic {boundary} exact: {same}"
 
 
-@pytest.mark.parametrize("seed", range(8))
+@pytest.mark.parametrize("seed", range(24))
 def test_random_3d_4d_shapes(pyi, orc_best, seed):
     rng = np.random.default_rng(100 + seed)
     c = _case(200 + seed)
@@ -127,3 +127,77 @@ def test_random_3d_4d_shapes(pyi, orc_best, seed):
         cls = pyi.geometric.Trivariate if nd == 3 else pyi.geometric.Quadrivariate
         got = fn(grid, *q, cls.bilinear())
         assert _close(got, want, f"seed {seed} {shape} {c['dtype']}") == 1.0
+
+
+MODELS = ["bicubic", "bilinear", "akima", "akima_periodic", "c_spline", "c_spline_not_a_knot", "c_spline_periodic",
+          "linear", "steffen", "polynomial"]
+
+
+def _rand_axis(rng, n, kind):
+    """(values, kwargs) of a random axis: regular with an inexact step, irregular, descending."""
+    if kind == "periodic":
+        return float(rng.choice([0.0, 10.0, -180.0])) + np.arange(n) * (360.0 / n), dict(period=360.0)
+    step = float(rng.choice([0.25, 0.3, 1.0 / 3.0, 2.5]))
+    v = float(rng.choice([0.0, -7.1, 100.3])) + np.arange(n) * step
+    if kind == "irregular":
+        v = v + rng.uniform(-0.3, 0.3, n) * step
+    if kind == "descending":
+        v = v[::-1].copy()
+    return v, {}
+
+
+@pytest.mark.parametrize("seed", range(90))
+def test_random_windowed_models(pyi, orc_best, seed):
+    """Every fitting model of the windowed path on random 2-D .. 4-D shapes, window
+    sizes, boundary modes and axis kinds (tests/test_gpu_windowed_nd.py holds the
+    fixed-shape cases)."""
+    rng = np.random.default_rng(500 + seed)
+    nd = int(rng.choice([2, 2, 3, 4]))
+    model = MODELS[seed % len(MODELS)]
+    boundary = str(rng.choice(["undef", "shrink"]))
+    # smallest window a model can fit (fewer nodes: NaN everywhere, nothing to compare)
+    least = {"akima": 3, "akima_periodic": 3, "bilinear": 1, "linear": 1, "polynomial": 1}.get(model, 2)
+    half = (int(rng.integers(least, 5)), int(rng.integers(least, 5)))
+    if model == "bicubic" and seed % 2 == 0:
+        half = (3, 3)  # the fast kernels' window
+    if model == "c_spline_periodic":
+        half, boundary = (half[0], half[0]), "undef"  # DESIGN.md, deviations: equal, unshrunken windows only
+    nx, ny = int(rng.integers(9, 30)), int(rng.integers(9, 30))
+    xv, xkw = _rand_axis(rng, nx, str(rng.choice(["periodic", "periodic", "regular", "irregular"])))
+    yv, ykw = _rand_axis(rng, ny, str(rng.choice(["regular", "irregular", "descending"])))
+    axes_v = [(xv, xkw), (yv, ykw)]
+    n = 12_000
+    q = [rng.uniform(xv.min() - 400.0 if xkw else xv.min() - 1.0, xv.max() + 400.0 if xkw else xv.max() + 1.0, n),
+         rng.uniform(yv.min() - 0.5, yv.max() + 0.5, n)]
+    q[0][::13] = xv[rng.integers(0, nx, q[0][::13].size)]
+    q[1][1::17] = yv[rng.integers(0, ny, q[1][1::17].size)]
+    q[0][2::499] = np.nan
+    zm = um = 0
+    if nd >= 3:
+        zv, zkw = _rand_axis(rng, int(rng.integers(2, 6)), str(rng.choice(["regular", "irregular", "descending"])))
+        axes_v.append((zv, zkw))
+        q.append(rng.uniform(zv.min() - 0.3, zv.max() + 0.3, n))
+        zm = int(rng.integers(0, 2))
+    if nd >= 4:
+        uv, ukw = _rand_axis(rng, int(rng.integers(2, 5)), str(rng.choice(["regular", "irregular"])))
+        axes_v.append((uv, ukw))
+        q.append(rng.uniform(uv.min() - 0.3, uv.max() + 0.3, n))
+        um = int(rng.integers(0, 2))
+    dtype = str(rng.choice(["float64", "float32"]))
+    shape = tuple(len(a[0]) for a in axes_v)
+    g = (rng.normal(size=shape) * 30.0).astype(dtype)
+    g[rng.random(shape) < 0.0005] = np.nan
+    oaxes = [orc_best.axis(v, **kw) for v, kw in axes_v]
+    grid = pyi.Grid(*[pyi.Axis(v, **kw) for v, kw in axes_v], g)
+    cls = {2: pyi.windowed.Bivariate, 3: pyi.windowed.Trivariate, 4: pyi.windowed.Quadrivariate}[nd]
+    cfg = getattr(cls, model)().with_boundary_mode(getattr(pyi.windowed.BoundaryConfig, boundary)())
+    cfg = cfg.with_half_window_size_x(half[0]).with_half_window_size_y(half[1])
+    if nd >= 3:
+        cfg = cfg.with_third_axis(getattr(pyi.windowed.AxisConfig, "nearest" if zm else "linear")())
+    if nd >= 4:
+        cfg = cfg.with_fourth_axis(getattr(pyi.windowed.AxisConfig, "nearest" if um else "linear")())
+    fn = {2: pyi.core.bivariate, 3: pyi.core.trivariate, 4: pyi.core.quadrivariate}[nd]
+    got = fn(grid, *q, cfg)
+    want, _ = orc_best.windowed_nd(oaxes, g, *q, method=model, half_x=half[0], half_y=half[1], boundary=boundary,
+                                   num_threads=0, z_method=zm, u_method=um)
+    _close(got, want, f"seed {seed} {nd}-D {shape} {model} {half} {boundary} {dtype}")
