@@ -201,3 +201,89 @@ def test_random_windowed_models(pyi, orc_best, seed):
     want, _ = orc_best.windowed_nd(oaxes, g, *q, method=model, half_x=half[0], half_y=half[1], boundary=boundary,
                                    num_threads=0, z_method=zm, u_method=um)
     _close(got, want, f"seed {seed} {nd}-D {shape} {model} {half} {boundary} {dtype}")
+
+
+def _irregular(rng, n, lo, hi):
+    """Random irregular ascending nodes: uniform, clustered or geometric spacing."""
+    style = int(rng.integers(0, 3))
+    if style == 0:
+        v = np.sort(rng.uniform(lo, hi, n))
+    elif style == 1:  # clusters: many nodes inside a few bins of the lookup table
+        centres = rng.uniform(lo, hi, max(2, n // 40))
+        v = np.sort(centres[rng.integers(0, centres.size, n)] + rng.normal(0.0, (hi - lo) * 1e-4, n))
+    else:
+        v = lo + (hi - lo) * (np.geomspace(1.0, 1000.0, n) - 1.0) / 999.0
+    v = np.unique(v)
+    return v
+
+
+@pytest.mark.parametrize("seed", range(200))
+def test_random_geometric_axes(pyi, orc_best, seed, monkeypatch):
+    """Geometric bilinear (2-D and 3-D) on random axes: periods other than 360,
+    inexact regular steps, descending and irregular (uniform / clustered /
+    geometric) latitudes of up to 3000 nodes, int64 time axes with large values,
+    every grid dtype; queries many periods away and on nodes."""
+    rng = np.random.default_rng(9000 + seed)
+    period = float(rng.choice([360.0, 2.0 * np.pi, 24.0, 1.0, 1000.0]))
+    nx = int(rng.integers(8, 300))
+    if rng.integers(0, 4) == 0:  # open regular x
+        xv, xkw = float(rng.uniform(-50, 50)) + np.arange(nx) * float(rng.uniform(0.01, 3.0)), {}
+    else:
+        xv, xkw = float(rng.choice([0.0, -period / 2, period * 0.1])) + np.arange(nx) * (period / nx), dict(period=period)
+    ykind = int(rng.integers(0, 4))
+    if ykind == 0:
+        yv = _irregular(rng, int(rng.integers(3, 3000)), -80.0, 80.0)
+    elif ykind == 1:
+        yv = float(rng.uniform(-90, 0)) + np.arange(int(rng.integers(2, 400))) * float(rng.uniform(0.05, 0.7))
+    elif ykind == 2:
+        yv = (float(rng.uniform(-90, 0)) + np.arange(int(rng.integers(2, 400))) * float(rng.choice([0.25, 0.5, 0.1])))[::-1].copy()
+    else:
+        yv = -89.875 + np.arange(int(rng.integers(2, 200))) * 0.25
+    ny = yv.size
+    dtype = str(rng.choice(["float64", "float64", "float32", "int16", "uint8", "int64"]))
+    nd = 2 if seed % 3 else 3
+    shape = (nx, ny) if nd == 2 else (nx, ny, int(rng.integers(2, 6)))
+    if nx * ny > 200_000:
+        nd, shape = 2, (nx, ny)
+    g = rng.normal(size=shape) * 40.0
+    if np.dtype(dtype).kind == "f":
+        g = g.astype(dtype)
+        g[rng.random(shape) < 0.002] = np.nan
+    else:
+        info = np.iinfo(dtype)
+        g = np.clip(np.round(g), info.min, info.max).astype(dtype)
+    n = 40_000
+    span = (period if xkw else xv[-1] - xv[0])
+    far = float(rng.choice([2.0, 50.0, 1e5])) if xkw else 0.05
+    x = rng.uniform(xv[0] - far * span, xv[-1] + far * span, n)
+    y = rng.uniform(yv.min() - 0.01 * (yv.max() - yv.min() + 1), yv.max() + 0.01 * (yv.max() - yv.min() + 1), n)
+    x[::11] = xv[rng.integers(0, nx, x[::11].size)] + (period * rng.integers(-3, 4, x[::11].size) if xkw else 0.0)
+    y[1::13] = yv[rng.integers(0, ny, y[1::13].size)]
+    y[2::17] = np.nextafter(yv[rng.integers(0, ny, y[2::17].size)], rng.choice([-1e9, 1e9]))
+    x[3::997] = np.nan
+    y[4::991] = np.inf
+    oaxes = [orc_best.axis(xv, **xkw), orc_best.axis(yv)]
+    axes = [pyi.Axis(xv, **xkw), pyi.Axis(yv)]
+    q = [x, y]
+    if nd == 3:
+        t0 = int(rng.choice([0, 1_609_459_200_000_000_000, -4_000_000_000_000_000_000]))
+        dt = int(rng.choice([1, 3_600_000_000_000, 86_400_000_000_000, 7]))
+        tv = t0 + np.arange(shape[2], dtype=np.int64) * dt
+        oaxes.append(orc_best.axis(tv))
+        axes.append(pyi.TemporalAxis(tv.view("datetime64[ns]")))
+        z = rng.integers(tv[0] - dt, tv[-1] + dt + 1, n, dtype=np.int64)
+        z[5::19] = tv[rng.integers(0, tv.size, z[5::19].size)]
+        z[6::983] = np.iinfo(np.int64).min
+        q.append(z)
+    grid = pyi.Grid(*axes, g)
+    want, _ = orc_best.geometric(oaxes, g, *q, method=0, num_threads=0)
+    what = f"seed {seed} {shape} {dtype} period={period if xkw else None} ykind={ykind}"
+    args = list(q)
+    if nd == 3:
+        args[2] = args[2].view("datetime64[ns]")
+    fn = pyi.core.bivariate if nd == 2 else pyi.core.trivariate
+    cfg = (pyi.geometric.Bivariate if nd == 2 else pyi.geometric.Trivariate).bilinear()
+    monkeypatch.setenv("PYINTERP_B200_BILINEAR", "tolerance")
+    _close(fn(grid, *args, cfg), want, what + " tolerance")
+    monkeypatch.setenv("PYINTERP_B200_BILINEAR", "exact")
+    assert _close(fn(grid, *args, cfg), want, what + " exact") == 1.0, what
