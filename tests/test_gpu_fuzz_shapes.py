@@ -287,3 +287,55 @@ def test_random_geometric_axes(pyi, orc_best, seed, monkeypatch):
     _close(fn(grid, *args, cfg), want, what + " tolerance")
     monkeypatch.setenv("PYINTERP_B200_BILINEAR", "exact")
     assert _close(fn(grid, *args, cfg), want, what + " exact") == 1.0, what
+
+
+@pytest.mark.parametrize("seed", range(120))
+def test_random_axis_lookups(pyi, orc_best, seed):
+    """find_indexes / find_index on random axes -- float64 or int64, regular or
+    irregular, ascending or descending, with or without a period (which may be
+    longer than the axis) -- on adversarial coordinates: bit-exact."""
+    import axes_zoo
+    rng = np.random.default_rng(4000 + seed)
+    n = int(rng.integers(1, 400))
+    integer = bool(rng.integers(0, 3) == 0)
+    irregular = bool(rng.integers(0, 2)) and n >= 3
+    period = None
+    if integer:
+        step = int(rng.choice([1, 7, 3600, 86_400_000_000_000]))
+        start = int(rng.choice([0, -31, 1_609_459_200_000_000_000]))
+        v = start + np.arange(n, dtype=np.int64) * step
+        if irregular:
+            v = start + np.cumsum(rng.integers(1, 9, n)).astype(np.int64) * step
+        if rng.integers(0, 3) == 0 and n >= 2:
+            period = int((v[-1] - v[0]) + step * int(rng.integers(1, 4)))
+    else:
+        step = float(rng.choice([0.25, 0.1, 1.0 / 3.0, 17.142857142857142, 1e-3]))
+        start = float(rng.choice([0.0, -180.0, 1e6, -89.875]))
+        v = start + np.arange(n) * step
+        if irregular:
+            v = start + np.cumsum(rng.uniform(0.2, 3.0, n)) * step
+        if rng.integers(0, 3) == 0 and n >= 2:
+            period = float((v[-1] - v[0]) + step * float(rng.choice([1.0, 2.5, 1.0 + 1e-9])))
+    flip = bool(rng.integers(0, 3) == 0) and n >= 2
+    kw = {} if period is None else dict(period=period)
+    try:
+        c = orc_best.axis(v, **kw)
+    except Exception:
+        pytest.skip("the reference rejects this axis")
+    if integer:
+        per = kw.get("period")
+        g = pyi.TemporalAxis(v.view("datetime64[ns]"), period=None if per is None else np.timedelta64(per, "ns"))
+    else:
+        g = pyi.Axis(v, **kw)
+    if flip:
+        g.flip(inplace=True)
+        c.flip()
+    d = c.describe()
+    gd = g._desc()
+    assert (gd.kind, gd.size, gd.is_ascending, gd.is_periodic) == (d["kind"], d["size"], d["is_ascending"], d["is_periodic"])
+    coords = axes_zoo.coords_for(d, 20_000, seed)
+    got = g.find_indexes(coords)
+    want = c.find_indexes(coords)
+    assert np.array_equal(got, want), (seed, np.flatnonzero((got != want).any(1))[:5])
+    for bounded in (False, True):
+        assert np.array_equal(g.find_index(coords, bounded), c.find_index(coords, bounded)), (seed, bounded)
