@@ -339,3 +339,41 @@ def test_random_axis_lookups(pyi, orc_best, seed):
     assert np.array_equal(got, want), (seed, np.flatnonzero((got != want).any(1))[:5])
     for bounded in (False, True):
         assert np.array_equal(g.find_index(coords, bounded), c.find_index(coords, bounded)), (seed, bounded)
+
+
+@pytest.mark.parametrize("seed", range(40))
+def test_random_fills(pyi, orc_best, seed):
+    """gauss_seidel / multigrid / loess on random shapes (1 x n, n x 1, odd, tiny)
+    and parameters: grid, iteration count and residual bit for bit."""
+    import golden_util as gu
+    rng = np.random.default_rng(7000 + seed)
+    shape = (int(rng.integers(1, 90)), int(rng.integers(1, 90)))
+    if seed % 7 == 0:
+        shape = (1, shape[1]) if seed % 2 else (shape[0], 1)
+    dtype = str(rng.choice(["float64", "float32"]))
+    g0 = gu.fill_field(shape, dtype, 7100 + seed, blobs=int(rng.integers(1, 4)))
+    fg = str(rng.choice(["zonal_average", "zero"]))
+    per = bool(rng.integers(0, 2))
+    its = int(rng.integers(0, 40))
+    eps = float(rng.choice([0.0, 1e-4, 1e-2]))
+    what = (seed, shape, dtype, fg, per, its, eps)
+    relax = float(rng.choice([1.0, 1.3, 1.9]))
+    want = g0.copy()
+    r_want = orc_best.fill_gauss_seidel(want, fg, per, its, eps, relax, num_threads=3)
+    got = g0.copy()
+    assert pyi.fill.gauss_seidel(got, first_guess=fg, is_periodic=per, max_iterations=its, epsilon=eps,
+                                 relaxation=relax) == r_want, what
+    assert np.array_equal(got, want, equal_nan=True), what
+    pre, post = int(rng.integers(0, 4)), int(rng.integers(1, 4))
+    want = g0.copy()
+    r_want = orc_best.fill_multigrid(want, fg, per, min(its, 6), eps, pre, post, num_threads=3)
+    got = g0.copy()
+    assert pyi.fill.multigrid(got, first_guess=fg, is_periodic=per, max_iterations=min(its, 6), epsilon=eps,
+                              pre_smooth=pre, post_smooth=post) == r_want, what
+    assert np.array_equal(got, want, equal_nan=True), what
+    hx, hy = int(rng.integers(1, 7)), int(rng.integers(1, 7))
+    vt = str(rng.choice(["undefined", "defined", "all"]))
+    want = orc_best.fill_loess(g0, hx, hy, vt, fg, per, min(its, 12), eps)
+    got = pyi.fill.loess(g0, nx=hx, ny=hy, value_type=vt, first_guess=fg, is_periodic=per,
+                         max_iterations=min(its, 12), epsilon=eps)
+    assert np.array_equal(got, want, equal_nan=True), what + (hx, hy, vt)
