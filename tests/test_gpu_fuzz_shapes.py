@@ -377,3 +377,47 @@ def test_random_fills(pyi, orc_best, seed):
     got = pyi.fill.loess(g0, nx=hx, ny=hy, value_type=vt, first_guess=fg, is_periodic=per,
                          max_iterations=min(its, 12), epsilon=eps)
     assert np.array_equal(got, want, equal_nan=True), what + (hx, hy, vt)
+
+
+def test_ragged_sizes_through_the_host_pipeline(pyi, orc_best, monkeypatch):
+    """Empty, tiny and ragged point counts (around the pipeline's chunk sizes and
+    the vector widths of the kernels), host and device entry, every path of the
+    0.25 degree grid: identical to each other and to the oracle."""
+    import torch
+    s = pyi.synthetic
+    lon, lat = s.lon_axis_values(), s.lat_axis_values()
+    g = s.field(lon, lat)
+    g[::37, ::11] = np.nan
+    t = s.time_axis_values(6)
+    g3 = s.field(lon, lat, nz=6, dtype="float32", noise=0.0)
+    grid = pyi.Grid(pyi.Axis(lon, period=360.0), pyi.Axis(lat), g, resident=True)
+    grid3 = pyi.Grid(pyi.Axis(lon, period=360.0), pyi.Axis(lat), pyi.TemporalAxis(t), g3, resident=True)
+    o2 = [orc_best.axis(lon, period=360.0), orc_best.axis(lat)]
+    o3 = o2 + [orc_best.axis(t.astype("datetime64[ns]").astype(np.int64))]
+    nmax = (1 << 23) + 3
+    x, y, z = s.queries(nmax, 77, ndim=3, time_values=t)
+    sizes = [0, 1, 2, 3, 5, 31, 32, 33, 127, 129, 1000, (1 << 17) - 1, (1 << 17) + 1, (1 << 20) - 1, (1 << 20) + 1,
+             3 * (1 << 20) + 5, (1 << 22) - 1, (1 << 22), (1 << 22) + 7, nmax]
+    want_bil, _ = orc_best.geometric(o2, g, x, y, method=0, num_threads=0)
+    want_tri, _ = orc_best.geometric(o3, g3, x, y, z, method=0, num_threads=0)
+    want_cub, _ = orc_best.windowed2d(o2, g, x[:1 << 21], y[:1 << 21], num_threads=0, stateless=True)
+    xd, yd, zd = (torch.from_numpy(v).cuda() for v in (x, y, z))
+    for n in sizes:
+        for mode in ("tolerance", "exact"):
+            monkeypatch.setenv("PYINTERP_B200_BILINEAR", mode)
+            host = pyi.bivariate(grid, x[:n], y[:n])
+            dev = pyi.bivariate(grid, xd[:n], yd[:n]).cpu().numpy()
+            assert host.shape == (n,) and np.array_equal(host, dev, equal_nan=True), (n, mode)
+            if mode == "exact":
+                assert np.array_equal(host, want_bil[:n], equal_nan=True), n
+            else:
+                _close(host, want_bil[:n], f"bilinear n={n}")
+        host = pyi.trivariate(grid3, x[:n], y[:n], z[:n].view("datetime64[ns]"))
+        dev = pyi.trivariate(grid3, xd[:n], yd[:n], zd[:n]).cpu().numpy()
+        assert host.dtype == np.float32 and np.array_equal(host, dev, equal_nan=True), n
+        assert np.array_equal(host, want_tri[:n], equal_nan=True), n
+        m = min(n, 1 << 21)
+        host = pyi.bivariate(grid, x[:m], y[:m], "bicubic")
+        dev = pyi.bivariate(grid, xd[:m], yd[:m], "bicubic").cpu().numpy()
+        assert np.array_equal(host, dev, equal_nan=True), n
+        _close(host, want_cub[:m], f"bicubic n={m}")
