@@ -60,7 +60,7 @@ __device__ __forceinline__ void bracket_regular_i64(const DAxis& a, long long z,
 __device__ __forceinline__ RegBracket bracket_f64(const DAxis& a, const double* sp, const int* slut,
                                                   double c, bool& ok) {
   if (a.kind != 0) return bracket_irregular(a, sp, slut, c, ok);
-  return bracket_regular<false>(a, c, 0.0, ok);
+  return bracket_regular<false, 2>(a, c, 0.0, ok);
 }
 
 // linear<Z, R> / nearest<Z, R> (interpolate/linear.hpp:22-33, nearest.hpp:21-32)
