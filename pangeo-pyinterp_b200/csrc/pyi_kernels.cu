@@ -69,24 +69,50 @@ __device__ __forceinline__ R eval_bilinear(R x, R y, R x0, R y0, R x1, R y1, R q
   return omt * (omu * q00 + u * q01) + t * (omu * q10 + u * q11);
 }
 
+// The four comparable distances of a query to the corners of its cell, in the
+// corner order (x0,y0) (x0,y1) (x1,y0) (x1,y1).  Same operations on the same
+// operands as four calls of comparable_distance; the seven distinct sines /
+// cosines (out of sixteen) are evaluated once.
+template <typename R>
+__device__ __forceinline__ void corner_distances(R x, R y, R x0, R y0, R x1, R y1, R (&d2)[4]) {
+  const R d2r = RT<R>::pi() / R(180);
+  const R lon = x * d2r, lat = y * d2r;
+  const R lat_c[2] = {y0 * d2r, y1 * d2r};
+  const R lon_c[2] = {x0 * d2r, x1 * d2r};
+  const R cos_lat = RT<R>::cos_(lat);
+  R hav_lat[2], cos_c[2], hav_lon[2];
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    hav_lat[j] = hav<R>(lat_c[j] - lat);
+    cos_c[j] = RT<R>::cos_(lat_c[j]);
+    hav_lon[j] = hav<R>(lon_c[j] - lon);
+  }
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const int i = k >> 1, j = k & 1;
+    d2[k] = hav_lat[j] + cos_lat * cos_c[j] * hav_lon[i];
+  }
+}
+
 // InverseDistanceWeighting::evaluate bivariate.hpp:189-232
 template <typename R>
 __device__ __forceinline__ R eval_idw(int exp_, R x, R y, R x0, R y0, R x1, R y1, R q00, R q01,
                                       R q10, R q11) {
-  const R cx[4] = {x0, x0, x1, x1};
-  const R cy[4] = {y0, y1, y0, y1};
   const R cq[4] = {q00, q01, q10, q11};
   const R eps2 = RT<R>::eps() * RT<R>::eps();
   const double half_exp = exp_ * 0.5;
+  R d2[4];
+  corner_distances<R>(x, y, x0, y0, x1, y1, d2);
   R wsum = R(0);
   R vsum = R(0);
 #pragma unroll
   for (int k = 0; k < 4; ++k) {
-    const R d2 = comparable_distance<R>(x, y, cx[k], cy[k]);
-    if (d2 <= eps2) {
+    if (d2[k] <= eps2) {
       return cq[k];
     }
-    const R w = static_cast<R>(1 / pow(static_cast<double>(d2), half_exp));
+    // exponent 2 (the default, config.cpp:46): std::pow(d, 1.0) is d itself, no pow()
+    const double dd = static_cast<double>(d2[k]);
+    const R w = static_cast<R>(1 / (exp_ == 2 ? dd : pow(dd, half_exp)));
     wsum += w;
     vsum += cq[k] * w;
   }
@@ -97,14 +123,13 @@ __device__ __forceinline__ R eval_idw(int exp_, R x, R y, R x0, R y0, R x1, R y1
 template <typename R>
 __device__ __forceinline__ R eval_nearest(R x, R y, R x0, R y0, R x1, R y1, R q00, R q01, R q10,
                                           R q11) {
-  R best = comparable_distance<R>(x, y, x0, y0);
+  R d2[4];
+  corner_distances<R>(x, y, x0, y0, x1, y1, d2);
+  R best = d2[0];
   R val = q00;
-  R d = comparable_distance<R>(x, y, x0, y1);
-  if (d < best) { best = d; val = q01; }
-  d = comparable_distance<R>(x, y, x1, y0);
-  if (d < best) { best = d; val = q10; }
-  d = comparable_distance<R>(x, y, x1, y1);
-  if (d < best) { best = d; val = q11; }
+  if (d2[1] < best) { best = d2[1]; val = q01; }
+  if (d2[2] < best) { best = d2[2]; val = q10; }
+  if (d2[3] < best) { best = d2[3]; val = q11; }
   return val;
 }
 
