@@ -43,6 +43,8 @@ BYTES_PER_POINT = {"bilinear": 24, "bilinear_irrlat": 24, "bicubic": 24, "trivar
                    # the other half of the geometric matrix: idw on the 2-D grid, bilinear on a float64 3-D grid
                    # (x, y, z 24 + out 8 + 8 corners x 8 = 96)
                    "idw": 24, "trivariate_f64": 96,
+                   # the same 2-D grid stored as float32 (float32 results: 16 in + 4 out)
+                   "bilinear_f32": 20,
                    # K6: streams only; the windows are compute / L2 work
                    "c_spline2d": 24, "bicubic3d": 28}
 # windowed workloads: fitting model of the public API
@@ -69,7 +71,8 @@ def parse():
 
 
 def default_points(workload: str) -> int:
-    return {"bilinear": 1_000_000_000, "bilinear_irrlat": 1_000_000_000, "idw": 100_000_000,
+    return {"bilinear": 1_000_000_000, "bilinear_irrlat": 1_000_000_000, "bilinear_f32": 1_000_000_000,
+            "idw": 100_000_000,
             "trivariate_f64": 100_000_000, "bicubic": 100_000_000, "trivariate": 100_000_000,
             "quadrivariate": 100_000_000, "c_spline2d": 20_000_000, "bicubic3d": 20_000_000}[workload]
 
@@ -105,6 +108,8 @@ def build_host_case(workload: str):
     lon, lat = syn.lon_axis_values(), syn.lat_axis_values()
     if workload == "bilinear_irrlat":  # BASELINE configs[4]: irregular latitude axis
         lat = syn.irregular_lat_values()
+    if workload == "bilinear_f32":
+        return dict(nd=2, lon=lon, lat=lat, grid=syn.field(lon, lat).astype(np.float32), dtype="f32")
     if workload in ("bilinear", "bilinear_irrlat", "bicubic", "c_spline2d", "idw"):
         return dict(nd=2, lon=lon, lat=lat, grid=syn.field(lon, lat), dtype="f64")
     if workload == "trivariate_f64":
@@ -130,6 +135,7 @@ def workload_name(workload, n):
     shape = {"bilinear": "bivariate bilinear f64 Grid2D 1440x720 circular lon",
              "bilinear_irrlat": "bivariate bilinear f64 Grid2D 1440x720 circular lon, irregular (Gaussian-like) latitude",
              "idw": "bivariate inverse distance weighting (exp 2) f64 Grid2D 1440x720 circular lon",
+             "bilinear_f32": "bivariate bilinear f32 Grid2D 1440x720 circular lon (float32 results)",
              "trivariate_f64": "trivariate bilinear f64 Grid3D 1440x720x120 int64 TemporalAxis",
              "bicubic": "bivariate bicubic (6x6 window) f64 Grid2D 1440x720 circular lon",
              "trivariate": "trivariate bilinear f32 Grid3D 1440x720x365 int64 TemporalAxis",
@@ -371,7 +377,7 @@ def oracle_guard(env, pyi, case, grid, workload):
     # 2-D bilinear: from 2^22 points per launch the default value mode runs the tolerance kernel -- the
     # kernel the timed region runs -- so the guard is that large and goes through the device entry
     # (one launch; the host path would cut it into chunks below the threshold)
-    big = workload in ("bilinear", "bilinear_irrlat")
+    big = workload in ("bilinear", "bilinear_irrlat", "bilinear_f32")
     n_guard = 4_200_000 if big else 1_000_000
     q = host_queries(case, n_guard, 1001 + env.rank)
     kind, run = cpu_run(case, workload, None)
@@ -675,7 +681,7 @@ def main():
         del grid
         torch.cuda.empty_cache()
         sub = [("bicubic", 100_000_000, ()), ("trivariate", 100_000_000, ()), ("quadrivariate", 100_000_000, ()),
-               ("idw", 100_000_000, ()), ("trivariate_f64", 100_000_000, ()),
+               ("idw", 100_000_000, ()), ("trivariate_f64", 100_000_000, ()), ("bilinear_f32", 400_000_000, ()),
                ("bilinear_irrlat", 1_000_000_000, (1_000_000, 10_000_000, 100_000_000, 1_000_000_000))]
         if world >= 8 and not args.points:
             # configs[4] sweeps to 1e10 points in total: 1.25e9 per GPU on eight of them (30 GB of streams each)

@@ -62,12 +62,28 @@ __device__ __forceinline__ double cubic4(double c0, double c1, double c2, double
 // Two adjacent grid values, loaded as one aligned piece (16 bytes of float64,
 // 8 bytes of float32); the arithmetic is float64 for both (the reference's
 // window holds doubles, cache.hpp:46-60, and only the result is cast).
+// (loaded with asm volatile: __ldg is speculatable for the compiler, which may then drop the
+// "window (0, 0) for a lane that is not computed" select in front of it, pyi_fast2d.cuh)
 template <typename T>
 struct BcsPair;
 template <>
-struct BcsPair<double> { using type = double2; };
+struct BcsPair<double> {
+  using type = double2;
+  static __device__ __forceinline__ double2 load(const double* p) {
+    double2 v;
+    asm volatile("ld.global.nc.v2.f64 {%0,%1}, [%2];" : "=d"(v.x), "=d"(v.y) : "l"(p));
+    return v;
+  }
+};
 template <>
-struct BcsPair<float> { using type = float2; };
+struct BcsPair<float> {
+  using type = float2;
+  static __device__ __forceinline__ float2 load(const float* p) {
+    float2 v;
+    asm volatile("ld.global.nc.v2.f32 {%0,%1}, [%2];" : "=f"(v.x), "=f"(v.y) : "l"(p));
+    return v;
+  }
+};
 
 // T: grid (and result) type, double or float.
 // XM / YM: tol_ok of the axes (1 general, 2 exact nodes); PER: x has a period;
@@ -176,7 +192,7 @@ bicubic_sep_kernel(const __grid_constant__ WinNdParams p) {
           const double cx = cubic4(p.cw[0][i + 1][0], p.cw[0][i + 1][1], p.cw[0][i + 1][2], p.cw[0][i + 1][3], gtx);
           if (EVEN || (i & 1) == 0) {
             PYI_CHECK_RANGE(idx, 2, cells, "K4s row piece");
-            const V2 v = __ldg(reinterpret_cast<const V2*>(data + idx));
+            const V2 v = BcsPair<T>::load(data + idx);
             a0 = fma(cx, static_cast<double>(v.x), a0);
             a1 = fma(cx, static_cast<double>(v.y), a1);
           } else {
@@ -187,7 +203,7 @@ bicubic_sep_kernel(const __grid_constant__ WinNdParams p) {
             int shifted = idx + (par0 ? 1 : -1);
             if (PER) shifted = shifted >= cells ? shifted - cells : shifted;
             PYI_CHECK_RANGE(shifted, 2, cells, "K4s shifted row piece");
-            const V2 v = __ldg(reinterpret_cast<const V2*>(data + shifted));
+            const V2 v = BcsPair<T>::load(data + shifted);
             b0 = fma(cx, static_cast<double>(v.x), b0);
             b1 = fma(cx, static_cast<double>(v.y), b1);
           }

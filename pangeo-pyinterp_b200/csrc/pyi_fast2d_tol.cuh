@@ -262,22 +262,126 @@ bilinear2d_tol_kernel(const __grid_constant__ GeoParams p) {
   }
 }
 
+// K1f: the same verified brackets for FLOAT32 results (float32 and small-integer
+// grids), regular y.  Nothing is approximated here: once the bracket is the
+// reference's, the value is its own float arithmetic (bivariate.hpp:78-96 casts
+// the corner coordinates and the query to float; Bilinear::evaluate,
+// geometric/bivariate.hpp:110-132, divides and sums in float) -- the operations
+// of fast2d_point<float> (pyi_fast2d.cuh) on the same operands, so the results
+// are BIT-IDENTICAL to the reference; only the search for the bracket is the
+// cheap one.  Two points per thread, 16-byte loads, 8-byte stores.
+template <bool PER, int XM, int YM, int MINB>
+__global__ void __launch_bounds__(kFastThreads, MINB)
+bilinear2d_tolf_kernel(const __grid_constant__ GeoParams p) {
+  const DAxis& ax = p.ax[0];
+  const DAxis& ay = p.ax[1];
+  const bool ydesc = ay.desc_ok != 0;
+  const unsigned groups = static_cast<unsigned>(p.n / 2);
+  const unsigned stride = gridDim.x * blockDim.x;
+  float* __restrict__ out = static_cast<float*>(p.out);
+  for (unsigned g = blockIdx.x * blockDim.x + threadIdx.x; g < groups; g += stride) {
+    const size_t base = static_cast<size_t>(g) * 2;
+    double x[2], y[2];
+    VecIO<2>::load(p.x + base, x);
+    VecIO<2>::load(p.y + base, y);
+    long long cell[2];
+    bool safe[2];
+    float tnum[2], unum[2], dx[2], dy[2];
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+      double c = x[i], jf = 0.0;
+      bool s = true;
+      if (PER) {
+        int unused;
+        jf = rint_magic(fma(x[i], ax.inv_period, ax.tol_poff), unused);
+        c = fma(-jf, ax.period, x[i]);
+        s = static_cast<int>(static_cast<unsigned>(__double2hiint(x[i])) & 0x7ff00000u) < ax.tol_xhi;
+      }
+      int kx, ky;
+      double td, ud, x0n, x1n, y0n, y1n;
+      tol_regular_nodes<XM, PER>(ax, c, x[i], jf, kx, td, s, x0n, x1n);
+      tol_regular_nodes<YM, false>(ay, y[i], y[i], 0.0, ky, ud, s, y0n, y1n);
+      // bivariate.hpp:78-89 in float: x1 and the query are normalised against the
+      // float-rounded x0 promoted back to double (see fast2d_point)
+      const float x0 = static_cast<float>(x0n);
+      double px = x[i];
+      if (PER) {
+        const double x0d = static_cast<double>(x0);
+        const double hi0 = __dadd_rn(x0d, ax.period);
+        const bool seam = kx == ax.n - 1;
+        x1n = seam ? ax.seam_c1_f32 : x1n;
+        // the seam constant is normalised already; any other cell needing it is re-done
+        s = s && (seam || !(x1n >= hi0 || x1n < x0d));
+        const bool out2 = x[i] >= hi0 || x[i] < x0d;
+        const double pn = norm_fast(x[i], x0d, ax.period, ax.inv_period);
+        px = out2 ? pn : x[i];
+      }
+      tnum[i] = __fsub_rn(static_cast<float>(px), x0);
+      dx[i] = __fsub_rn(static_cast<float>(x1n), x0);
+      const float y0 = static_cast<float>(y0n);
+      unum[i] = __fsub_rn(static_cast<float>(y[i]), y0);
+      dy[i] = __fsub_rn(static_cast<float>(y1n), y0);
+      safe[i] = s;
+      // (indexes clamped as well: the load below must be legal whatever an unsettled lane holds)
+      const int kxc = min(max(kx, 0), ax.n - 1), kyc = min(max(ky, 0), ay.n - 1);
+      cell[i] = s ? static_cast<long long>(kxc) * ay.n + kyc : 0LL;
+    }
+    Cell<float> q[2];
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+      PYI_CHECK_RANGE(cell[i], 1, static_cast<long long>(ax.n) * ay.n, "K1f packed cell");
+      q[i].load(p.packed, cell[i]);
+    }
+    float o[2];
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+      // descending y: the reference's first corner is the lower node, k + 1
+      const float v00 = ydesc ? q[i].v01 : q[i].v00, v01 = ydesc ? q[i].v00 : q[i].v01;
+      const float v10 = ydesc ? q[i].v11 : q[i].v10, v11 = ydesc ? q[i].v10 : q[i].v11;
+      const float t = __fdiv_rn(tnum[i], dx[i]);
+      const float u = __fdiv_rn(unum[i], dy[i]);
+      const float omt = __fsub_rn(1.0f, t);
+      const float omu = __fsub_rn(1.0f, u);
+      const float a = __fadd_rn(__fmul_rn(omu, v00), __fmul_rn(u, v01));
+      const float b = __fadd_rn(__fmul_rn(omu, v10), __fmul_rn(u, v11));
+      o[i] = __fadd_rn(__fmul_rn(omt, a), __fmul_rn(t, b));
+    }
+    if (!(safe[0] && safe[1])) {  // rare: on a node, outside an axis, NaN (as in the float64 kernel)
+#pragma unroll
+      for (int i = 0; i < 2; ++i) {
+        if (safe[i]) continue;
+        bool far = false;
+        if (!p.bounds_error && sane(x[i]) && sane(y[i])) {
+          far = beyond_ends(ay, y[i]) || (!PER && beyond_ends(ax, x[i]));
+        }
+        if (!far) {
+          const unsigned slot = atomicAdd(p.queue, 1u);
+          if (slot < p.queue_cap) p.queue[1 + slot] = static_cast<unsigned>(base + i);
+        }
+        o[i] = RT<float>::nan();
+      }
+    }
+    __stcs(reinterpret_cast<float2*>(out + base), make_float2(o[0], o[1]));
+  }
+}
+
 // The points the hot kernel queued (on a node, NaN, far-away longitudes ...)
 // and the n % pts tail, through the generic code.  Nothing to do when the queue
 // overflowed: the exact kernel launched next recomputes every point.
+template <typename R>
 __global__ void __launch_bounds__(kFastThreads)
 tol2d_redo_kernel(const __grid_constant__ GeoParams p, int pts) {
   const unsigned total = *p.queue;
   if (total > p.queue_cap) return;
-  double* __restrict__ out = static_cast<double*>(p.out);
+  R* __restrict__ out = static_cast<R*>(p.out);
   const unsigned stride = gridDim.x * blockDim.x;
   for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
     const long long k = p.queue[1 + i];
-    out[k] = slow_point<double>(p, __ldg(p.x + k), __ldg(p.y + k), k);
+    out[k] = slow_point<R>(p, __ldg(p.x + k), __ldg(p.y + k), k);
   }
   if (blockIdx.x == 0 && threadIdx.x < static_cast<unsigned>(p.n % pts)) {
     const long long k = p.n - (p.n % pts) + threadIdx.x;
-    out[k] = slow_point<double>(p, __ldg(p.x + k), __ldg(p.y + k), k);
+    out[k] = slow_point<R>(p, __ldg(p.x + k), __ldg(p.y + k), k);
   }
 }
 
@@ -315,10 +419,16 @@ static bool tol2d_eligible(const GeoParams& p) {
   if (p.value_mode == PYI_VALUES_DEFAULT && p.n < (1LL << 22) && !(forced != nullptr && forced[0] == 't')) {
     return false;
   }
-  if (p.dtype != PYI_F64 && p.dtype != PYI_I64 && p.dtype != PYI_U64) return false;  // float64 results
   if (p.method != PYI_BILINEAR || !fast2d_eligible(p)) return false;
   if (!p.ax[0].tol_ok) return false;
   if (p.ax[1].kind == 0 && !p.ax[1].tol_ok) return false;
+  const bool r64 = p.dtype == PYI_F64 || p.dtype == PYI_I64 || p.dtype == PYI_U64;
+  if (!r64) {
+    // float32 results (K1f, bit-identical): regular y, 16-byte coordinate pairs, 8-byte result pairs
+    if (p.ax[1].kind != 0) return false;
+    const uintptr_t in = reinterpret_cast<uintptr_t>(p.x) | reinterpret_cast<uintptr_t>(p.y);
+    return (in & 15) == 0 && (reinterpret_cast<uintptr_t>(p.out) & 7) == 0;
+  }
   const uintptr_t align = reinterpret_cast<uintptr_t>(p.x) | reinterpret_cast<uintptr_t>(p.y) |
                           reinterpret_cast<uintptr_t>(p.out);
   return (align & 31) == 0;
@@ -389,7 +499,21 @@ static void launch_tol2d_p(const GeoParams& p, cudaStream_t stream) {
   }
 }
 
+template <bool PER>
+static void launch_tolf_p(const GeoParams& p, cudaStream_t stream) {
+  const int blocks = grid_for((p.n + 1) / 2, kFastThreads, 4);
+  const int xm = p.ax[0].tol_ok, ym = p.ax[1].tol_ok;
+  if (xm == 2) {
+    if (ym == 2) bilinear2d_tolf_kernel<PER, 2, 2, 4><<<blocks, kFastThreads, 0, stream>>>(p);
+    else bilinear2d_tolf_kernel<PER, 2, 1, 4><<<blocks, kFastThreads, 0, stream>>>(p);
+  } else {
+    if (ym == 2) bilinear2d_tolf_kernel<PER, 1, 2, 4><<<blocks, kFastThreads, 0, stream>>>(p);
+    else bilinear2d_tolf_kernel<PER, 1, 1, 4><<<blocks, kFastThreads, 0, stream>>>(p);
+  }
+}
+
 static cudaError_t launch_tol2d(const GeoParams& p, cudaStream_t stream) {
+  const bool r64 = p.dtype == PYI_F64 || p.dtype == PYI_I64 || p.dtype == PYI_U64;
   const long long chunk = 1LL << 31;  // multiple of 4: keeps the 32-byte alignment of the slices
   int pts, minb;
   bool prefetch;
@@ -400,7 +524,7 @@ static cudaError_t launch_tol2d(const GeoParams& p, cudaStream_t stream) {
     q.index_base = p.index_base + begin;
     q.x = p.x + begin;
     q.y = p.y + begin;
-    q.out = static_cast<char*>(p.out) + begin * 8;
+    q.out = static_cast<char*>(p.out) + begin * (r64 ? 8 : 4);
     // the queue: the caller's (host pipeline: one per stream slot), else a
     // per-launch one from the stream-ordered allocator, so that concurrent
     // calls on other streams never share it
@@ -412,19 +536,25 @@ static cudaError_t launch_tol2d(const GeoParams& p, cudaStream_t stream) {
       q.queue_cap = kTolQueue;
     }
     e = cudaMemsetAsync(q.queue, 0, sizeof(unsigned), stream);
-    if (e == cudaSuccess) {
+    if (e == cudaSuccess && r64) {
       if (p.ax[0].period != 0.0) launch_tol2d_p<true>(q, stream);
       else launch_tol2d_p<false>(q, stream);
       // kernels compiled once use the default points per thread
       const bool sweep = p.ax[0].period != 0.0 && p.ax[0].tol_ok == 2 && !(p.ax[1].kind == 0 && p.ax[1].tol_ok == 1);
-      tol2d_redo_kernel<<<sm_count(), kFastThreads, 0, stream>>>(q, sweep ? pts : 2);
+      tol2d_redo_kernel<double><<<sm_count(), kFastThreads, 0, stream>>>(q, sweep ? pts : 2);
+      g_launches.fetch_add(2);
+      e = cudaGetLastError();
+    } else if (e == cudaSuccess) {
+      if (p.ax[0].period != 0.0) launch_tolf_p<true>(q, stream);
+      else launch_tolf_p<false>(q, stream);
+      tol2d_redo_kernel<float><<<sm_count(), kFastThreads, 0, stream>>>(q, 2);
       g_launches.fetch_add(2);
       e = cudaGetLastError();
     }
     // the bit-identical kernel behind the queue: returns at once unless it overflowed
     if (e == cudaSuccess) {
       q.run_if_overflow = q.queue;
-      e = launch_fast2d_r<double>(q, stream);
+      e = r64 ? launch_fast2d_r<double>(q, stream) : launch_fast2d_r<float>(q, stream);
     }
     if (own) {
       const cudaError_t e2 = cudaFreeAsync(q.queue, stream);

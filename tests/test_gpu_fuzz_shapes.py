@@ -77,7 +77,8 @@ def test_random_2d_shapes(pyi, orc_best, seed, monkeypatch):
     # geometric bilinear: tolerance kernel forced (float64 results), then bit-identical
     want, _ = orc_best.geometric(oaxes, c["g"], x, y, method=0, num_threads=0)
     monkeypatch.setenv("PYINTERP_B200_BILINEAR", "tolerance")
-    _close(pyi.bivariate(grid, x, y), want, what + " bilinear tolerance")
+    same = _close(pyi.bivariate(grid, x, y), want, what + " bilinear tolerance")
+    assert same == 1.0 or want.dtype == np.float64, what  # float32 results: bit-identical in every mode (K1f)
     monkeypatch.setenv("PYINTERP_B200_BILINEAR", "exact")
     assert _close(pyi.bivariate(grid, x, y), want, what + " bilinear exact") == 1.0
     # windowed bicubic, both boundary modes: separable / weights kernels, then bit-identical
@@ -284,7 +285,8 @@ def test_random_geometric_axes(pyi, orc_best, seed, monkeypatch):
     fn = pyi.core.bivariate if nd == 2 else pyi.core.trivariate
     cfg = (pyi.geometric.Bivariate if nd == 2 else pyi.geometric.Trivariate).bilinear()
     monkeypatch.setenv("PYINTERP_B200_BILINEAR", "tolerance")
-    _close(fn(grid, *args, cfg), want, what + " tolerance")
+    same = _close(fn(grid, *args, cfg), want, what + " tolerance")
+    assert same == 1.0 or (nd == 2 and want.dtype == np.float64), what  # only K1t (float64, 2-D) rounds differently
     monkeypatch.setenv("PYINTERP_B200_BILINEAR", "exact")
     assert _close(fn(grid, *args, cfg), want, what + " exact") == 1.0, what
 

@@ -42,6 +42,8 @@ def main():
     x, y = s.queries(n, 1001)
     xd, yd = torch.from_numpy(x).cuda(), torch.from_numpy(y).cuda()
     for name, la, gg in (("f64 regular", lat, g), ("f32 regular", lat, g.astype(np.float32)),
+                         ("i16 regular", lat, np.round(g * 1000).astype(np.int16)),
+                         ("f32 descending", lat[::-1].copy(), g[:, ::-1].astype(np.float32)),
                          ("f64 irregular", s.irregular_lat_values(), g)):
         grid = pyi.Grid(pyi.Axis(lon, period=360.0), pyi.Axis(la), gg, resident=True)
         for mode in ("tolerance", "exact"):
