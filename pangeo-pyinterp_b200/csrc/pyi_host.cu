@@ -638,6 +638,70 @@ void stencil_cubics(const double* w6, double step, double (*cw)[4]) {
   }
 }
 
+// The same table for the fitting models that are LINEAR in the node values and
+// cubic on a cell, bivariate/spline.hpp:96-118 (y, then x) being separable for
+// them: `linear` (univariate/linear.hpp), `c_spline` (cspline.hpp:84-139) and
+// `c_spline_not_a_knot` (cspline_not_a_knot.hpp:114-215).  On uniformly spaced
+// nodes the spline's node coefficients c_i (CSplineBase::x_) times step^2 solve
+//   G[i-1] + 4 G[i] + G[i+1] = 3 (y[i+1] - 2 y[i] + y[i-1]),  i = 1..4
+// closed by G[0] = G[5] = 0 (natural) or G[0] - 2 G[1] + G[2] = 0,
+// G[3] - 2 G[4] + G[5] = 0 (not-a-knot), whatever the step; on the centre cell
+// (cspline_base.hpp:32-40,112)
+//   s(t) = y2 + t (y3 - y2 - (G3 + 2 G2) / 3) + t^2 G2 + t^3 (G3 - G2) / 3 .
+// Solved for the six unit vectors in long double.  False for the other models.
+bool model_stencil_cubics(int method, double (*cw)[4]) {
+  for (int e = 0; e < 8; ++e) {
+    for (int c = 0; c < 4; ++c) cw[e][c] = 0.0;
+  }
+  if (method == PYI_S_LINEAR) {
+    cw[3][0] = 1.0;
+    cw[3][1] = -1.0;
+    cw[4][1] = 1.0;
+    return true;
+  }
+  if (method != PYI_S_C_SPLINE && method != PYI_S_C_SPLINE_NOT_A_KNOT) return false;
+  long double a[6][12] = {};
+  for (int i = 1; i <= 4; ++i) {
+    a[i][i - 1] = 1.0L;
+    a[i][i] = 4.0L;
+    a[i][i + 1] = 1.0L;
+    a[i][6 + i - 1] += 3.0L;
+    a[i][6 + i] -= 6.0L;
+    a[i][6 + i + 1] += 3.0L;
+  }
+  if (method == PYI_S_C_SPLINE) {
+    a[0][0] = 1.0L;
+    a[5][5] = 1.0L;
+  } else {
+    a[0][0] = 1.0L, a[0][1] = -2.0L, a[0][2] = 1.0L;
+    a[5][3] = 1.0L, a[5][4] = -2.0L, a[5][5] = 1.0L;
+  }
+  for (int c = 0; c < 6; ++c) {  // Gauss-Jordan with partial pivoting
+    int piv = c;
+    for (int r = c + 1; r < 6; ++r) {
+      if (std::fabs(a[r][c]) > std::fabs(a[piv][c])) piv = r;
+    }
+    if (a[piv][c] == 0.0L) return false;
+    for (int k = 0; k < 12; ++k) std::swap(a[c][k], a[piv][k]);
+    const long double inv = 1.0L / a[c][c];
+    for (int k = 0; k < 12; ++k) a[c][k] *= inv;
+    for (int r = 0; r < 6; ++r) {
+      if (r == c || a[r][c] == 0.0L) continue;
+      const long double f = a[r][c];
+      for (int k = 0; k < 12; ++k) a[r][k] -= f * a[c][k];
+    }
+  }
+  for (int j = 0; j < 6; ++j) {
+    const long double g2 = a[2][6 + j], g3 = a[3][6 + j];
+    const long double d2 = j == 2 ? 1.0L : 0.0L, d3 = j == 3 ? 1.0L : 0.0L;
+    cw[j + 1][0] = static_cast<double>(d2);
+    cw[j + 1][1] = static_cast<double>(d3 - d2 - (g3 + 2.0L * g2) / 3.0L);
+    cw[j + 1][2] = static_cast<double>(g2);
+    cw[j + 1][3] = static_cast<double>((g3 - g2) / 3.0L);
+  }
+  return true;
+}
+
 // What a kernel launch on one device reads of a grid.
 struct GridView {
   const void* data{nullptr};
@@ -1393,6 +1457,12 @@ int pyi_windowed(const pyi_grid* grid, const pyi_windowed_nd_config* cfg, int64_
   for (int a = 0; a < 2; ++a) std::memcpy(p.w6[a], grid->w6[a], sizeof(p.w6[a]));
   p.cw_ok = grid->cw_ok;
   std::memcpy(p.cw, grid->cw, sizeof(p.cw));
+  if (cfg->method != PYI_S_BICUBIC) {
+    // the separable stencil also serves the models that are linear in the node
+    // values on axes that qualify for it (pyi_windowed.cu): their own cubics
+    p.cw_ok = grid->cw_ok && nd == 2 && cfg->half_x == 3 && cfg->half_y == 3 &&
+              model_stencil_cubics(cfg->method, p.cw[0]) && model_stencil_cubics(cfg->method, p.cw[1]);
+  }
   p.cells = 1;
   for (int a = 0; a < nd; ++a) p.cells *= grid->shape[a];
   const size_t out_elem = result_is_f64(grid->dtype) ? 8 : 4;

@@ -21,6 +21,10 @@ pytestmark = pytest.mark.gpu
 MODELS = ["akima", "akima_periodic", "c_spline", "c_spline_not_a_knot", "c_spline_periodic", "linear",
           "steffen", "polynomial"]
 SPATIAL = ["bicubic", "bilinear"] + MODELS
+# models that are linear in the window values and cubic on a cell: on a 6 x 6 window of
+# a 2-D float grid with regular ascending axes the tolerance mode computes them with the
+# separable stencil (K4s, pyi_bicubics.cuh), values within the tolerance, not bit-identical
+STENCIL = ("bicubic", "linear", "c_spline", "c_spline_not_a_knot")
 
 
 def _axes(pyi, o, specs):
@@ -111,8 +115,59 @@ def test_bivariate_models(pyi, orc_best, bicubic_mode, model, boundary):
             want, _ = ref.windowed_nd(caxes, g, q[0], q[1], method=model, half_x=half[0], half_y=half[1],
                                       boundary=boundary, num_threads=0)
             exact = close(got, want, 50.0, f"{model} {boundary} {half} {dtype}")
-            assert exact == 1.0 or (bicubic_mode == "weights" and model == "bicubic" and half == (3, 3)), \
+            assert exact == 1.0 or (bicubic_mode == "weights" and model in STENCIL and half == (3, 3)), \
                 (model, boundary, half, dtype, exact)
+
+
+@pytest.mark.parametrize("model", ["linear", "c_spline", "c_spline_not_a_knot"])
+@pytest.mark.parametrize("dtype", ["float64", "float32"])
+def test_stencil_models_on_the_quarter_degree_grid(pyi, synthetic, orc_best, bicubic_mode, model, dtype):
+    """`linear`, `c_spline`, `c_spline_not_a_knot` on the default 6 x 6 window over the
+    0.25 degree grid (circular longitude): the separable stencil with the model's own
+    cubics in tolerance mode, the generic kernel bit for bit in exact mode; both
+    boundary modes, NaN cells, queries on nodes / outside / non-finite, the
+    bounds-error report, host and device memory (bivariate/spline.hpp:96-118)."""
+    import torch
+    ref = orc_best
+    lon, lat = synthetic.lon_axis_values(1440), synthetic.lat_axis_values(720)
+    g = synthetic.field(lon, lat).astype(dtype)
+    rng = np.random.default_rng(77)
+    g[rng.random(g.shape) < 0.0005] = np.nan
+    grid = pyi.Grid(pyi.Axis(lon, period=360.0), pyi.Axis(lat), g)
+    caxes = [ref.axis(lon, period=360.0), ref.axis(lat)]
+    n = 300_000
+    x = rng.uniform(-400.0, 800.0, n)
+    y = rng.uniform(lat[0] - 1.0, lat[-1] + 1.0, n)
+    x[::11] = lon[rng.integers(0, lon.size, x[::11].size)]
+    y[1::13] = lat[rng.integers(0, lat.size, y[1::13].size)]
+    x[2::997] = np.nan
+    y[3::991] = np.inf
+    for boundary in ("undef", "shrink"):
+        cfg = _cfg(pyi, 2, model, (3, 3), boundary)
+        want, _ = ref.windowed_nd(caxes, g, x, y, method=model, half_x=3, half_y=3, boundary=boundary,
+                                  num_threads=0)
+        got = pyi.core.bivariate(grid, x, y, cfg)
+        exact = close(got, want, 1.0, f"{model} {dtype} {boundary} host")
+        assert exact == 1.0 or bicubic_mode == "weights", (model, dtype, boundary, exact)
+        dev = pyi.core.bivariate(grid, torch.from_numpy(x).cuda(), torch.from_numpy(y).cuda(), cfg)
+        assert np.array_equal(dev.cpu().numpy(), got, equal_nan=True), (model, dtype, boundary)
+        # explicit value modes override the process default
+        ex = pyi.core.bivariate(grid, x, y, cfg.with_value_mode("exact"))
+        assert close(ex, want, 1.0, f"{model} {dtype} {boundary} exact mode") == 1.0
+    inside = np.isfinite(x) & np.isfinite(y) & (y >= lat[0]) & (y <= lat[-1])
+    cfg = _cfg(pyi, 2, model, (3, 3), "shrink").with_bounds_error(True)
+    got = pyi.core.bivariate(grid, x[inside], y[inside], cfg)
+    want, _ = ref.windowed_nd(caxes, g, x[inside], y[inside], method=model, half_x=3, half_y=3,
+                              boundary="shrink", num_threads=0)
+    close(got, want, 1.0, f"{model} {dtype} bounds_error on, all inside")
+    xs, ys = x[inside][:50_000].copy(), y[inside][:50_000].copy()
+    ys[40_000] = lat[-1] + 2.0
+    oob = ref.windowed_nd(caxes, g, xs, ys, method=model, half_x=3, half_y=3, boundary="shrink",
+                          bounds_error=True, num_threads=0)[1]
+    assert oob is not None and oob[0] == 40_000
+    with pytest.raises(IndexError) as ei:
+        pyi.core.bivariate(grid, xs, ys, cfg)
+    assert str(ei.value) == oob[2]
 
 
 @pytest.mark.parametrize("model", ["bicubic", "bilinear", "c_spline", "akima", "steffen", "polynomial"])
