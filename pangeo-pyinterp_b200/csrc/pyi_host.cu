@@ -4,6 +4,8 @@
 // values launches the sm_100a kernels of pyi_kernels.cu, and returns
 // PYI_NO_DEVICE when no CUDA device is usable.
 #include <cuda_runtime.h>
+#include <emmintrin.h>
+#include <unistd.h>
 
 #include <algorithm>
 #include <atomic>
@@ -12,6 +14,8 @@
 #include <condition_variable>
 #include <cstdio>
 #include <cstring>
+#include <deque>
+#include <functional>
 #include <map>
 #include <memory>
 #include <mutex>
@@ -282,26 +286,157 @@ bool host_pinned(const void* p) {
   return attr.type == cudaMemoryTypeHost;
 }
 
-void parallel_memcpy(void* dst, const void* src, size_t bytes) {
-  const size_t kMin = 2u << 20;  // bytes per copying thread, at least
-  unsigned hw = std::thread::hardware_concurrency();
-  const unsigned nt = static_cast<unsigned>(
-      std::min<size_t>(std::max(1u, std::min(hw, 16u)), std::max<size_t>(1, bytes / kMin)));
-  if (nt <= 1) {
-    std::memcpy(dst, src, bytes);
+// Staging threads of the host pipeline: a persistent pool shared by every call
+// of the process (round 2: creating and joining 16 threads per 64 MB copy cost a
+// quarter of a pageable call; eight device shards each spawning their own
+// oversubscribed the host).  The caller of run() works on its own batch too, so
+// a batch completes even when every worker is busy with other callers.  The
+// pool is leaked on purpose (no destructor races at exit) and re-created in a
+// forked child, whose copy of it has no threads.
+class CopyPool {
+ public:
+  static CopyPool& get() {
+    static std::mutex mu;
+    static CopyPool* pool = nullptr;
+    static long pid = -1;
+    std::lock_guard<std::mutex> lock(mu);
+    const long me = static_cast<long>(getpid());
+    if (pool == nullptr || pid != me) {
+      pool = new CopyPool();
+      pid = me;
+    }
+    return *pool;
+  }
+  unsigned threads() const { return workers_ + 1; }
+
+  // fn(part) for every part in [0, parts), on the pool's threads and the caller
+  template <typename F>
+  void run(unsigned parts, F&& fn) {
+    if (parts <= 1 || workers_ == 0) {
+      for (unsigned k = 0; k < parts; ++k) fn(k);
+      return;
+    }
+    auto batch = std::make_shared<Batch>();
+    batch->parts = parts;
+    batch->fn = [&fn](unsigned k) { fn(k); };
+    {
+      std::lock_guard<std::mutex> lock(mu_);
+      queue_.push_back(batch);
+    }
+    cv_.notify_all();
+    work(*batch);
+    {
+      std::lock_guard<std::mutex> lock(mu_);
+      auto it = std::find(queue_.begin(), queue_.end(), batch);
+      if (it != queue_.end()) queue_.erase(it);
+    }
+    std::unique_lock<std::mutex> lock(batch->mu);
+    batch->cv.wait(lock, [&] { return batch->done.load() == parts; });
+  }
+
+ private:
+  struct Batch {
+    std::function<void(unsigned)> fn;
+    unsigned parts{0};
+    std::atomic<unsigned> next{0};
+    std::atomic<unsigned> done{0};
+    std::mutex mu;
+    std::condition_variable cv;
+  };
+  static void work(Batch& b) {
+    for (;;) {
+      const unsigned k = b.next.fetch_add(1);
+      if (k >= b.parts) return;
+      b.fn(k);
+      if (b.done.fetch_add(1) + 1 == b.parts) {
+        std::lock_guard<std::mutex> lock(b.mu);
+        b.cv.notify_all();
+      }
+    }
+  }
+  CopyPool() {
+    // PYINTERP_B200_COPY_THREADS: staging threads of the process (default: the host's
+    // hardware threads, at most 32)
+    const char* e = getenv("PYINTERP_B200_COPY_THREADS");
+    const int want = e ? atoi(e) : 0;
+    const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+    const unsigned n = want >= 1 && want <= 256 ? static_cast<unsigned>(want) : std::min(hw, 32u);
+    workers_ = n - 1;
+    for (unsigned t = 0; t < workers_; ++t) {
+      std::thread([this] {
+        for (;;) {
+          std::shared_ptr<Batch> b;
+          {
+            std::unique_lock<std::mutex> lock(mu_);
+            cv_.wait(lock, [&] { return !queue_.empty(); });
+            b = queue_.front();
+            if (b->next.load() >= b->parts) {  // nothing left to claim: retire it
+              queue_.pop_front();
+              continue;
+            }
+          }
+          work(*b);
+        }
+      }).detach();
+    }
+  }
+  std::mutex mu_;
+  std::condition_variable cv_;
+  std::deque<std::shared_ptr<Batch>> queue_;
+  unsigned workers_{0};
+};
+
+// One part of a staging copy with streaming (non-temporal) stores: the
+// destination is not read into the cache first, which saves the write-allocate
+// third of the copy's DRAM traffic -- the staged gigabytes are never touched by
+// the CPU again (the DMA engine reads them).  PYINTERP_B200_COPY=memcpy keeps
+// plain memcpy.
+void stream_copy(char* dst, const char* src, size_t len) {
+  static const bool plain = [] {
+    const char* e = getenv("PYINTERP_B200_COPY");
+    return e != nullptr && e[0] == 'm';
+  }();
+  if (plain || len < 4096) {
+    std::memcpy(dst, src, len);
     return;
   }
-  std::vector<std::thread> th;
-  const size_t part = (bytes / nt + 63) & ~static_cast<size_t>(63);
-  for (unsigned t = 0; t < nt; ++t) {
-    const size_t off = std::min(bytes, t * part);
-    const size_t len = std::min(part, bytes - off);
-    if (len == 0) break;
-    th.emplace_back([=] {
-      std::memcpy(static_cast<char*>(dst) + off, static_cast<const char*>(src) + off, len);
-    });
+  const size_t head = static_cast<size_t>(-reinterpret_cast<uintptr_t>(dst)) & 63;
+  std::memcpy(dst, src, head);
+  dst += head;
+  src += head;
+  len -= head;
+  const size_t blocks = len / 64;
+  for (size_t b = 0; b < blocks; ++b) {
+    const __m128i v0 = _mm_loadu_si128(reinterpret_cast<const __m128i*>(src));
+    const __m128i v1 = _mm_loadu_si128(reinterpret_cast<const __m128i*>(src + 16));
+    const __m128i v2 = _mm_loadu_si128(reinterpret_cast<const __m128i*>(src + 32));
+    const __m128i v3 = _mm_loadu_si128(reinterpret_cast<const __m128i*>(src + 48));
+    _mm_stream_si128(reinterpret_cast<__m128i*>(dst), v0);
+    _mm_stream_si128(reinterpret_cast<__m128i*>(dst + 16), v1);
+    _mm_stream_si128(reinterpret_cast<__m128i*>(dst + 32), v2);
+    _mm_stream_si128(reinterpret_cast<__m128i*>(dst + 48), v3);
+    src += 64;
+    dst += 64;
   }
-  for (auto& t : th) t.join();
+  _mm_sfence();
+  std::memcpy(dst, src, len - blocks * 64);
+}
+
+void parallel_memcpy(void* dst, const void* src, size_t bytes) {
+  const size_t kMin = 1u << 20;  // bytes per part, at least
+  if (bytes < 2 * kMin) {
+    stream_copy(static_cast<char*>(dst), static_cast<const char*>(src), bytes);
+    return;
+  }
+  CopyPool& pool = CopyPool::get();
+  // a few parts per thread: the threads are shared with other calls and finish unevenly
+  const unsigned parts = static_cast<unsigned>(std::min<size_t>(bytes / kMin, 4u * pool.threads()));
+  const size_t part = (bytes / parts + 63) & ~static_cast<size_t>(63);
+  pool.run(parts, [=](unsigned k) {
+    const size_t off = std::min(bytes, k * part);
+    const size_t len = std::min(part, bytes - off);
+    if (len) stream_copy(static_cast<char*>(dst) + off, static_cast<const char*>(src) + off, len);
+  });
 }
 
 // ---------------------------------------------------------------------------
