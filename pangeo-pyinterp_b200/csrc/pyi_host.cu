@@ -775,26 +775,32 @@ void stencil_cubics(const double* w6, double step, double (*cw)[4]) {
 
 // The same table for the fitting models that are LINEAR in the node values and
 // cubic on a cell, bivariate/spline.hpp:96-118 (y, then x) being separable for
-// them: `linear` (univariate/linear.hpp), `c_spline` (cspline.hpp:84-139) and
-// `c_spline_not_a_knot` (cspline_not_a_knot.hpp:114-215).  On uniformly spaced
-// nodes the spline's node coefficients c_i (CSplineBase::x_) times step^2 solve
+// them: `linear` (univariate/linear.hpp) and windowed `bilinear`
+// (bivariate/bilinear.hpp, the same function), `c_spline` (cspline.hpp:84-139),
+// `c_spline_not_a_knot` (cspline_not_a_knot.hpp:114-215) and `c_spline_periodic`
+// (cspline_periodic.hpp:129-201).  On uniformly spaced nodes the spline's node
+// coefficients c_i (CSplineBase::x_) times step^2 solve, whatever the step,
 //   G[i-1] + 4 G[i] + G[i+1] = 3 (y[i+1] - 2 y[i] + y[i-1]),  i = 1..4
-// closed by G[0] = G[5] = 0 (natural) or G[0] - 2 G[1] + G[2] = 0,
-// G[3] - 2 G[4] + G[5] = 0 (not-a-knot), whatever the step; on the centre cell
-// (cspline_base.hpp:32-40,112)
+// closed by G[0] = G[5] = 0 (natural), by G[0] - 2 G[1] + G[2] = 0 and
+// G[3] - 2 G[4] + G[5] = 0 (not-a-knot), or by G[0] = G[5] and the wrap-around
+// row G[4] + 4 G[5] + G[1] = 3 ((y[1] - y[0]) - (y[5] - y[4])) (periodic); on
+// the centre cell (cspline_base.hpp:32-40,112)
 //   s(t) = y2 + t (y3 - y2 - (G3 + 2 G2) / 3) + t^2 G2 + t^3 (G3 - G2) / 3 .
 // Solved for the six unit vectors in long double.  False for the other models.
 bool model_stencil_cubics(int method, double (*cw)[4]) {
   for (int e = 0; e < 8; ++e) {
     for (int c = 0; c < 4; ++c) cw[e][c] = 0.0;
   }
-  if (method == PYI_S_LINEAR) {
+  if (method == PYI_S_LINEAR || method == PYI_S_BILINEAR) {
     cw[3][0] = 1.0;
     cw[3][1] = -1.0;
     cw[4][1] = 1.0;
     return true;
   }
-  if (method != PYI_S_C_SPLINE && method != PYI_S_C_SPLINE_NOT_A_KNOT) return false;
+  if (method != PYI_S_C_SPLINE && method != PYI_S_C_SPLINE_NOT_A_KNOT && method != PYI_S_C_SPLINE_PERIODIC) {
+    return false;
+  }
+  // rows: equations, columns 0..5: G[0..5], columns 6..11: the six unit vectors y = e_j
   long double a[6][12] = {};
   for (int i = 1; i <= 4; ++i) {
     a[i][i - 1] = 1.0L;
@@ -807,9 +813,13 @@ bool model_stencil_cubics(int method, double (*cw)[4]) {
   if (method == PYI_S_C_SPLINE) {
     a[0][0] = 1.0L;
     a[5][5] = 1.0L;
-  } else {
+  } else if (method == PYI_S_C_SPLINE_NOT_A_KNOT) {
     a[0][0] = 1.0L, a[0][1] = -2.0L, a[0][2] = 1.0L;
     a[5][3] = 1.0L, a[5][4] = -2.0L, a[5][5] = 1.0L;
+  } else {
+    a[0][0] = 1.0L, a[0][5] = -1.0L;
+    a[5][4] = 1.0L, a[5][5] = 4.0L, a[5][1] = 1.0L;
+    a[5][6 + 1] += 3.0L, a[5][6 + 0] -= 3.0L, a[5][6 + 5] -= 3.0L, a[5][6 + 4] += 3.0L;
   }
   for (int c = 0; c < 6; ++c) {  // Gauss-Jordan with partial pivoting
     int piv = c;

@@ -38,15 +38,16 @@ cudaError_t launch_windowed_nd(const WinNdParams& p, cudaStream_t stream) {
   if (p.n <= 0) return cudaSuccess;
   // bicubic on a 6 x 6 window, 2-D .. 4-D: precomputed-weights pass, then the
   // generic kernel recomputes the points that pass tagged
-  // `linear`, `c_spline` and `c_spline_not_a_knot` on a 6 x 6 window are linear in
-  // the window values and cubic on a cell: in tolerance mode the separable
-  // stencil (K4s) serves them with their own cubics (pyi_host.cu:
+  // `linear` / `bilinear` and the three `c_spline` models on a 6 x 6 window are
+  // linear in the window values and cubic on a cell: in tolerance mode the
+  // separable stencil (K4s) serves them with their own cubics (pyi_host.cu:
   // model_stencil_cubics); everything else about a point is the bicubic case
   const char* which = getenv("PYINTERP_B200_BICUBIC");
   const bool weights_only = which != nullptr && which[0] == 'w';
   const bool stencil_model = p.ndim == 2 && p.half_x == 3 && p.half_y == 3 && p.cw_ok &&
-                             (p.method == PYI_S_LINEAR || p.method == PYI_S_C_SPLINE ||
-                              p.method == PYI_S_C_SPLINE_NOT_A_KNOT) &&
+                             (p.method == PYI_S_LINEAR || p.method == PYI_S_BILINEAR ||
+                              p.method == PYI_S_C_SPLINE || p.method == PYI_S_C_SPLINE_NOT_A_KNOT ||
+                              p.method == PYI_S_C_SPLINE_PERIODIC) &&
                              !weights_only && bicubics_eligible(p);
   if (p.ndim >= 2 && (p.method == PYI_S_BICUBIC || stencil_model) && p.half_x == 3 && p.half_y == 3 &&
       p.w_ok && (p.ndim == 2 || p.planes) && !force_generic() && !exact_bicubic(p)) {
