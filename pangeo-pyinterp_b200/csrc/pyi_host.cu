@@ -1590,8 +1590,13 @@ int pyi_windowed(const pyi_grid* grid, const pyi_windowed_nd_config* cfg, int64_
     p.u6_ok[a] = grid->u6_ok[a];
     std::memcpy(p.u6[a], grid->u6[a], sizeof(p.u6[a]));
   }
+  // the plane-major copy serves bicubic in every mode and, unless the caller asks for
+  // bit-identical values, the other models' 6 x 6 fast pass (pyi_winmodels.cuh)
   const bool want_planes =
-      nd >= 3 && cfg->method == PYI_S_BICUBIC && cfg->half_x == 3 && cfg->half_y == 3;
+      nd >= 3 && cfg->half_x == 3 && cfg->half_y == 3 &&
+      (cfg->method == PYI_S_BICUBIC ||
+       (cfg->method != PYI_S_POLYNOMIAL && cfg->value_mode != PYI_VALUES_EXACT && grid->cw_ok &&
+        (grid->dtype == PYI_F64 || grid->dtype == PYI_F32)));
   if (want_planes) {
     DeviceGuard guard(grid->device);
     if (guard.err != cudaSuccess) return cuda_fail(guard.err, "cudaSetDevice");
@@ -1605,8 +1610,10 @@ int pyi_windowed(const pyi_grid* grid, const pyi_windowed_nd_config* cfg, int64_
   if (cfg->method != PYI_S_BICUBIC) {
     // the separable stencil also serves the models that are linear in the node
     // values on axes that qualify for it (pyi_windowed.cu): their own cubics
-    p.cw_ok = grid->cw_ok && nd == 2 && cfg->half_x == 3 && cfg->half_y == 3 &&
-              model_stencil_cubics(cfg->method, p.cw[0]) && model_stencil_cubics(cfg->method, p.cw[1]);
+    const bool local = cfg->method == PYI_S_AKIMA || cfg->method == PYI_S_AKIMA_PERIODIC ||
+                       cfg->method == PYI_S_STEFFEN;  // no table: pyi_winmodels.cuh
+    p.cw_ok = grid->cw_ok && nd >= 2 && cfg->half_x == 3 && cfg->half_y == 3 &&
+              (local || (model_stencil_cubics(cfg->method, p.cw[0]) && model_stencil_cubics(cfg->method, p.cw[1])));
   }
   p.cells = 1;
   for (int a = 0; a < nd; ++a) p.cells *= grid->shape[a];

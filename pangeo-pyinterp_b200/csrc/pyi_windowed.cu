@@ -24,6 +24,7 @@ static bool force_generic() {
 #include "pyi_fastwin_nd.cuh"
 #include "pyi_bicubicw.cuh"
 #include "pyi_bicubics.cuh"
+#include "pyi_winmodels.cuh"
 
 namespace pyi {
 // K6 (pyi_windowed_nd.cuh) is instantiated per window capacity in
@@ -80,6 +81,16 @@ cudaError_t launch_windowed_nd(const WinNdParams& p, cudaStream_t stream) {
       if (e == cudaSuccess) e = e2;
     }
     return e;
+  }
+  // akima / akima_periodic / steffen (2-D .. 4-D) and the linear-in-values models on
+  // 3-D / 4-D grids, 6 x 6 window, tolerance mode: K4m, then the redo pass (scanning)
+  if (!weights_only && !force_generic() && !exact_bicubic(p) && winmodels_eligible(p)) {
+    cudaError_t e = launch_winmodels(p, stream);
+    if (e != cudaSuccess) return e;
+    WinNdParams q = p;
+    q.redo = 1;
+    q.queue = nullptr;
+    return launch_windowed_nd_w<6>(q, stream);
   }
   // 2-D bicubic / bilinear keep K4 and its fast path
   if (p.ndim == 2 && p.method <= PYI_S_BILINEAR) {

@@ -25,6 +25,9 @@ SPATIAL = ["bicubic", "bilinear"] + MODELS
 # a 2-D float grid with regular ascending axes the tolerance mode computes them with the
 # separable stencil (K4s, pyi_bicubics.cuh), values within the tolerance, not bit-identical
 STENCIL = ("bicubic", "bilinear", "linear", "c_spline", "c_spline_not_a_knot", "c_spline_periodic")
+# akima / akima_periodic / steffen have a 6 x 6 tolerance kernel too (K4m, pyi_winmodels.cuh, 2-D .. 4-D),
+# which also serves the linear-in-values models on 3-D / 4-D grids; only polynomial stays generic
+FAST6 = STENCIL + ("akima", "akima_periodic", "steffen")
 
 
 def _axes(pyi, o, specs):
@@ -115,11 +118,12 @@ def test_bivariate_models(pyi, orc_best, bicubic_mode, model, boundary):
             want, _ = ref.windowed_nd(caxes, g, q[0], q[1], method=model, half_x=half[0], half_y=half[1],
                                       boundary=boundary, num_threads=0)
             exact = close(got, want, 50.0, f"{model} {boundary} {half} {dtype}")
-            assert exact == 1.0 or (bicubic_mode == "weights" and model in STENCIL and half == (3, 3)), \
+            assert exact == 1.0 or (bicubic_mode == "weights" and model in FAST6 and half == (3, 3)), \
                 (model, boundary, half, dtype, exact)
 
 
-@pytest.mark.parametrize("model", ["bilinear", "linear", "c_spline", "c_spline_not_a_knot", "c_spline_periodic"])
+@pytest.mark.parametrize("model", ["bilinear", "linear", "c_spline", "c_spline_not_a_knot", "c_spline_periodic",
+                                   "akima", "akima_periodic", "steffen"])
 @pytest.mark.parametrize("dtype", ["float64", "float32"])
 def test_stencil_models_on_the_quarter_degree_grid(pyi, synthetic, orc_best, bicubic_mode, model, dtype):
     """The fitting models that are linear in the window values on the default 6 x 6 window over the
@@ -195,7 +199,7 @@ def test_trivariate_models(pyi, orc_best, bicubic_mode, model, z_kind, z_method)
             want, _ = ref.windowed_nd(caxes, g, q[0], q[1], q[2], method=model, boundary=boundary,
                                       num_threads=0, z_method=0 if z_method == "linear" else 1)
             exact = close(got, want, 50.0, f"{model} {z_kind} {z_method} {boundary} {dtype}")
-            assert exact == 1.0 or (bicubic_mode == "weights" and model == "bicubic"), \
+            assert exact == 1.0 or (bicubic_mode == "weights" and model in FAST6), \
                 (model, z_kind, z_method, boundary, dtype, exact)
 
 
@@ -219,6 +223,32 @@ def test_quadrivariate_models(pyi, orc_best, model, methods):
                                   u_method=0 if methods[1] == "linear" else 1)
         exact = close(got, want, 50.0, f"{model} {methods} {dtype}")
         assert exact == 1.0, (model, methods, dtype, exact)
+
+
+@pytest.mark.parametrize("model", ["c_spline", "linear", "akima", "akima_periodic", "steffen"])
+def test_quadrivariate_models_default_window(pyi, orc_best, bicubic_mode, model):
+    """4-D grids, the default 6 x 6 window: the tolerance pass over the plane-major copy
+    (pyi_winmodels.cuh) against the reference, both boundary modes, every z / u method."""
+    ref = orc_best
+    iz = axes_zoo.i64_axes()
+    specs = [(np.arange(36) * 10.0, dict(period=360.0), False), (-85.0 + np.arange(18) * 10.0, {}, False),
+             iz["monthly30"], (np.round(5500.0 * (np.arange(9) / 8) ** 2.2, 1), {}, False)]
+    gaxes, caxes = _axes(pyi, ref, specs)
+    ds = [c.describe() for c in caxes]
+    for dtype in ("float32", "float64"):
+        g = _field(tuple(d["size"] for d in ds), dtype, nan=0.0005)
+        grid = pyi.Grid(*gaxes, g)
+        q = _queries(4, 10_000, 6)
+        for boundary, methods in (("undef", ("linear", "linear")), ("shrink", ("nearest", "linear")),
+                                  ("undef", ("linear", "nearest"))):
+            cfg = _cfg(pyi, 4, model, (3, 3), boundary, z_method=methods[0], u_method=methods[1])
+            got = pyi.core.quadrivariate(grid, q[0], q[1], q[2].view("datetime64[ns]"), q[3], cfg)
+            want, _ = ref.windowed_nd(caxes, g, q[0], q[1], q[2], q[3], method=model, half_x=3, half_y=3,
+                                      boundary=boundary, num_threads=0,
+                                      z_method=0 if methods[0] == "linear" else 1,
+                                      u_method=0 if methods[1] == "linear" else 1)
+            exact = close(got, want, 50.0, f"{model} {methods} {boundary} {dtype}")
+            assert exact == 1.0 or bicubic_mode == "weights", (model, methods, boundary, dtype, exact)
 
 
 def test_windowed_nd_bounds_error_and_device_tensors(pyi, orc_best):
