@@ -46,9 +46,9 @@ BYTES_PER_POINT = {"bilinear": 24, "bilinear_irrlat": 24, "bicubic": 24, "trivar
                    # the same 2-D grid stored as float32 (float32 results: 16 in + 4 out)
                    "bilinear_f32": 20,
                    # K6: streams only; the windows are compute / L2 work
-                   "c_spline2d": 24, "akima2d": 24, "steffen2d": 24, "bicubic3d": 28, "c_spline3d": 28}
+                   "c_spline2d": 24, "akima2d": 24, "steffen2d": 24, "polynomial2d": 24, "bicubic3d": 28, "c_spline3d": 28}
 # windowed workloads: fitting model of the public API
-WINDOWED = {"bicubic": "bicubic", "c_spline2d": "c_spline", "akima2d": "akima", "steffen2d": "steffen",
+WINDOWED = {"bicubic": "bicubic", "c_spline2d": "c_spline", "akima2d": "akima", "steffen2d": "steffen", "polynomial2d": "polynomial",
             "bicubic3d": "bicubic", "c_spline3d": "c_spline"}
 # geometric workloads: spatial method of the public API (default bilinear)
 GEOMETRIC = {"idw": "idw"}
@@ -75,7 +75,7 @@ def default_points(workload: str) -> int:
     return {"bilinear": 1_000_000_000, "bilinear_irrlat": 1_000_000_000, "bilinear_f32": 1_000_000_000,
             "idw": 100_000_000,
             "trivariate_f64": 100_000_000, "bicubic": 100_000_000, "trivariate": 100_000_000,
-            "quadrivariate": 100_000_000, "c_spline2d": 20_000_000, "akima2d": 20_000_000, "steffen2d": 20_000_000,
+            "quadrivariate": 100_000_000, "c_spline2d": 20_000_000, "akima2d": 20_000_000, "steffen2d": 20_000_000, "polynomial2d": 20_000_000,
             "bicubic3d": 20_000_000, "c_spline3d": 20_000_000}[workload]
 
 
@@ -112,7 +112,7 @@ def build_host_case(workload: str):
         lat = syn.irregular_lat_values()
     if workload == "bilinear_f32":
         return dict(nd=2, lon=lon, lat=lat, grid=syn.field(lon, lat).astype(np.float32), dtype="f32")
-    if workload in ("bilinear", "bilinear_irrlat", "bicubic", "c_spline2d", "akima2d", "steffen2d", "idw"):
+    if workload in ("bilinear", "bilinear_irrlat", "bicubic", "c_spline2d", "akima2d", "steffen2d", "polynomial2d", "idw"):
         return dict(nd=2, lon=lon, lat=lat, grid=syn.field(lon, lat), dtype="f64")
     if workload == "trivariate_f64":
         t = syn.time_axis_values(120)
@@ -145,6 +145,7 @@ def workload_name(workload, n):
              "bicubic3d": "trivariate windowed bicubic (6x6 window, linear in time) f32 Grid3D 1440x720x365",
              "akima2d": "bivariate windowed akima (6x6 window) f64 Grid2D 1440x720 circular lon",
              "steffen2d": "bivariate windowed steffen (6x6 window) f64 Grid2D 1440x720 circular lon",
+             "polynomial2d": "bivariate windowed polynomial (6x6 window) f64 Grid2D 1440x720 circular lon",
              "c_spline3d": "trivariate windowed c_spline (6x6 window, linear in time) f32 Grid3D 1440x720x365",
              "quadrivariate": "quadrivariate bilinear f32 Grid4D 1440x720x12x50 time on z, irregular depth on u"}
     return f"{shape[workload]}, {n:.3g} uniform random points per GPU"

@@ -847,6 +847,59 @@ bool model_stencil_cubics(int method, double (*cw)[4]) {
   return true;
 }
 
+// `polynomial` (univariate/polynomial.hpp:58-102) on six uniformly spaced nodes as six
+// quintics in the cell coordinate t: the value is the Newton form
+// sum_k work[k] prod_{m<k} (x - xa[m]) of the reference's divided-difference table, which is
+// linear in the node values.  The table is the REFERENCE's: its in-place update reads entries
+// it has already overwritten (Eigen's SSE2 packet traversal of an aliased expression, restated
+// in pyi_univariate.cuh: uni_polynomial), mixing difference orders -- so, unlike the spline
+// models, the weights depend on the spacing and are built per axis from its step.
+void polynomial_stencil(double step, double (*pw)[6]) {
+  constexpr int n = 6;
+  const long double h = step;
+  long double work[n][n] = {};  // work[k][j]: coefficient of y[j] in work[k]
+  work[0][0] = 1.0L;
+  for (int k = 1; k < n; ++k) {
+    work[k][k] = 1.0L / h;
+    work[k][k - 1] = -1.0L / h;
+  }
+  auto update = [&](long double* dst, const long double* a, const long double* b, int ix) {
+    for (int j = 0; j < n; ++j) dst[j] = (a[j] - b[j]) / (ix * h);
+  };
+  for (int ix = 2; ix < n; ++ix) {
+    const int cnt = n - ix;
+    int k = 0;
+    const int peel = (ix & 1) < cnt ? (ix & 1) : cnt;
+    for (; k < peel; ++k) update(work[ix + k], work[ix + k], work[ix - 1 + k], ix);
+    for (; k + 2 <= cnt; k += 2) {  // a packet: both lanes read before either is stored
+      long double a0[n], a1[n];
+      update(a0, work[ix + k], work[ix - 1 + k], ix);
+      update(a1, work[ix + k + 1], work[ix + k], ix);
+      for (int j = 0; j < n; ++j) {
+        work[ix + k][j] = a0[j];
+        work[ix + k + 1][j] = a1[j];
+      }
+    }
+    for (; k < cnt; ++k) update(work[ix + k], work[ix + k], work[ix - 1 + k], ix);
+  }
+  long double poly[n][n] = {};  // poly[j][d]: coefficient of t^d in the weight of y[j]
+  long double basis[n] = {1.0L};  // prod_{m<k} (x - xa[m]) with x = xa[2] + t h
+  for (int k = 0; k < n; ++k) {
+    if (k > 0) {
+      const long double c = 2.0L - (k - 1);
+      long double next[n];
+      for (int d = 0; d < n; ++d) next[d] = ((d > 0 ? basis[d - 1] : 0.0L) + c * basis[d]) * h;
+      for (int d = 0; d < n; ++d) basis[d] = next[d];
+    }
+    for (int j = 0; j < n; ++j) {
+      for (int d = 0; d < n; ++d) poly[j][d] += work[k][j] * basis[d];
+    }
+  }
+  for (int j = 0; j < n; ++j) {
+    for (int d = 0; d < n; ++d) pw[j][d] = static_cast<double>(poly[j][d]);
+  }
+}
+
 // What a kernel launch on one device reads of a grid.
 struct GridView {
   const void* data{nullptr};
@@ -1595,7 +1648,7 @@ int pyi_windowed(const pyi_grid* grid, const pyi_windowed_nd_config* cfg, int64_
   const bool want_planes =
       nd >= 3 && cfg->half_x == 3 && cfg->half_y == 3 &&
       (cfg->method == PYI_S_BICUBIC ||
-       (cfg->method != PYI_S_POLYNOMIAL && cfg->value_mode != PYI_VALUES_EXACT && grid->cw_ok &&
+       (cfg->value_mode != PYI_VALUES_EXACT && grid->cw_ok &&
         (grid->dtype == PYI_F64 || grid->dtype == PYI_F32)));
   if (want_planes) {
     DeviceGuard guard(grid->device);
@@ -1613,7 +1666,11 @@ int pyi_windowed(const pyi_grid* grid, const pyi_windowed_nd_config* cfg, int64_
     const bool local = cfg->method == PYI_S_AKIMA || cfg->method == PYI_S_AKIMA_PERIODIC ||
                        cfg->method == PYI_S_STEFFEN;  // no table: pyi_winmodels.cuh
     p.cw_ok = grid->cw_ok && nd >= 2 && cfg->half_x == 3 && cfg->half_y == 3 &&
-              (local || (model_stencil_cubics(cfg->method, p.cw[0]) && model_stencil_cubics(cfg->method, p.cw[1])));
+              (local || cfg->method == PYI_S_POLYNOMIAL ||
+               (model_stencil_cubics(cfg->method, p.cw[0]) && model_stencil_cubics(cfg->method, p.cw[1])));
+    if (p.cw_ok && cfg->method == PYI_S_POLYNOMIAL) {
+      for (int a = 0; a < 2; ++a) polynomial_stencil(grid->dax[a].step, p.pw[a]);
+    }
   }
   p.cells = 1;
   for (int a = 0; a < nd; ++a) p.cells *= grid->shape[a];

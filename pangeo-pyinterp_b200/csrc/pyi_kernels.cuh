@@ -94,12 +94,17 @@ struct WinNdParams {
   // zero), valid when cw_ok
   int32_t cw_ok;
   double cw[2][8][4];
+  // `polynomial` on a 6 x 6 window (pyi_winmodels.cuh): the six window weights of the x / y
+  // axis as quintics in the cell coordinate (pyi_host.cu: polynomial_stencil), valid when cw_ok
+  double pw[2][6][6];
   // separable pass: queue[0] counts the points it tagged for the redo pass,
   // queue[1 ..] holds the first queue_cap of them; the redo pass scans the
   // output for tags only when there is no queue or it overflowed
   unsigned* queue;
   unsigned queue_cap;
 };
+
+static_assert(sizeof(WinNdParams) <= 4000, "kernel parameters are limited to 4 KB");
 
 struct FindParams {
   DAxis ax;

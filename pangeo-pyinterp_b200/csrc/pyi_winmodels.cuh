@@ -24,7 +24,10 @@
 //   * the models that are linear in the values (linear / bilinear, c_spline,
 //     c_spline_not_a_knot, c_spline_periodic) on 3-D / 4-D grids: two dot
 //     products with the model's six cubics (pyi_host.cu: model_stencil_cubics);
-//     2-D grids take the separable kernel (pyi_bicubics.cuh) instead.
+//     2-D grids take the separable kernel (pyi_bicubics.cuh) instead;
+//   * polynomial (polynomial.hpp:58-102), also linear in the values: dot
+//     products with six quintics built from the reference's own (aliased)
+//     divided-difference table and the axis step (pyi_host.cu: polynomial_stencil).
 // No division by a spacing is left (the reference divides by the rounded node
 // differences; axes whose max |coordinate| / |step| reaches 2^16 stay on the
 // generic kernel, as for bicubic): values agree with the reference to rounding
@@ -37,7 +40,11 @@
 
 namespace pyi {
 
-enum { WM_STENCIL = 0, WM_AKIMA = 1, WM_STEFFEN = 2 };
+enum { WM_STENCIL = 0, WM_AKIMA = 1, WM_STEFFEN = 2, WM_POLY = 3 };
+
+__device__ __forceinline__ double quintic(const double (&c)[6], double t) {
+  return fma(fma(fma(fma(fma(c[5], t, c[4]), t, c[3]), t, c[2]), t, c[1]), t, c[0]);
+}
 
 __device__ __forceinline__ double hermite_unit(double v2, double a2, double d2, double d3, double t) {
   const double c = fma(-2.0, d2, fma(3.0, a2, -d3));
@@ -77,7 +84,7 @@ __device__ __forceinline__ double steffen6(const double (&v)[6], double t) {
 template <int MODEL>
 __device__ __forceinline__ double winmodel6(const WinNdParams& p, const double (&v)[6], const double (&w)[6],
                                             double t) {
-  if (MODEL == WM_STENCIL) return dot6(w, v);
+  if (MODEL == WM_STENCIL || MODEL == WM_POLY) return dot6(w, v);
   if (MODEL == WM_AKIMA) return akima6(v, t, p.method == PYI_S_AKIMA_PERIODIC);
   return steffen6(v, t);
 }
@@ -139,6 +146,13 @@ __device__ __forceinline__ bool winmodel_point(const WinNdParams& p, double x, d
     for (int j = 0; j < 6; ++j) {
       wx[j] = cubic4(p.cw[0][j + 1][0], p.cw[0][j + 1][1], p.cw[0][j + 1][2], p.cw[0][j + 1][3], tx);
       wy[j] = cubic4(p.cw[1][j + 1][0], p.cw[1][j + 1][1], p.cw[1][j + 1][2], p.cw[1][j + 1][3], ty);
+    }
+  }
+  if (MODEL == WM_POLY) {
+#pragma unroll
+    for (int j = 0; j < 6; ++j) {
+      wx[j] = quintic(p.pw[0][j], tx);
+      wy[j] = quintic(p.pw[1][j], ty);
     }
   }
   const long long n1 = ay.n;
@@ -234,6 +248,8 @@ static int winmodel_of(const WinNdParams& p) {
       return WM_AKIMA;
     case PYI_S_STEFFEN:
       return WM_STEFFEN;
+    case PYI_S_POLYNOMIAL:
+      return WM_POLY;
     case PYI_S_LINEAR:
     case PYI_S_BILINEAR:
     case PYI_S_C_SPLINE:
@@ -273,6 +289,7 @@ static void launch_winmodels_z(const WinNdParams& p, cudaStream_t stream) {
   switch (winmodel_of(p)) {
     case WM_AKIMA: launch_winmodels_m<ND, ZT, WM_AKIMA>(p, stream); break;
     case WM_STEFFEN: launch_winmodels_m<ND, ZT, WM_STEFFEN>(p, stream); break;
+    case WM_POLY: launch_winmodels_m<ND, ZT, WM_POLY>(p, stream); break;
     default:
       if constexpr (ND >= 3) launch_winmodels_m<ND, ZT, WM_STENCIL>(p, stream);
       break;

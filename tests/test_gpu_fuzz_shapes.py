@@ -159,7 +159,7 @@ def test_random_windowed_models(pyi, orc_best, seed):
     # smallest window a model can fit (fewer nodes: NaN everywhere, nothing to compare)
     least = {"akima": 3, "akima_periodic": 3, "bilinear": 1, "linear": 1, "polynomial": 1}.get(model, 2)
     half = (int(rng.integers(least, 5)), int(rng.integers(least, 5)))
-    if model != "polynomial" and seed % 2 == 0:
+    if seed % 2 == 0:
         half = (3, 3)  # the fast kernels' window (bicubic; the stencil also serves the linear-in-values models)
     if model == "c_spline_periodic":
         half, boundary = (half[0], half[0]), "undef"  # DESIGN.md, deviations: equal, unshrunken windows only

@@ -26,8 +26,8 @@ SPATIAL = ["bicubic", "bilinear"] + MODELS
 # separable stencil (K4s, pyi_bicubics.cuh), values within the tolerance, not bit-identical
 STENCIL = ("bicubic", "bilinear", "linear", "c_spline", "c_spline_not_a_knot", "c_spline_periodic")
 # akima / akima_periodic / steffen have a 6 x 6 tolerance kernel too (K4m, pyi_winmodels.cuh, 2-D .. 4-D),
-# which also serves the linear-in-values models on 3-D / 4-D grids; only polynomial stays generic
-FAST6 = STENCIL + ("akima", "akima_periodic", "steffen")
+# which also serves polynomial and, on 3-D / 4-D grids, the other linear-in-values models
+FAST6 = STENCIL + ("akima", "akima_periodic", "steffen", "polynomial")
 
 
 def _axes(pyi, o, specs):
@@ -123,7 +123,7 @@ def test_bivariate_models(pyi, orc_best, bicubic_mode, model, boundary):
 
 
 @pytest.mark.parametrize("model", ["bilinear", "linear", "c_spline", "c_spline_not_a_knot", "c_spline_periodic",
-                                   "akima", "akima_periodic", "steffen"])
+                                   "akima", "akima_periodic", "steffen", "polynomial"])
 @pytest.mark.parametrize("dtype", ["float64", "float32"])
 def test_stencil_models_on_the_quarter_degree_grid(pyi, synthetic, orc_best, bicubic_mode, model, dtype):
     """The fitting models that are linear in the window values on the default 6 x 6 window over the
@@ -225,7 +225,7 @@ def test_quadrivariate_models(pyi, orc_best, model, methods):
         assert exact == 1.0, (model, methods, dtype, exact)
 
 
-@pytest.mark.parametrize("model", ["c_spline", "linear", "akima", "akima_periodic", "steffen"])
+@pytest.mark.parametrize("model", ["c_spline", "linear", "akima", "akima_periodic", "steffen", "polynomial"])
 def test_quadrivariate_models_default_window(pyi, orc_best, bicubic_mode, model):
     """4-D grids, the default 6 x 6 window: the tolerance pass over the plane-major copy
     (pyi_winmodels.cuh) against the reference, both boundary modes, every z / u method."""
