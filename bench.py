@@ -686,7 +686,8 @@ def main():
     if args.workload == "bilinear" and not args.no_secondary:
         del grid
         torch.cuda.empty_cache()
-        sub = [("bicubic", 100_000_000, ()), ("c_spline2d", 100_000_000, ()), ("trivariate", 100_000_000, ()),
+        sub = [("bicubic", 100_000_000, ()), ("c_spline2d", 100_000_000, ()), ("akima2d", 50_000_000, ()),
+               ("trivariate", 100_000_000, ()),
                ("quadrivariate", 100_000_000, ()),
                ("idw", 100_000_000, ()), ("trivariate_f64", 100_000_000, ()), ("bilinear_f32", 400_000_000, ()),
                ("bilinear_irrlat", 1_000_000_000, (1_000_000, 10_000_000, 100_000_000, 1_000_000_000))]

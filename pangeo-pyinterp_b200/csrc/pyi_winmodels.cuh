@@ -223,8 +223,8 @@ __device__ __forceinline__ bool winmodel_point(const WinNdParams& p, double x, d
   return true;
 }
 
-template <int DT, int ND, typename ZT, typename R, int MODEL>
-__global__ void __launch_bounds__(128, ND == 2 ? 5 : 1)
+template <int DT, int ND, typename ZT, typename R, int MODEL, int MINB>
+__global__ void __launch_bounds__(128, MINB)
 winmodel_kernel(const __grid_constant__ WinNdParams p) {
   const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
   R* __restrict__ out = static_cast<R*>(p.out);
@@ -274,13 +274,28 @@ static bool winmodels_eligible(const WinNdParams& p) {
   return p.dtype != PYI_F64 || (reinterpret_cast<uintptr_t>(data) & 15) == 0;
 }
 
+template <int ND, typename ZT, int MODEL, int MINB>
+static void launch_winmodels_b(const WinNdParams& p, cudaStream_t stream) {
+  const int blocks = grid_for(p.n, 128, MINB < 4 ? 8 : MINB);
+  if (p.dtype == PYI_F64) {
+    winmodel_kernel<PYI_F64, ND, ZT, double, MODEL, MINB><<<blocks, 128, 0, stream>>>(p);
+  } else {
+    winmodel_kernel<PYI_F32, ND, ZT, float, MODEL, MINB><<<blocks, 128, 0, stream>>>(p);
+  }
+}
+
 template <int ND, typename ZT, int MODEL>
 static void launch_winmodels_m(const WinNdParams& p, cudaStream_t stream) {
-  const int blocks = grid_for(p.n, 128, ND == 2 ? 5 : 8);
-  if (p.dtype == PYI_F64) {
-    winmodel_kernel<PYI_F64, ND, ZT, double, MODEL><<<blocks, 128, 0, stream>>>(p);
+  // resident blocks per SM: 2-D (L2-resident grid, latency bound) 8 x 128 threads at <= 64
+  // registers; 3-D / 4-D (DRAM bound) no cap.  PYINTERP_B200_M_MINB = 5 | 8 | 10 for experiments.
+  if constexpr (ND == 2) {
+    const char* e = getenv("PYINTERP_B200_M_MINB");
+    const int minb = e ? atoi(e) : 8;
+    if (minb == 5) return launch_winmodels_b<ND, ZT, MODEL, 5>(p, stream);
+    if (minb == 10) return launch_winmodels_b<ND, ZT, MODEL, 10>(p, stream);
+    return launch_winmodels_b<ND, ZT, MODEL, 8>(p, stream);
   } else {
-    winmodel_kernel<PYI_F32, ND, ZT, float, MODEL><<<blocks, 128, 0, stream>>>(p);
+    return launch_winmodels_b<ND, ZT, MODEL, 1>(p, stream);
   }
 }
 
