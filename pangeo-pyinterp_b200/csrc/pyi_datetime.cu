@@ -114,6 +114,21 @@ __device__ __forceinline__ long long order_of_magnitude(int resolution) {
   }
 }
 
+// a / 1000^k truncating, k = 0 .. 6 (warp-uniform switch): a division by a
+// run-time 64-bit divisor is a ~100-instruction subroutine, by a constant a
+// multiply-high -- the kernel went from 17-24 % to the HBM roofline's range
+__device__ __forceinline__ long long div_pow1000(long long a, int k) {
+  switch (k) {
+    case 0: return a;
+    case 1: return a / 1000LL;
+    case 2: return a / 1000000LL;
+    case 3: return a / 1000000000LL;
+    case 4: return a / 1000000000000LL;
+    case 5: return a / 1000000000000000LL;
+    default: return a / 1000000000000000000LL;
+  }
+}
+
 // one value of dateutils::convert (dateutils.hpp:845-933)
 __device__ __forceinline__ long long convert_one(long long value, int src, int dst,
                                                  long long src_mag, long long dst_mag, int& bad) {
@@ -149,8 +164,8 @@ __device__ __forceinline__ long long convert_one(long long value, int src, int d
       break;
     default: {
       // FractionalSeconds::epoch + days_since_epoch (dateutils.hpp:402-412,473-482)
-      long long sec = value / src_mag;
-      long long frac = value % src_mag;
+      long long sec = div_pow1000(value, src - PYI_RES_SECOND);  // value / src_mag
+      long long frac = value - sec * src_mag;                     // value % src_mag
       if (frac < 0) {
         frac += src_mag;
         sec -= 1;
@@ -185,8 +200,9 @@ __device__ __forceinline__ long long convert_one(long long value, int src, int d
                             ckd_mul(seconds, dst_mag, bad), bad);
       if (src >= PYI_RES_SECOND) {
         // FractionalSeconds::cast (dateutils.hpp:422-427)
-        const long long c = src_mag <= dst_mag ? ckd_mul(dst_mag / src_mag, fractional, bad)
-                                               : fractional / (src_mag / dst_mag);
+        // dst_mag / src_mag and src_mag / dst_mag are powers of 1000
+        const long long c = src_mag <= dst_mag ? ckd_mul(order_of_magnitude(PYI_RES_SECOND + dst - src), fractional, bad)
+                                               : div_pow1000(fractional, src - dst);
         v = ckd_add(v, c, bad);
       }
       return v;
@@ -194,9 +210,44 @@ __device__ __forceinline__ long long convert_one(long long value, int src, int d
   }
 }
 
+// Closed form of convert_one between two FIXED-LENGTH units (day .. picosecond):
+// the normalisation to (days, seconds, fraction) and back is value * F when the
+// source unit is the longer one (F = ratio of the unit lengths) and
+// floor(value / G) when it is the shorter one -- as long as none of the
+// reference's checked operations can overflow, which `safe_abs` guarantees
+// (every intermediate is bounded by |value| * max(F, 1) + 3 * 86400 * dst_mag).
+// Values beyond it, and every other unit pair (calendar units, weeks, femto- /
+// attoseconds whose day products overflow for any negative value), take the
+// checked sequence.  KIND 0: none, 1: multiply, 2: floor-divide.
+struct FastPlan {
+  int kind;
+  long long factor;
+  unsigned long long safe_abs;
+  double inv_factor;
+};
+
+__device__ __forceinline__ long long floor_div(long long a, long long g, double inv_g) {
+  using U = unsigned long long;
+  long long q = static_cast<long long>(floor(static_cast<double>(a) * inv_g));
+  // |r| <= 2 g + 2^12: the quotient of the doubles is off by a few units at most; q g itself may
+  // pass the int64 range by that much next to its ends, hence the wrapping (unsigned) products
+  long long r = static_cast<long long>(static_cast<U>(a) - static_cast<U>(q) * static_cast<U>(g));
+  const long long q2 = static_cast<long long>(floor(static_cast<double>(r) * inv_g));
+  q += q2;
+  r = static_cast<long long>(static_cast<U>(r) - static_cast<U>(q2) * static_cast<U>(g));
+  if (r < 0) {
+    --q;
+  } else if (r >= g) {
+    ++q;
+  }
+  return q;
+}
+
+template <int KIND>
 __global__ void __launch_bounds__(kThreads)
 datetime_convert_kernel(const long long* __restrict__ in, long long* __restrict__ out, long long n,
-                        long long index_base, int src, int dst, unsigned long long* bad_key) {
+                        long long index_base, int src, int dst, const FastPlan plan,
+                        unsigned long long* bad_key) {
   const long long src_mag = src >= PYI_RES_SECOND ? order_of_magnitude(src) : 1;
   const long long dst_mag = dst >= PYI_RES_SECOND ? order_of_magnitude(dst) : 0;
   const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
@@ -204,7 +255,15 @@ datetime_convert_kernel(const long long* __restrict__ in, long long* __restrict_
   for (long long k = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; k < n;
        k += stride) {
     int bad = 0;
-    const long long v = convert_one(__ldcs(in + k), src, dst, src_mag, dst_mag, bad);
+    const long long value = __ldcs(in + k);
+    long long v;
+    const unsigned long long mag = value < 0 ? 0ULL - static_cast<unsigned long long>(value)
+                                             : static_cast<unsigned long long>(value);
+    if (KIND != 0 && mag <= plan.safe_abs) {
+      v = KIND == 1 ? value * plan.factor : floor_div(value, plan.factor, plan.inv_factor);
+    } else {
+      v = convert_one(value, src, dst, src_mag, dst_mag, bad);
+    }
     __stcs(out + k, v);
     if (bad != 0) {
       const unsigned long long kk =
@@ -222,8 +281,34 @@ cudaError_t launch_datetime_convert(const long long* in, long long* out, long lo
                                     unsigned long long* bad_key, cudaStream_t stream) {
   if (n <= 0) return cudaSuccess;
   const int blocks = grid_for(n, kThreads, 8);
-  datetime_convert_kernel<<<blocks, kThreads, 0, stream>>>(in, out, n, index_base, src, dst,
-                                                           bad_key);
+  // unit lengths in picoseconds, day .. picosecond
+  static const long long kLength[13] = {0, 0, 0, 86400000000000000LL, 3600000000000000LL, 60000000000000LL,
+                                        1000000000000LL, 1000000000LL, 1000000LL, 1000LL, 1LL, 0, 0};
+  FastPlan plan{0, 1, 0ULL, 1.0};
+  if (src >= PYI_RES_DAY && src <= PYI_RES_PICOSECOND && dst >= PYI_RES_DAY && dst <= PYI_RES_PICOSECOND &&
+      src != dst) {
+    const long long ls = kLength[src], ld = kLength[dst];
+    const long long dst_mag = dst >= PYI_RES_SECOND ? 1000000000000LL / ld : 1;
+    const long long slack = 3 * 86400LL * dst_mag;  // <= 2.6e17
+    const long long top = 9223372036854775807LL - slack;
+    if (ls > ld) {
+      plan.kind = 1;
+      plan.factor = ls / ld;
+      plan.safe_abs = static_cast<unsigned long long>(top / plan.factor);
+    } else {
+      plan.kind = 2;
+      plan.factor = ld / ls;
+      plan.safe_abs = static_cast<unsigned long long>(top);
+    }
+    plan.inv_factor = 1.0 / static_cast<double>(plan.factor);
+  }
+  if (plan.kind == 1) {
+    datetime_convert_kernel<1><<<blocks, kThreads, 0, stream>>>(in, out, n, index_base, src, dst, plan, bad_key);
+  } else if (plan.kind == 2) {
+    datetime_convert_kernel<2><<<blocks, kThreads, 0, stream>>>(in, out, n, index_base, src, dst, plan, bad_key);
+  } else {
+    datetime_convert_kernel<0><<<blocks, kThreads, 0, stream>>>(in, out, n, index_base, src, dst, plan, bad_key);
+  }
   g_launches.fetch_add(1);
   return cudaGetLastError();
 }

@@ -353,6 +353,54 @@ def test_datetime_conversion_overflow(pyi, orc_best):
         pyi.core.convert_resolution(nat, "s", "ns")
 
 
+def test_datetime_conversion_extremes(pyi, orc_best):
+    """The closed form of the fixed-length units (value * F / floor(value / G), pyi_datetime.cu) hands
+    over to the checked sequence where an intermediate of the reference could overflow: values around
+    that hand-over, around the true overflow limit and at the ends of int64, one by one against the
+    reference (its result, or its overflow error)."""
+    ref = orc_best
+    fixed = ["D", "h", "m", "s", "ms", "us", "ns", "ps"]
+    length = dict(zip(fixed, [86400 * 10 ** 12, 3600 * 10 ** 12, 60 * 10 ** 12, 10 ** 12, 10 ** 9, 10 ** 6, 10 ** 3, 1]))
+    top, low = 2 ** 63 - 1, -2 ** 63
+    rng = np.random.default_rng(8)
+    checked = raised = 0
+    for src in fixed:
+        for dst in fixed + ["W", "fs"]:
+            if src == dst:
+                continue
+            f = max(1, length[src] // length.get(dst, 1)) if dst in length else 1
+            mag = 10 ** 12 // length[dst] if dst in length and length[dst] <= 10 ** 12 else 1
+            edges = {0, 1, -1, top, low, low + 1, 2 ** 62, -2 ** 62, top // f, -(top // f)}
+            for centre in (top // f, (top - 3 * 86400 * mag) // f, top - 3 * 86400 * mag):
+                for d in (-2, -1, 0, 1, 2, 86400 * mag, -86400 * mag):
+                    edges.update({centre + d, -(centre + d)})
+            edges.update(int(v) for v in rng.integers(low, top, 12, dtype=np.int64))
+            vals = np.array(sorted(v for v in edges if low <= v <= top), dtype=np.int64)
+            want = np.zeros_like(vals)
+            bad = np.zeros(vals.size, dtype=bool)
+            for k in range(vals.size):
+                try:
+                    want[k] = ref.datetime_convert(vals[k:k + 1], src, dst)[0]
+                except OverflowError:
+                    bad[k] = True
+            good = vals[~bad]
+            if good.size:
+                got = pyi.core.convert_resolution(good, src, dst)
+                assert np.array_equal(got, want[~bad]), (src, dst, good[got != want[~bad]][:4])
+                checked += good.size
+            if bad.any():  # the whole array: same error as the reference (first failing value)
+                with pytest.raises(OverflowError) as e_ref:
+                    ref.datetime_convert(vals, src, dst)
+                with pytest.raises(OverflowError) as e_got:
+                    pyi.core.convert_resolution(vals, src, dst)
+                assert str(e_ref.value) in str(e_got.value), (src, dst)
+                for v in vals[bad][:6]:
+                    with pytest.raises(OverflowError):
+                        pyi.core.convert_resolution(np.array([v], dtype=np.int64), src, dst)
+                raised += 1
+    assert checked > 1500 and raised > 20
+
+
 def test_temporal_axis_casts_on_device(pyi, orc_best):
     ref = orc_best
     """trivariate with datetime64[s] / [D] coordinates on a datetime64[ns]
