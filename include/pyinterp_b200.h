@@ -265,6 +265,15 @@ int pyi_grid_update(pyi_grid *grid, const void *data, int mem);
  * type). Skipped, with PYI_OK, when it would take more than half of the free
  * device memory: the kernels then gather from the plain C-order array. */
 int pyi_grid_pack(pyi_grid *grid);
+/* The reference's Grid borrows the caller's numpy buffer (pybind/grid.hpp:214-226), which may be
+ * written between calls (pyinterp/tests/core/windowed/test_bivariate.py:234-250).  Instead of
+ * pyi_grid_update before every call, a binding can hand the buffer over once: `host_data` (the
+ * grid's bytes, C order, alive and at the same address until pyi_grid_destroy) is page-locked in
+ * place.  pyi_grid_mark_stale then says "the buffer may have changed": the next compute call either
+ * reads it in place over PCIe (few points against a large array: no upload at all) or refreshes the
+ * device copies first, at link speed.  Failure to page-lock only costs speed. */
+int pyi_grid_track_host(pyi_grid *grid, const void *host_data);
+int pyi_grid_mark_stale(pyi_grid *grid);
 void pyi_grid_destroy(pyi_grid *grid);
 
 /* ---- the hot path ---------------------------------------------------------- */

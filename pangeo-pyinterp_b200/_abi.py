@@ -152,6 +152,8 @@ SIGNATURES = {
     "pyi_grid_create": (_P, [C.c_int, C.POINTER(_P), C.c_int, _P, _I64P, C.c_int, C.c_uint, _IP]),
     "pyi_grid_update": (C.c_int, [_P, _P, C.c_int]),
     "pyi_grid_pack": (C.c_int, [_P]),
+    "pyi_grid_track_host": (C.c_int, [_P, _P]),
+    "pyi_grid_mark_stale": (C.c_int, [_P]),
     "pyi_grid_destroy": (None, [_P]),
     "pyi_geometric": (C.c_int, [_P, C.POINTER(GeometricConfig), C.c_int64, _P, _P, _P, _P, _P,
                                 C.c_int, _I64P, _IP, _P]),

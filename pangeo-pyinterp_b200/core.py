@@ -13,6 +13,7 @@ host-buffer path; torch CUDA tensors stay on the device.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import Any
 
 import numpy as np
@@ -443,6 +444,13 @@ class Grid:
         if not self._h:
             _abi.check(st.value, "Grid")
             raise ValueError(lib.pyi_last_error().decode())
+        # a borrowed C-contiguous host array is handed over once (page-locked in place): calls then
+        # only say that it may have changed, and the library decides between reading it in place
+        # and refreshing the device copies (pyi_grid_track_host)
+        self._tracked = False
+        if (self._array is not None and not self._resident and src is self._array and src.nbytes > 0
+                and os.environ.get("PYINTERP_B200_TRACK_HOST", "1") != "0"):
+            self._tracked = lib.pyi_grid_track_host(self._h, ptr) == _abi.PYI_OK
 
     def __del__(self):
         h = getattr(self, "_h", None)
@@ -505,7 +513,11 @@ class Grid:
             _abi.check(_lib().pyi_grid_update(self._h, _np_ptr(src), _abi.PYI_MEM_HOST), "Grid.refresh")
 
     def _before_call(self) -> None:
-        if not self._resident:
+        if self._resident:
+            return
+        if self._tracked:
+            _abi.check(_lib().pyi_grid_mark_stale(self._h), "Grid")
+        else:
             self.refresh()
 
 

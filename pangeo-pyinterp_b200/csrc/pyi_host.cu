@@ -750,6 +750,13 @@ struct pyi_grid {
   // cubic coefficients of the separable bicubic stencil (pyi_bicubics.cuh)
   int cw_ok{0};
   double cw[2][8][4]{};
+  // The caller's host array when it may change between calls (pyi_grid_track_host): page-locked in
+  // place, so that a refresh runs at link speed and a small call can read it over PCIe directly.
+  const void* host_src{nullptr};
+  const void* host_dev{nullptr};  // device-side alias of host_src, null when it could not be mapped
+  bool host_registered{false};    // this handle page-locked it (released in pyi_grid_destroy)
+  mutable std::atomic<int> stale{0};
+  mutable std::mutex update_mu;
 };
 
 namespace {
@@ -919,7 +926,18 @@ void free_replica(int device, GridReplica& r) {
 // View of `grid` on `device` (the calling thread's current device).  On the
 // grid's own device that is the handle itself; elsewhere a replica is created
 // or refreshed with peer copies (NVLink when peer access is available).
+// Set for the duration of a small host-memory call on a tracked grid: kernels read the caller's
+// page-locked array through its device alias (no packed copy, no plane-major copy: generic kernels).
+thread_local const void* tl_inplace = nullptr;
+
 int grid_view(const pyi_grid* grid, int device, GridView& view) {
+  if (device == grid->device && tl_inplace != nullptr) {
+    view.data = tl_inplace;
+    view.packed = nullptr;
+    view.planes = nullptr;
+    view.dax = grid->dax;
+    return PYI_OK;
+  }
   if (device == grid->device) {
     view.data = grid->d_data;
     view.packed = grid->d_packed;
@@ -1097,6 +1115,31 @@ int require_grid_device(const pyi_grid* grid) {
   }
   keep_pool_cached(dev);
   return PYI_OK;
+}
+
+// A tracked grid whose host array may have changed since the device copies were made
+// (pyi_grid_mark_stale): a small host-memory call reads the array in place -- `touched` bytes of
+// scattered sectors against the whole array over the same link -- and leaves the copies stale;
+// any other call refreshes them first.
+struct InPlace {
+  bool on{false};
+  ~InPlace() {
+    if (on) tl_inplace = nullptr;
+  }
+};
+int sync_grid(const pyi_grid* grid, long long n, long long touched_per_point, int mem, InPlace& inplace) {
+  if (grid->host_src == nullptr || grid->stale.load() == 0) return PYI_OK;
+  if (mem == PYI_MEM_HOST && grid->host_dev != nullptr && n < kShardMinPoints &&
+      static_cast<double>(n) * static_cast<double>(touched_per_point) * 4.0 <= static_cast<double>(grid->bytes)) {
+    tl_inplace = grid->host_dev;
+    inplace.on = true;
+    return PYI_OK;
+  }
+  std::lock_guard<std::mutex> lock(grid->update_mu);
+  if (grid->stale.load() == 0) return PYI_OK;
+  const int st = pyi_grid_update(const_cast<pyi_grid*>(grid), grid->host_src, PYI_MEM_HOST);
+  if (st == PYI_OK) grid->stale.store(0);
+  return st;
 }
 
 }  // namespace
@@ -1456,10 +1499,69 @@ int pyi_grid_pack(pyi_grid* grid) {
   return PYI_OK;
 }
 
+namespace {
+// Buffers page-locked by pyi_grid_track_host, counted per base address: several handles may share one
+// array, and it stays locked until the last of them is destroyed.
+std::mutex g_reg_mu;
+std::map<const void*, std::pair<size_t, int>> g_registered;
+}  // namespace
+
+int pyi_grid_track_host(pyi_grid* grid, const void* host_data) {
+  if (!grid || !host_data) return fail(PYI_BAD_ARG, "null argument");
+  if (grid->host_src != nullptr) return fail(PYI_BAD_ARG, "pyi_grid_track_host: the grid already tracks an array");
+  DeviceGuard guard(grid->device);
+  if (guard.err != cudaSuccess) return cuda_fail(guard.err, "cudaSetDevice");
+  grid->host_src = host_data;
+  grid->host_dev = nullptr;
+  // Page-lock the array where it lies.  An array somebody else page-locked (the caller, an
+  // overlapping registration) is still refreshed at link speed but never read in place: its
+  // mapping is not this library's to keep alive.  Failure only costs speed.
+  std::lock_guard<std::mutex> lock(g_reg_mu);
+  auto it = g_registered.find(host_data);
+  if (it != g_registered.end() && it->second.first >= grid->bytes) {
+    ++it->second.second;
+    grid->host_registered = true;
+  } else if (it == g_registered.end()) {
+    const cudaError_t e = cudaHostRegister(const_cast<void*>(host_data), std::max<size_t>(grid->bytes, 1),
+                                           cudaHostRegisterPortable | cudaHostRegisterMapped);
+    if (e == cudaSuccess) {
+      g_registered[host_data] = {grid->bytes, 1};
+      grid->host_registered = true;
+    } else {
+      cudaGetLastError();
+    }
+  }
+  if (grid->host_registered) {
+    void* alias = nullptr;
+    if (cudaHostGetDevicePointer(&alias, const_cast<void*>(host_data), 0) == cudaSuccess) {
+      grid->host_dev = alias;
+    } else {
+      cudaGetLastError();
+    }
+  }
+  return PYI_OK;
+}
+
+int pyi_grid_mark_stale(pyi_grid* grid) {
+  if (!grid) return fail(PYI_BAD_ARG, "null grid");
+  if (grid->host_src == nullptr) return fail(PYI_BAD_ARG, "pyi_grid_mark_stale: the grid tracks no host array");
+  grid->stale.store(1);
+  return PYI_OK;
+}
+
 void pyi_grid_destroy(pyi_grid* grid) {
   if (!grid) return;
   {
     DeviceGuard guard(grid->device);
+    if (grid->host_registered) {
+      std::lock_guard<std::mutex> lock(g_reg_mu);
+      auto it = g_registered.find(grid->host_src);
+      if (it != g_registered.end() && --it->second.second == 0) {
+        cudaHostUnregister(const_cast<void*>(grid->host_src));
+        cudaGetLastError();
+        g_registered.erase(it);
+      }
+    }
     if (!grid->borrowed) cudaFree(grid->d_data);
     cudaFree(grid->d_packed);
     cudaFree(grid->d_planes);
@@ -1500,6 +1602,9 @@ int pyi_geometric(const pyi_grid* grid, const pyi_geometric_config* cfg, int64_t
   p.bounds_error = cfg->bounds_error;
   p.value_mode = cfg->value_mode;
   if (n == 0) return PYI_OK;
+  InPlace inplace;
+  st = sync_grid(grid, n, 32LL << grid->ndim, mem, inplace);  // 2^ndim corners, a 32-byte sector each
+  if (st != PYI_OK) return st;
   const size_t out_elem = result_is_f64(grid->dtype) ? 8 : 4;
   auto bind = [&](pyi::GeoParams& q, const GridView& v) {
     for (int k = 0; k < grid->ndim; ++k) q.ax[k] = v.dax[k];
@@ -1643,6 +1748,20 @@ int pyi_windowed(const pyi_grid* grid, const pyi_windowed_nd_config* cfg, int64_
     p.u6_ok[a] = grid->u6_ok[a];
     std::memcpy(p.u6[a], grid->u6[a], sizeof(p.u6[a]));
   }
+  InPlace inplace;
+  {
+    // sectors a point touches in the C-order array: 2-D window rows are contiguous along y; from
+    // 3-D on y is strided and every window value is a sector of its own (the z / u pair shares one
+    // about half of the time)
+    long long touched;
+    if (nd <= 2) {
+      touched = 2LL * cfg->half_x * std::max<long long>(64, 2LL * (nd == 2 ? cfg->half_y : 1) * 8 + 32);
+    } else {
+      touched = 2LL * cfg->half_x * 2LL * cfg->half_y * 48 * (nd >= 4 ? 2 : 1);
+    }
+    st = sync_grid(grid, n, touched, mem, inplace);
+    if (st != PYI_OK) return st;
+  }
   // the plane-major copy serves bicubic in every mode and, unless the caller asks for
   // bit-identical values, the other models' 6 x 6 fast pass (pyi_winmodels.cuh)
   const bool want_planes =
@@ -1650,7 +1769,7 @@ int pyi_windowed(const pyi_grid* grid, const pyi_windowed_nd_config* cfg, int64_
       (cfg->method == PYI_S_BICUBIC ||
        (cfg->value_mode != PYI_VALUES_EXACT && grid->cw_ok &&
         (grid->dtype == PYI_F64 || grid->dtype == PYI_F32)));
-  if (want_planes) {
+  if (want_planes && !inplace.on) {
     DeviceGuard guard(grid->device);
     if (guard.err != cudaSuccess) return cuda_fail(guard.err, "cudaSetDevice");
     st = grid_planes(grid, false);

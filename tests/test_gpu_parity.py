@@ -761,3 +761,51 @@ def test_divisors_with_all_ones_significand(pyi, orc_best, monkeypatch):
     assert np.array_equal(pyi.bivariate(grid2, x2, y2, "bicubic"), want, equal_nan=True)
     want, _ = orc_best.geometric(o2, g2, x2, y2, method=0, num_threads=0)
     assert np.array_equal(pyi.bivariate(grid2, x2, y2), want, equal_nan=True)
+
+
+def test_tracked_host_grid_in_place_and_refresh(pyi, synthetic, orc_best):
+    """A grid over a borrowed host array (pyi_grid_track_host): small calls read the page-locked array
+    in place, large calls refresh the device copies first; both see what the caller wrote into the
+    array since the last call (pyinterp/tests/core/windowed/test_bivariate.py:234-250), and agree with
+    a resident grid over a copy of the same values.  3-D as well; two handles over one array."""
+    lon, lat = synthetic.lon_axis_values(720), synthetic.lat_axis_values(360)
+    g = synthetic.field(lon, lat)
+    grid = pyi.Grid(pyi.Axis(lon, period=360.0), pyi.Axis(lat), g)
+    assert grid._tracked
+    caxes = [orc_best.axis(lon, period=360.0), orc_best.axis(lat)]
+    rng = np.random.default_rng(12)
+    for n in (50, 3_000, 400_000):  # in place, in place, refreshed (400 000 x 128 B x 4 > 2 MB)
+        x, y = rng.uniform(-200.0, 500.0, n), rng.uniform(-91.0, 91.0, n)
+        for round_ in range(2):
+            g[rng.integers(0, 720, 50), rng.integers(0, 360, 50)] = rng.normal(size=50)  # the caller writes
+            g[5 + round_, 7] = np.nan
+            resident = pyi.Grid(pyi.Axis(lon, period=360.0), pyi.Axis(lat), g.copy(), resident=True)
+            for method in ("bilinear", "nearest", "bicubic", "akima"):
+                got = pyi.bivariate(grid, x, y, method)
+                want = pyi.bivariate(resident, x, y, method)
+                assert np.array_equal(np.isnan(got), np.isnan(want)), (n, method)
+                close(got, want, 1.0, f"tracked {method} n={n}")
+            want, _ = orc_best.geometric(caxes, g, x, y, num_threads=0)
+            got = pyi.core.bivariate(grid, x, y, pyi.geometric.Bivariate.bilinear().with_value_mode("exact"))
+            assert np.array_equal(got, want, equal_nan=True), n
+    # bounds error from the in-place path
+    with pytest.raises(ValueError, match="out of bounds"):
+        pyi.bivariate(grid, np.array([10.0, 20.0]), np.array([0.0, 95.0]), "bilinear", bounds_error=True)
+    # a second handle over the same array; the first one goes away
+    other = pyi.Grid(pyi.Axis(lon, period=360.0), pyi.Axis(lat), g)
+    x, y = rng.uniform(0.0, 360.0, 100), rng.uniform(-80.0, 80.0, 100)
+    want = pyi.bivariate(grid, x, y)
+    del grid
+    g[:, :] += 1.0
+    assert np.allclose(pyi.bivariate(other, x, y), want + 1.0, rtol=0, atol=1e-12, equal_nan=True)
+    # 3-D, temporal axis
+    t = synthetic.time_axis_values(40)
+    g3 = synthetic.field(lon[::4], lat[::4], nz=40, dtype="float32")
+    grid3 = pyi.Grid(pyi.Axis(lon[::4], period=360.0), pyi.Axis(lat[::4]), pyi.TemporalAxis(t), g3)
+    res3 = pyi.Grid(pyi.Axis(lon[::4], period=360.0), pyi.Axis(lat[::4]), pyi.TemporalAxis(t), g3.copy(), resident=True)
+    for n in (200, 300_000):
+        x, y, z = synthetic.queries(n, 3, ndim=3, time_values=t)
+        for method in ("bilinear", "c_spline"):
+            got = pyi.trivariate(grid3, x, y, z.view("datetime64[ns]"), method)
+            want = pyi.trivariate(res3, x, y, z.view("datetime64[ns]"), method)
+            close(got, want, 1.0, f"tracked 3-D {method} n={n}")
