@@ -756,8 +756,15 @@ struct pyi_grid {
   const void* host_dev{nullptr};  // device-side alias of host_src, null when it could not be mapped
   bool host_registered{false};    // this handle page-locked it (released in pyi_grid_destroy)
   mutable std::atomic<int> stale{0};
+  // the plain device array is current but the packed / plane-major copies are not (a refresh made
+  // for a call too small to pay for rebuilding them)
+  mutable std::atomic<int> derived_stale{0};
   mutable std::mutex update_mu;
 };
+
+extern "C" {
+static int grid_planes(const pyi_grid* grid, bool refresh);
+}
 
 namespace {
 
@@ -1127,19 +1134,61 @@ struct InPlace {
     if (on) tl_inplace = nullptr;
   }
 };
-int sync_grid(const pyi_grid* grid, long long n, long long touched_per_point, int mem, InPlace& inplace) {
-  if (grid->host_src == nullptr || grid->stale.load() == 0) return PYI_OK;
-  if (mem == PYI_MEM_HOST && grid->host_dev != nullptr && n < kShardMinPoints &&
-      static_cast<double>(n) * static_cast<double>(touched_per_point) * 4.0 <= static_cast<double>(grid->bytes)) {
-    tl_inplace = grid->host_dev;
-    inplace.on = true;
-    return PYI_OK;
+int rebuild_derived(pyi_grid* grid) {
+  if (grid->d_planes) {
+    const int st = grid_planes(grid, true);
+    if (st != PYI_OK) return st;
   }
-  std::lock_guard<std::mutex> lock(grid->update_mu);
-  if (grid->stale.load() == 0) return PYI_OK;
-  const int st = pyi_grid_update(const_cast<pyi_grid*>(grid), grid->host_src, PYI_MEM_HOST);
-  if (st == PYI_OK) grid->stale.store(0);
-  return st;
+  if (grid->d_packed) return pyi_grid_pack(grid);
+  return PYI_OK;
+}
+
+// `plain_rate`: points per second of the kernels this call would run on the plain array (the generic
+// ones; for 2-D windowed calls the fast kernels themselves, which read nothing else).
+int sync_grid(const pyi_grid* grid, long long n, long long touched_per_point, int mem, InPlace& inplace,
+              double plain_rate) {
+  if (grid->host_src == nullptr) return PYI_OK;
+  pyi_grid* g = const_cast<pyi_grid*>(grid);
+  if (grid->stale.load() != 0) {
+    if (mem == PYI_MEM_HOST && grid->host_dev != nullptr && n < kShardMinPoints &&
+        static_cast<double>(n) * static_cast<double>(touched_per_point) * 4.0 <= static_cast<double>(grid->bytes)) {
+      tl_inplace = grid->host_dev;
+      inplace.on = true;
+      return PYI_OK;
+    }
+    std::lock_guard<std::mutex> lock(grid->update_mu);
+    if (grid->stale.load() != 0) {
+      // the plain array only; the derived copies follow below when this call can use them
+      DeviceGuard guard(grid->device);
+      if (guard.err != cudaSuccess) return cuda_fail(guard.err, "cudaSetDevice");
+      if (grid->borrowed) return fail(PYI_BAD_ARG, "a grid over borrowed device memory tracks no host array");
+      PYI_CUDA(cudaMemcpy(g->d_data, grid->host_src, grid->bytes, cudaMemcpyHostToDevice));
+      grid->derived_stale.store(1);
+      grid->stale.store(0);
+      grid->version.fetch_add(1);
+    }
+  }
+  if (grid->derived_stale.load() != 0) {
+    // A call that the kernels reading the plain array finish sooner than the packed (2^ndim x the
+    // array) and plane-major copies take to rebuild runs on the plain array; the next larger call
+    // rebuilds them.
+    const double rebuild_s = 50e-6 + static_cast<double>(grid->bytes) *
+                                         (static_cast<double>(1 << grid->ndim) / 1.5e12 + 1.0 / 1.0e12);
+    if (mem == PYI_MEM_HOST && n < kShardMinPoints && static_cast<double>(n) < plain_rate * rebuild_s) {
+      tl_inplace = grid->d_data;
+      inplace.on = true;
+      return PYI_OK;
+    }
+    std::lock_guard<std::mutex> lock(grid->update_mu);
+    if (grid->derived_stale.load() != 0) {
+      DeviceGuard guard(grid->device);
+      if (guard.err != cudaSuccess) return cuda_fail(guard.err, "cudaSetDevice");
+      const int st = rebuild_derived(g);
+      if (st != PYI_OK) return st;
+      grid->derived_stale.store(0);
+    }
+  }
+  return PYI_OK;
 }
 
 }  // namespace
@@ -1460,6 +1509,7 @@ int pyi_grid_update(pyi_grid* grid, const void* data, int mem) {
                         mem == PYI_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice));
   }
   grid->version.fetch_add(1);
+  grid->derived_stale.store(0);
   if (grid->d_planes) {
     int st = grid_planes(grid, true);
     if (st != PYI_OK) return st;
@@ -1603,7 +1653,8 @@ int pyi_geometric(const pyi_grid* grid, const pyi_geometric_config* cfg, int64_t
   p.value_mode = cfg->value_mode;
   if (n == 0) return PYI_OK;
   InPlace inplace;
-  st = sync_grid(grid, n, 32LL << grid->ndim, mem, inplace);  // 2^ndim corners, a 32-byte sector each
+  // 2^ndim corners, a 32-byte sector each; generic kernel: 5-9 Gpts/s
+  st = sync_grid(grid, n, 32LL << grid->ndim, mem, inplace, 5e9);
   if (st != PYI_OK) return st;
   const size_t out_elem = result_is_f64(grid->dtype) ? 8 : 4;
   auto bind = [&](pyi::GeoParams& q, const GridView& v) {
@@ -1759,7 +1810,10 @@ int pyi_windowed(const pyi_grid* grid, const pyi_windowed_nd_config* cfg, int64_
     } else {
       touched = 2LL * cfg->half_x * 2LL * cfg->half_y * 48 * (nd >= 4 ? 2 : 1);
     }
-    st = sync_grid(grid, n, touched, mem, inplace);
+    // K6 on the plain array: ~1e9 (1-D), 2e8 (3-D), 1e8 (4-D) points/s; 2-D windowed kernels read
+    // the plain array anyway
+    const double plain_rate = nd == 2 ? 1e30 : (nd == 1 ? 1e9 : (nd == 3 ? 2e8 : 1e8));
+    st = sync_grid(grid, n, touched, mem, inplace, plain_rate);
     if (st != PYI_OK) return st;
   }
   // the plane-major copy serves bicubic in every mode and, unless the caller asks for

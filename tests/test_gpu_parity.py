@@ -768,16 +768,18 @@ def test_tracked_host_grid_in_place_and_refresh(pyi, synthetic, orc_best):
     in place, large calls refresh the device copies first; both see what the caller wrote into the
     array since the last call (pyinterp/tests/core/windowed/test_bivariate.py:234-250), and agree with
     a resident grid over a copy of the same values.  3-D as well; two handles over one array."""
-    lon, lat = synthetic.lon_axis_values(720), synthetic.lat_axis_values(360)
+    lon, lat = synthetic.lon_axis_values(1440), synthetic.lat_axis_values(720)
     g = synthetic.field(lon, lat)
     grid = pyi.Grid(pyi.Axis(lon, period=360.0), pyi.Axis(lat), g)
     assert grid._tracked
     caxes = [orc_best.axis(lon, period=360.0), orc_best.axis(lat)]
     rng = np.random.default_rng(12)
-    for n in (50, 3_000, 400_000):  # in place, in place, refreshed (400 000 x 128 B x 4 > 2 MB)
+    # in place; in place; plain array refreshed, generic kernels (400 000 x 128 B x 4 > 8.3 MB, below
+    # 2^20 points); packed copy rebuilt, fast kernels
+    for n in (50, 3_000, 400_000, 1_200_000):
         x, y = rng.uniform(-200.0, 500.0, n), rng.uniform(-91.0, 91.0, n)
         for round_ in range(2):
-            g[rng.integers(0, 720, 50), rng.integers(0, 360, 50)] = rng.normal(size=50)  # the caller writes
+            g[rng.integers(0, 1440, 50), rng.integers(0, 720, 50)] = rng.normal(size=50)  # the caller writes
             g[5 + round_, 7] = np.nan
             resident = pyi.Grid(pyi.Axis(lon, period=360.0), pyi.Axis(lat), g.copy(), resident=True)
             for method in ("bilinear", "nearest", "bicubic", "akima"):
