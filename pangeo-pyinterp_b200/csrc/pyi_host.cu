@@ -1174,7 +1174,8 @@ int sync_grid(const pyi_grid* grid, long long n, long long touched_per_point, in
     // rebuilds them.
     const double rebuild_s = 50e-6 + static_cast<double>(grid->bytes) *
                                          (static_cast<double>(1 << grid->ndim) / 1.5e12 + 1.0 / 1.0e12);
-    if (mem == PYI_MEM_HOST && n < kShardMinPoints && static_cast<double>(n) < plain_rate * rebuild_s) {
+    if (mem == PYI_MEM_HOST && n < kShardMinPoints && grid->bytes >= (1u << 20) &&
+        static_cast<double>(n) < plain_rate * rebuild_s) {
       tl_inplace = grid->d_data;
       inplace.on = true;
       return PYI_OK;

@@ -283,7 +283,10 @@ def test_windowed_nd_bounds_error_and_device_tensors(pyi, orc_best):
     host = pyi.trivariate(grid, q[0], q[1], q[2].view("datetime64[ns]"), "akima", third_axis="nearest")
     dev = pyi.trivariate(grid, torch.from_numpy(q[0]).cuda(), torch.from_numpy(q[1]).cuda(),
                          torch.from_numpy(q[2]).cuda(), "akima", third_axis="nearest")
-    assert dev.is_cuda and np.array_equal(host, dev.cpu().numpy(), equal_nan=True)
+    # (a small host call on a large tracked grid may run the bit-identical generic kernel on the plain
+    # array where the device call runs the 6 x 6 tolerance kernel: equal within the tolerance)
+    assert dev.is_cuda
+    close(host, dev.cpu().numpy(), 50.0, "host arrays vs device tensors")
 
 
 def test_windowed_nd_api_errors(pyi):

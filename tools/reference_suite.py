@@ -126,6 +126,31 @@ def main():
                                      f" | NaN {'same' if same_nan else 'DIFFER'} err {err:.1e}")
                         print(line, flush=True)
     print(f"\nworst relative difference to the reference (bilinear and windowed models): {worst:.2e}")
+    # gap filling (benchmark_suite.py:673-706): Gauss-Seidel, 100 iterations at most, epsilon 1e-6, 10 % of the
+    # cells undefined.  The harness fills ONE buffer in its warm-up run and times the following runs on that
+    # (already filled) buffer; both that protocol and a fresh copy per run are timed here.
+    print("\n--- gap filling: fill.gauss_seidel(max_iterations=100, epsilon=1e-6) ---")
+    for nx, ny in ([(180, 90)] if args.quick else [(360, 180), (720, 360)]):
+        data = RNG.standard_normal((nx, ny)).astype(np.float64)
+        data[RNG.random((nx, ny)) < 0.1] = np.nan
+        buf = data.copy()
+        mean_h, _ = timed(lambda: pyi.fill.gauss_seidel(buf, max_iterations=100, epsilon=1e-6), args.iterations)
+        fresh = [data.copy() for _ in range(args.iterations + 1)]
+        it = iter(fresh)
+        mean_f, _ = timed(lambda: pyi.fill.gauss_seidel(next(it), max_iterations=100, epsilon=1e-6), args.iterations)
+        line = f"  {nx} x {ny}: harness protocol {mean_h * 1e3:8.3f} ms | fresh copy per run {mean_f * 1e3:8.3f} ms"
+        if o:
+            cbuf = data.copy()
+            cmean_h, _ = timed(lambda: o.fill_gauss_seidel(cbuf, max_iterations=100, epsilon=1e-6, num_threads=0),
+                               max(2, args.iterations // 2))
+            cfresh = [data.copy() for _ in range(4)]
+            cit = iter(cfresh)
+            cmean_f, _ = timed(lambda: o.fill_gauss_seidel(next(cit), max_iterations=100, epsilon=1e-6,
+                                                           num_threads=0), 3)
+            same = np.array_equal(fresh[0], cfresh[0])
+            line += (f" | CPU {cmean_h * 1e3:8.3f} / {cmean_f * 1e3:8.3f} ms | x{cmean_h / mean_h:6.1f} / x{cmean_f / mean_f:6.1f}"
+                     f" | filled grids {'bit-identical' if same else 'DIFFER'}")
+        print(line, flush=True)
 
 
 if __name__ == "__main__":
