@@ -417,6 +417,16 @@ int pyi_format_bounds_error(const pyi_grid *grid, int axis, const void *coord,
 int pyi_format_temporal(int is_timedelta, int resolution, int64_t value,
                         char *buf, size_t len);
 
+/* The window weights the 6 x 6 tolerance kernels use for a fitting model that is linear in the node
+ * values (pyi_spatial_method: bilinear, linear, the three c_spline models, polynomial), as polynomials
+ * in the cell coordinate t of the centre cell of six uniformly spaced nodes `step` apart:
+ * out[6 * j + d] = coefficient of t^d in the weight of node j, so that the reference's univariate
+ * operator()(xa, ya, xa[2] + t step) (univariate/{linear,cspline*,polynomial}.hpp) equals
+ * sum_j (sum_d out[6 j + d] t^d) ya[j] to rounding.  Host arithmetic only (no device needed): it
+ * exists so that the tables can be checked against the reference without a GPU.  PYI_BAD_ARG for
+ * the other models. */
+int pyi_model_stencil(int method, double step, double *out36);
+
 /* Number of kernel launches issued by this library in this process. */
 int64_t pyi_launch_count(void);
 

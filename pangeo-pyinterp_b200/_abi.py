@@ -170,6 +170,7 @@ SIGNATURES = {
     "pyi_fill_loess_static": (C.c_int, [_P, _P, C.c_int, C.c_int64, C.c_int64, C.POINTER(LoessConfig), _P]),
     "pyi_format_bounds_error": (C.c_int, [_P, C.c_int, _P, C.c_char_p, C.c_size_t]),
     "pyi_format_temporal": (C.c_int, [C.c_int, C.c_int, C.c_int64, C.c_char_p, C.c_size_t]),
+    "pyi_model_stencil": (C.c_int, [C.c_int, C.c_double, _P]),
     "pyi_launch_count": (C.c_int64, []),
 }
 

@@ -2255,6 +2255,27 @@ std::string temporal_text(bool timedelta, int res, long long value) {
 
 }  // namespace
 
+int pyi_model_stencil(int method, double step, double* out36) {
+  if (!out36 || !(step > 0.0)) return fail(PYI_BAD_ARG, "pyi_model_stencil: null output or non-positive step");
+  for (int k = 0; k < 36; ++k) out36[k] = 0.0;
+  if (method == PYI_S_POLYNOMIAL) {
+    double pw[6][6];
+    polynomial_stencil(step, pw);
+    for (int j = 0; j < 6; ++j) {
+      for (int d = 0; d < 6; ++d) out36[6 * j + d] = pw[j][d];
+    }
+    return PYI_OK;
+  }
+  double cw[8][4];
+  if (!model_stencil_cubics(method, cw)) {
+    return fail(PYI_BAD_ARG, "pyi_model_stencil: the model is not linear in the node values");
+  }
+  for (int j = 0; j < 6; ++j) {
+    for (int d = 0; d < 4; ++d) out36[6 * j + d] = cw[j + 1][d];
+  }
+  return PYI_OK;
+}
+
 int pyi_format_temporal(int is_timedelta, int resolution, int64_t value, char* buf, size_t len) {
   if (!buf || len == 0 || resolution < PYI_RES_YEAR || resolution > PYI_RES_ATTOSECOND) return -1;
   const std::string s = temporal_text(is_timedelta != 0, resolution, value);

@@ -89,3 +89,31 @@ def test_product_never_imports_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".hpp", ".h")):
                 text = open(os.path.join(dirpath, f), errors="replace").read()
                 assert "liboracle" not in text and "import orc" not in text and "oracle/" not in text, f
+
+
+@pytest.mark.parametrize("model", ["linear", "c_spline", "c_spline_not_a_knot", "c_spline_periodic", "polynomial"])
+def test_model_stencil_tables_against_the_oracle(model):
+    """pyi_model_stencil (host arithmetic): the window weights the 6 x 6 tolerance kernels use for the
+    fitting models that are linear in the node values, against the oracle's univariate model
+    (univariate/{linear,cspline,cspline_not_a_knot,cspline_periodic,polynomial}.hpp) on six uniform
+    nodes -- several steps and offsets (the polynomial table depends on the step: the reference's
+    divided-difference update is aliased), random node values, t across the centre cell."""
+    import orc
+    o = orc.Oracle("reference" if orc.available("reference") else "port")
+    abi = importlib.import_module("pangeo-pyinterp_b200._abi")
+    lib = abi.load()
+    rng = np.random.default_rng(4)
+    for step in (0.25, 1.0, 2.5, 1.0 / 3.0, 30.0):
+        table = np.zeros(36)
+        st = lib.pyi_model_stencil(abi.SPATIAL_METHODS[model], step, table.ctypes.data_as(C.c_void_p))
+        assert st == 0
+        table = table.reshape(6, 6)
+        for start in (0.0, -7.0 * step, 100.0 * step):
+            xa = start + np.arange(6) * step
+            ya = rng.normal(size=6) * 10.0
+            for t in (0.03, 0.25, 0.5, 0.8, 0.97):
+                want = o.univariate(model, xa, ya, xa[2] + t * step)
+                got = float(sum(np.polyval(table[j][::-1], t) * ya[j] for j in range(6)))
+                assert abs(got - want) <= 1e-12 * max(1.0, np.abs(ya).max()), (model, step, start, t, got, want)
+    bad = np.zeros(36)
+    assert lib.pyi_model_stencil(abi.SPATIAL_METHODS["akima"], 1.0, bad.ctypes.data_as(C.c_void_p)) != 0
